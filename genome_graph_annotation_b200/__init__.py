@@ -1,0 +1,381 @@
+"""B200-native query engine for genome-graph annotation matrices (BRWT / Multi-BRWT / column-major).
+
+Python is only a thin ctypes binding over the C ABI of ``libggq.so`` (include/ggq.h) — used by the
+tests and by bench.py.  The product is the CUDA library; the reference-facing host interface is the
+C++ ``BinaryMatrix`` adapter in include/ggq/gpu_matrix.hpp.
+
+There is no CPU fallback: importing works without a GPU (so that the symbol table can be checked),
+but every compute call needs a CUDA device and raises :class:`GgqError` otherwise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libggq.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "ggq.h")
+
+u64p = C.POINTER(C.c_uint64)
+u8p = C.POINTER(C.c_uint8)
+READ_FN = C.CFUNCTYPE(C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t)
+
+GGQ_OK = 0
+STATUS = {0: "GGQ_OK", -1: "GGQ_ERR_FORMAT", -2: "GGQ_ERR_CUDA", -3: "GGQ_ERR_OOM", -4: "GGQ_ERR_ARG",
+          -5: "GGQ_ERR_LIMIT", -6: "GGQ_ERR_INTERNAL"}
+
+
+class GgqError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("%s: %s" % (STATUS.get(code, code), msg))
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Load libggq.so (built in-tree by ``make -C genome_graph_annotation_b200/csrc``).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libggq.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "or `make -C genome_graph_annotation_b200/csrc` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    sig = {
+        "ggq_last_error": (C.c_char_p, []),
+        "ggq_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+        "ggq_brwt_load": (C.c_int, [READ_FN, vp, C.c_int, C.POINTER(vp)]),
+        "ggq_brwt_load_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.POINTER(vp)]),
+        "ggq_colmajor_load": (C.c_int, [READ_FN, vp, C.c_int, C.POINTER(vp)]),
+        "ggq_colmajor_load_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.POINTER(vp)]),
+        "ggq_brwt_synthesize": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(vp)]),
+        "ggq_free": (None, [vp]),
+        "ggq_num_rows": (C.c_uint64, [vp]),
+        "ggq_num_columns": (C.c_uint64, [vp]),
+        "ggq_num_relations": (C.c_uint64, [vp]),
+        "ggq_num_nodes": (C.c_uint64, [vp]),
+        "ggq_total_column_size": (C.c_uint64, [vp]),
+        "ggq_device_bytes": (C.c_uint64, [vp]),
+        "ggq_last_probe_count": (C.c_uint64, [vp]),
+        "ggq_get_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(vp)]),
+        "ggq_rows_offsets": (u64p, [vp]),
+        "ggq_rows_columns": (u64p, [vp]),
+        "ggq_rows_count": (C.c_uint64, [vp]),
+        "ggq_rows_result_free": (None, [vp]),
+        "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_slice_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(u64p), u64p]),
+        "ggq_buffer_free": (None, [vp]),
+        "ggq_workspace_create": (C.c_int, [vp, C.POINTER(vp)]),
+        "ggq_workspace_free": (None, [vp]),
+        "ggq_workspace_stream": (vp, [vp]),
+        "ggq_get_rows_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
+        "ggq_get": (C.c_int, [vp, u64p, u64p, C.c_uint64, u8p]),
+        "ggq_has_column": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u8p]),
+        "ggq_get_column": (C.c_int, [vp, C.c_uint64, C.POINTER(u64p), u64p]),
+        "ggq_bv_load_buffer": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.POINTER(vp)]),
+        "ggq_bv_build": (C.c_int, [C.c_int, u64p, C.c_uint64, C.c_int, C.POINTER(vp)]),
+        "ggq_bv_synthesize": (C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(vp)]),
+        "ggq_bv_free": (None, [vp]),
+        "ggq_bv_size": (C.c_uint64, [vp]),
+        "ggq_bv_num_set_bits": (C.c_uint64, [vp]),
+        "ggq_bv_is_inverted": (C.c_int, [vp]),
+        "ggq_bv_device_bytes": (C.c_uint64, [vp]),
+        "ggq_bv_rank1": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
+        "ggq_bv_select1": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
+        "ggq_bv_get": (C.c_int, [vp, u64p, C.c_uint64, u8p]),
+        "ggq_bv_rank1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_bv_select1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_bv_get_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    L._ggq_signatures = sig
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != GGQ_OK:
+        raise GgqError(rc, lib().ggq_last_error().decode("utf-8", "replace"))
+
+
+def _u64(a):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    return a, a.ctypes.data_as(u64p)
+
+
+def device_count():
+    n = C.c_int()
+    rc = lib().ggq_device_count(C.byref(n))
+    return n.value if rc == GGQ_OK else 0
+
+
+def mix64(x):
+    """splitmix64 finaliser on numpy uint64 arrays — the portable generator of SURVEY.md §8(d)."""
+    x = np.asarray(x, dtype=np.uint64).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(30)
+        x *= np.uint64(0xBF58476D1CE4E5B9)
+        x ^= x >> np.uint64(27)
+        x *= np.uint64(0x94D049BB133111EB)
+        x ^= x >> np.uint64(31)
+    return x
+
+
+def density_threshold(d):
+    """T = floor(d * 2^64), computed once in extended precision."""
+    t = int(np.floor(np.longdouble(d) * np.longdouble(2.0) ** 64))
+    return min(max(t, 0), (1 << 64) - 1)
+
+
+SEED_MUL = 0x9E3779B97F4A7C15
+
+
+class GpuMatrix:
+    """GPU-resident BinaryMatrix (reference interface: common/binary_matrix.hpp:9-29).
+
+    ``get_row(i)`` returns exactly what the reference's ``get_row(i)`` returns (same order);
+    ``get_rows / slice_rows / has_column`` are the batched compositions named by the north star.
+    """
+
+    def __init__(self, handle, kind):
+        self._h = C.c_void_p(handle)
+        self.kind = kind
+
+    # -- construction -----------------------------------------------------------------------
+    @classmethod
+    def load_brwt(cls, data, device=0):
+        """BRWT::load on the reference's serialized stream.  Returns (matrix, bytes_consumed)."""
+        h = C.c_void_p()
+        used = C.c_size_t()
+        _check(lib().ggq_brwt_load_buffer(data, len(data), C.byref(used), device, C.byref(h)))
+        m = cls(h.value, "brwt")
+        m.consumed = used.value
+        return m
+
+    @classmethod
+    def load_colmajor(cls, data, device=0):
+        h = C.c_void_p()
+        used = C.c_size_t()
+        _check(lib().ggq_colmajor_load_buffer(data, len(data), C.byref(used), device, C.byref(h)))
+        m = cls(h.value, "colmajor")
+        m.consumed = used.value
+        return m
+
+    @classmethod
+    def synthesize_brwt(cls, n_rows, n_cols, density, seed=42, arity=4, device=0, threshold=None):
+        h = C.c_void_p()
+        t = density_threshold(density) if threshold is None else threshold
+        _check(lib().ggq_brwt_synthesize(n_rows, n_cols, t, seed, arity, device, C.byref(h)))
+        m = cls(h.value, "brwt")
+        m.threshold, m.seed = t, seed
+        return m
+
+    def close(self):
+        if self._h:
+            lib().ggq_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- scalars ----------------------------------------------------------------------------
+    num_rows = property(lambda s: lib().ggq_num_rows(s._h))
+    num_columns = property(lambda s: lib().ggq_num_columns(s._h))
+    num_relations = property(lambda s: lib().ggq_num_relations(s._h))
+    num_nodes = property(lambda s: lib().ggq_num_nodes(s._h))
+    total_column_size = property(lambda s: lib().ggq_total_column_size(s._h))
+    device_bytes = property(lambda s: lib().ggq_device_bytes(s._h))
+    last_probe_count = property(lambda s: lib().ggq_last_probe_count(s._h))
+
+    # -- queries (host buffers) ---------------------------------------------------------------
+    def get_rows_csr(self, rows):
+        """-> (offsets[n+1], cols[offsets[n]]) as uint64 arrays."""
+        rows, rp = _u64(rows)
+        res = C.c_void_p()
+        _check(lib().ggq_get_rows(self._h, rp, rows.size, C.byref(res)))
+        try:
+            n = rows.size
+            off = np.ctypeslib.as_array(lib().ggq_rows_offsets(res), shape=(n + 1,)).copy()
+            total = int(off[-1])
+            if total:
+                cols = np.ctypeslib.as_array(lib().ggq_rows_columns(res), shape=(total,)).copy()
+            else:
+                cols = np.zeros(0, dtype=np.uint64)
+        finally:
+            lib().ggq_rows_result_free(res)
+        return off, cols
+
+    def get_rows_into(self, rows, offsets, cols):
+        """Caller-provided (e.g. pinned) output arrays; returns the number of column ids."""
+        n_cols = C.c_uint64()
+        _check(lib().ggq_get_rows_into(self._h, rows.ctypes.data_as(u64p), rows.size,
+                                       offsets.ctypes.data_as(u64p), cols.ctypes.data_as(u64p),
+                                       cols.size, C.byref(n_cols)))
+        return n_cols.value
+
+    def get_rows(self, rows):
+        off, cols = self.get_rows_csr(rows)
+        return [cols[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+    def get_row(self, row):
+        return self.get_rows_csr([row])[1]
+
+    def slice_rows(self, rows):
+        rows, rp = _u64(rows)
+        out = u64p()
+        n = C.c_uint64()
+        _check(lib().ggq_slice_rows(self._h, rp, rows.size, C.byref(out), C.byref(n)))
+        try:
+            res = np.ctypeslib.as_array(out, shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint64)
+        finally:
+            lib().ggq_buffer_free(out)
+        return res
+
+    def get_cells(self, rows, cols):
+        rows, rp = _u64(rows)
+        cols, cp = _u64(cols)
+        out = np.empty(rows.size, dtype=np.uint8)
+        _check(lib().ggq_get(self._h, rp, cp, rows.size, out.ctypes.data_as(u8p)))
+        return out
+
+    def get(self, row, col):
+        return bool(self.get_cells([row], [col])[0])
+
+    def has_column(self, rows, col):
+        rows, rp = _u64(rows)
+        out = np.empty(rows.size, dtype=np.uint8)
+        _check(lib().ggq_has_column(self._h, rp, rows.size, col, out.ctypes.data_as(u8p)))
+        return out
+
+    def get_column(self, col):
+        out = u64p()
+        n = C.c_uint64()
+        _check(lib().ggq_get_column(self._h, col, C.byref(out), C.byref(n)))
+        try:
+            res = np.ctypeslib.as_array(out, shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint64)
+        finally:
+            lib().ggq_buffer_free(out)
+        return res
+
+    # -- device-resident API (bench.py) -----------------------------------------------------
+    def workspace(self):
+        return Workspace(self)
+
+
+class Workspace:
+    def __init__(self, matrix):
+        self.m = matrix
+        h = C.c_void_p()
+        _check(lib().ggq_workspace_create(matrix._h, C.byref(h)))
+        self._h = h
+
+    @property
+    def stream(self):
+        return lib().ggq_workspace_stream(self._h)
+
+    def get_rows_device(self, d_rows_ptr, n, col_bytes=4):
+        """d_rows_ptr: device pointer (int).  -> (d_offsets_ptr, d_cols_ptr, n_cols), owned by the workspace."""
+        off = C.c_void_p()
+        cols = C.c_void_p()
+        total = C.c_uint64()
+        _check(lib().ggq_get_rows_device(self.m._h, self._h, C.c_void_p(d_rows_ptr), n, col_bytes,
+                                         C.byref(off), C.byref(cols), C.byref(total)))
+        return off.value, cols.value, total.value
+
+    def close(self):
+        if self._h:
+            lib().ggq_workspace_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+BV_KINDS = {"stat": 0, "sd": 1, "rrr": 2}
+
+
+class GpuBitVector:
+    """GPU-resident bit_vector_{stat,sd,rrr} (reference interface: common/bit_vector.hpp:12-46)."""
+
+    def __init__(self, handle, kind):
+        self._h = C.c_void_p(handle)
+        self.kind = kind
+
+    @classmethod
+    def build(cls, kind, words, n_bits, device=0):
+        words = np.ascontiguousarray(words, dtype=np.uint64)
+        if words.size == 0:
+            words = np.zeros(1, dtype=np.uint64)
+        h = C.c_void_p()
+        _check(lib().ggq_bv_build(BV_KINDS[kind], words.ctypes.data_as(u64p), n_bits, device, C.byref(h)))
+        return cls(h.value, kind)
+
+    @classmethod
+    def load(cls, kind, data, device=0):
+        h = C.c_void_p()
+        used = C.c_size_t()
+        _check(lib().ggq_bv_load_buffer(BV_KINDS[kind], data, len(data), C.byref(used), device, C.byref(h)))
+        v = cls(h.value, kind)
+        v.consumed = used.value
+        return v
+
+    @classmethod
+    def synthesize(cls, kind, n_bits, density, seed=42, device=0):
+        h = C.c_void_p()
+        _check(lib().ggq_bv_synthesize(BV_KINDS[kind], n_bits, density_threshold(density), seed, device, C.byref(h)))
+        return cls(h.value, kind)
+
+    def close(self):
+        if self._h:
+            lib().ggq_bv_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    size = property(lambda s: lib().ggq_bv_size(s._h))
+    num_set_bits = property(lambda s: lib().ggq_bv_num_set_bits(s._h))
+    is_inverted = property(lambda s: bool(lib().ggq_bv_is_inverted(s._h)))
+    device_bytes = property(lambda s: lib().ggq_bv_device_bytes(s._h))
+
+    def rank1(self, q):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        _check(lib().ggq_bv_rank1(self._h, qp, q.size, out.ctypes.data_as(u64p)))
+        return out
+
+    def select1(self, q):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        _check(lib().ggq_bv_select1(self._h, qp, q.size, out.ctypes.data_as(u64p)))
+        return out
+
+    def get(self, q):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint8)
+        _check(lib().ggq_bv_get(self._h, qp, q.size, out.ctypes.data_as(u8p)))
+        return out
+
+    def rank1_device(self, d_q, n, d_out, stream=0):
+        _check(lib().ggq_bv_rank1_device(self._h, d_q, n, d_out, stream))
+
+    def select1_device(self, d_q, n, d_out, stream=0):
+        _check(lib().ggq_bv_select1_device(self._h, d_q, n, d_out, stream))
+
+    def get_device(self, d_q, n, d_out, stream=0):
+        _check(lib().ggq_bv_get_device(self._h, d_q, n, d_out, stream))

@@ -1,0 +1,697 @@
+// libggq.so — host side of the engine: image upload, workspaces, kernel launches, the C ABI.
+// Kernels: ggq_kernels.cuh (queries, arena construction), ggq_builder.cuh (synthetic BRWT),
+// ggq_bv.cuh (bit_vector_{stat,sd,rrr} layouts).  No CPU fallback anywhere: every compute entry
+// point launches CUDA kernels or fails.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
+
+#include "../../include/ggq.h"
+#include "ggq_format.hpp"
+#include "ggq_tree.hpp"
+#include "ggq_kernels.cuh"
+#include "ggq_engine.hpp"
+#include "ggq_builder.cuh"
+#include "ggq_bv.cuh"
+#include "ggq_colmajor.cuh"
+
+namespace ggq {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string &msg) {
+    g_last_error = msg;
+    return code;
+}
+
+// ------------------------------------------------------------------------------------------
+// Image upload
+// ------------------------------------------------------------------------------------------
+template <typename T, typename S>
+static void upload_vec(DeviceBuf<T> &dst, const std::vector<S> &src, size_t min_elems = 1) {
+    static_assert(sizeof(T) == sizeof(S), "element size mismatch");
+    dst.alloc(std::max(src.size(), min_elems));
+    if (!src.empty()) CUDA_CHECK(cudaMemcpy(dst.p, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+}
+
+// chunk table for the header passes: one chunk = kChunkBlocks blocks of one lane
+void build_chunk_table(const FlatTree &t, std::vector<u32> *chunk_lane, std::vector<u32> *chunk_first,
+                       std::vector<u32> *lane_chunk_off) {
+    u32 G = t.n_groups();
+    lane_chunk_off->assign(size_t(G) * 4 + 1, 0);
+    chunk_lane->clear();
+    chunk_first->clear();
+    for (u32 g = 0; g < G; ++g) {
+        u32 cnt = u32(t.group_hot[g] >> kGhCntShift) & 7u;
+        u64 nb = t.group_nblocks[g];
+        if (nb > 0xFFFFFFFFull) throw ParseError("vector has more blocks than the engine supports");
+        for (u32 k = 0; k < 4; ++k) {
+            (*lane_chunk_off)[g * 4 + k] = u32(chunk_lane->size());
+            if (k >= cnt) continue;
+            for (u64 b = 0; b < nb; b += kChunkBlocks) {
+                chunk_lane->push_back(g * 4 + k);
+                chunk_first->push_back(u32(b));
+            }
+        }
+    }
+    (*lane_chunk_off)[size_t(G) * 4] = u32(chunk_lane->size());
+    if (chunk_lane->size() > 0xFFFFFFF0ull) throw ParseError("too many chunks");
+}
+
+static dim3 chunk_grid(u64 n_chunks) {
+    u64 x = std::min<u64>(n_chunks, 1u << 20);
+    u64 y = (n_chunks + x - 1) / std::max<u64>(x, 1);
+    return dim3(unsigned(std::max<u64>(x, 1)), unsigned(std::max<u64>(y, 1)));
+}
+
+// Builds rank headers, superblock bases, lane totals and select samples over a filled arena.
+void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
+    std::vector<u32> chunk_lane, chunk_first, lane_chunk_off;
+    build_chunk_table(t, &chunk_lane, &chunk_first, &lane_chunk_off);
+    DeviceBuf<u32> d_cl, d_cf, d_lco, d_sum;
+    DeviceBuf<u64> d_base;
+    upload_vec(d_cl, chunk_lane);
+    upload_vec(d_cf, chunk_first);
+    upload_vec(d_lco, lane_chunk_off);
+    u64 nch = chunk_lane.size();
+    d_sum.alloc(std::max<u64>(nch, 1));
+    d_base.alloc(std::max<u64>(nch, 1));
+    ChunkTable ct{d_cl.p, d_cf.p, d_lco.p, nch};
+    u32 n_lanes = t.n_groups() * 4;
+    if (nch) {
+        chunk_sum_kernel<<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_sum.p);
+        lane_scan_kernel<<<n_lanes, 256>>>(d_lco.p, d_sum.p, d_base.p, lane_ones.p, lane_sb_off.p, sb_base.p, n_lanes);
+        CUDA_CHECK(cudaGetLastError());
+    }
+    if (!ones_known) {
+        // synthetic trees: select sample geometry depends on the ones just counted
+        std::vector<u64> ones(n_lanes);
+        CUDA_CHECK(cudaMemcpy(ones.data(), lane_ones.p, n_lanes * 8, cudaMemcpyDeviceToHost));
+        FlatTree &mt = const_cast<FlatTree &>(t);
+        u64 sel_total = 0;
+        for (u32 li = 0; li < n_lanes; ++li) {
+            u32 node = mt.lane_node[li];
+            mt.lane_sel_off[li] = sel_total;
+            if (node == ~0u) continue;
+            mt.nodes[node].ones = ones[li];
+            if (!mt.nodes[node].children.empty() || mt.nodes[node].parent < 0)
+                sel_total += ((ones[li] + (1ull << kSelectShift) - 1) >> kSelectShift) + 1;
+        }
+        mt.total_sel = sel_total;
+        upload_vec(lane_sel_off, mt.lane_sel_off);
+        sel.alloc(std::max<u64>(sel_total, 1));
+    }
+    if (nch) {
+        header_kernel<<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_base.p,
+                                                        lane_info.p, lane_sel_off.p, sel.p, 1);
+        CUDA_CHECK(cudaGetLastError());
+    }
+    CUDA_CHECK(cudaDeviceSynchronize());
+}
+
+void Matrix::upload_tables(const FlatTree &t) {
+    upload_vec(group_hot, t.group_hot);
+    upload_vec(group_nblocks, t.group_nblocks);
+    upload_vec(lane_info, t.lane_info);
+    upload_vec(lane_aux, t.lane_aux);
+    upload_vec(lane_sb_off, t.lane_sb_off);
+    upload_vec(lane_sel_off, t.lane_sel_off);
+    upload_vec(leaf_col, t.leaf_col);
+    upload_vec(col_path_off, t.col_path_off);
+    upload_vec(col_path, t.col_path);
+    lane_ones.alloc(size_t(t.n_groups()) * 4);
+    CUDA_CHECK(cudaMemset(lane_ones.p, 0, size_t(t.n_groups()) * 4 * 8));
+    sb_base.alloc(std::max<u64>(t.total_sb, 1));
+    CUDA_CHECK(cudaMemset(sb_base.p, 0, std::max<u64>(t.total_sb, 1) * 8));
+}
+
+void Matrix::refresh_img() {
+    img.slots = slots.p;
+    img.group_hot = group_hot.p;
+    img.group_nblocks = group_nblocks.p;
+    img.lane_info = lane_info.p;
+    img.lane_aux = lane_aux.p;
+    img.lane_sb_off = lane_sb_off.p;
+    img.lane_sel_off = lane_sel_off.p;
+    img.lane_ones = lane_ones.p;
+    img.sb_base = sb_base.p;
+    img.sel = sel.p;
+    img.leaf_col = leaf_col.p;
+    img.col_path_off = col_path_off.p;
+    img.col_path = col_path.p;
+    img.n_rows = tree.n_rows;
+    img.n_cols = u32(tree.n_cols);
+    img.n_groups = tree.n_groups();
+    img.multi_leaf = tree.multi_column_leaves;
+}
+
+void Matrix::derive_stats() {
+    n_nodes = tree.nodes.size();
+    total_column_size = 0;
+    num_relations = 0;
+    for (const FlatNode &n : tree.nodes) {
+        total_column_size += n.size;
+        if (n.children.empty()) num_relations += n.ones * n.cols.size();
+    }
+    // descent kernel configuration
+    bm_words = u32((tree.leaf_col.size() + 31) / 32);
+    if (bm_words == 0) bm_words = 1;
+    int max_smem = 0;
+    CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    // rows per warp batch: as many as fit a ~5 KB/warp bitmap budget, at most 8
+    rb = 8;
+    while (rb > 1 && size_t(rb) * bm_words * 4 > 5 * 1024) rb >>= 1;
+    u32 worst = simulate_stack(tree, rb, kItemsPerIter) + 8;
+    cap_s = std::min<u32>(std::max<u32>(worst, 32), 192);
+    cap_s = (cap_s + 1) & ~1u;
+    cap_spill = worst > cap_s ? worst - cap_s : 0;
+    rows_smem = size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(rb) * bm_words * 4);
+    if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
+    CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
+    int per_sm = 0;
+    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel, kRowsWarps * 32, rows_smem));
+    if (per_sm < 1) per_sm = 1;
+    rows_grid = u32(sm_count * per_sm);
+    device_bytes = slots.bytes() + sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
+                   lane_info.bytes() * 3 + lane_sel_off.bytes() * 2 + leaf_col.bytes() + col_path.bytes() + col_path_off.bytes();
+}
+
+// host-parsed tree (plain bits per node) -> device image
+static Matrix *upload_brwt(FlatTree &&tree, int device) {
+    std::unique_ptr<Matrix> m(new Matrix());
+    m->kind = Matrix::BRWT;
+    m->device = device;
+    CUDA_CHECK(cudaSetDevice(device));
+    m->tree = std::move(tree);
+    FlatTree &t = m->tree;
+    assign_groups(&t);
+    assign_geometry(&t);
+    m->upload_tables(t);
+    m->slots.alloc(std::max<u64>(t.total_slots, 4));
+    CUDA_CHECK(cudaMemset(m->slots.p, 0, m->slots.bytes()));
+    m->sel.alloc(std::max<u64>(t.total_sel, 1));
+    // plain bits of all nodes, concatenated
+    u32 n_lanes = t.n_groups() * 4;
+    std::vector<u64> lane_plain_off(n_lanes, 0);
+    u64 total_words = 0;
+    for (u32 li = 0; li < n_lanes; ++li) {
+        if (t.lane_node[li] == ~0u) continue;
+        lane_plain_off[li] = total_words;
+        total_words += t.nodes[t.lane_node[li]].bits.w.size();
+    }
+    {
+        DeviceBuf<u32> d_plain;
+        DeviceBuf<u64> d_off;
+        d_plain.alloc(std::max<u64>(total_words, 1));
+        for (u32 li = 0; li < n_lanes; ++li) {
+            if (t.lane_node[li] == ~0u) continue;
+            const auto &w = t.nodes[t.lane_node[li]].bits.w;
+            CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+        }
+        upload_vec(d_off, lane_plain_off);
+        std::vector<u32> chunk_lane, chunk_first, lane_chunk_off;
+        build_chunk_table(t, &chunk_lane, &chunk_first, &lane_chunk_off);
+        DeviceBuf<u32> d_cl, d_cf, d_lco;
+        upload_vec(d_cl, chunk_lane);
+        upload_vec(d_cf, chunk_first);
+        upload_vec(d_lco, lane_chunk_off);
+        ChunkTable ct{d_cl.p, d_cf.p, d_lco.p, chunk_lane.size()};
+        if (ct.n_chunks) {
+            pack_plain_kernel<<<chunk_grid(ct.n_chunks), kChunkBlocks>>>(m->slots.p, m->group_hot.p, m->group_nblocks.p,
+                                                                         ct, d_plain.p, d_off.p);
+            CUDA_CHECK(cudaGetLastError());
+        }
+        CUDA_CHECK(cudaDeviceSynchronize());
+    }
+    for (FlatNode &n : t.nodes) { n.bits.w.clear(); n.bits.w.shrink_to_fit(); }
+    m->finalize_arena(t, true);
+    m->refresh_img();
+    m->derive_stats();
+    return m.release();
+}
+
+// ------------------------------------------------------------------------------------------
+// Workspaces
+// ------------------------------------------------------------------------------------------
+Workspace::Workspace(const Matrix *m_) : m(m_) {
+    CUDA_CHECK(cudaSetDevice(m->device));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    d_ctrl.alloc(8);
+    d_err.alloc(1);
+    CUDA_CHECK(cudaMallocHost(&h_ctrl, 8 * sizeof(u64)));
+    if (m->kind == Matrix::BRWT && m->cap_spill)
+        d_spill.alloc(size_t(m->rows_grid) * kRowsWarps * m->cap_spill);
+}
+
+Workspace::~Workspace() {
+    cudaSetDevice(m->device);
+    if (stream) cudaStreamDestroy(stream);
+    if (h_ctrl) cudaFreeHost(h_ctrl);
+    if (h_stage) cudaFreeHost(h_stage);
+}
+
+void Workspace::reserve_rows(u64 n) {
+    if (n + 1 <= cap_rows) return;
+    u64 c = std::max<u64>(n + 1, cap_rows * 2);
+    d_rows.alloc(c);
+    d_row_tmp_off.alloc(c);
+    d_row_cnt.alloc(c);
+    d_offsets.alloc(c);
+    d_bytes8.alloc(c);
+    size_t need = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, need, d_row_cnt.p, d_offsets.p, c, stream);
+    d_cub.alloc(need + 16);
+    cub_bytes = need;
+    cap_rows = c;
+}
+
+void Workspace::stage_reserve(size_t bytes) {
+    if (bytes <= h_stage_bytes) return;
+    if (h_stage) cudaFreeHost(h_stage);
+    h_stage = nullptr;
+    size_t nb = std::max(bytes, h_stage_bytes * 2);
+    CUDA_CHECK(cudaMallocHost(&h_stage, nb));
+    h_stage_bytes = nb;
+}
+
+Workspace *Matrix::acquire() const {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    if (!pool.empty()) {
+        Workspace *w = pool.back();
+        pool.pop_back();
+        return w;
+    }
+    return new Workspace(this);
+}
+void Matrix::release(Workspace *w) const {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    pool.push_back(w);
+}
+Matrix::~Matrix() {
+    for (Workspace *w : pool) delete w;
+}
+
+// ------------------------------------------------------------------------------------------
+// get_rows on the device: rows already in ws.d_rows or caller memory
+// ------------------------------------------------------------------------------------------
+static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
+    ws->reserve_rows(n);
+    cudaStream_t st = ws->stream;
+    if (n == 0) {
+        CUDA_CHECK(cudaMemsetAsync(ws->d_offsets.p, 0, 8, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        *total_out = 0;
+        ws->launches = 0;
+        return;
+    }
+    if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+        CUDA_CHECK(cudaMemsetAsync(ws->d_err.p, 0, sizeof(int), st));
+        RowsArgs a;
+        a.rows = d_rows; a.n = n;
+        a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
+        a.cursor = ws->d_ctrl.p;
+        a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
+        a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
+        a.bm_words = m->bm_words; a.rb = m->rb; a.err = ws->d_err.p;
+        u64 batches = (n + m->rb - 1) / m->rb;
+        u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+        brwt_rows_kernel<<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
+        CUDA_CHECK(cudaGetLastError());
+        size_t cb = ws->cub_bytes;
+        // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
+        CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
+        cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 3 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 4, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) throw std::runtime_error("descent stack overflow (engine bug)");
+        u64 total = ws->h_ctrl[0];
+        ws->last_probes = ws->h_ctrl[2];
+        ws->launches = 3;  // descent + 2 scan kernels
+        if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo (steady state never does)
+            ws->d_tmp.alloc(total + total / 8 + 1024);
+            continue;
+        }
+        *total_out = total;
+        size_t out_bytes = size_t(total) * col_bytes;
+        if (ws->d_out.n < out_bytes) ws->d_out.alloc(out_bytes + out_bytes / 8 + 1024);
+        if (total) {
+            u64 warps = batches;
+            u32 g = u32((warps * 32 + 255) / 256);
+            if (col_bytes == 8)
+                gather_rows_kernel<u64><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n, m->rb,
+                                                          reinterpret_cast<u64 *>(ws->d_out.p));
+            else
+                gather_rows_kernel<u32><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n, m->rb,
+                                                          reinterpret_cast<u32 *>(ws->d_out.p));
+            CUDA_CHECK(cudaGetLastError());
+            ws->launches += 1;
+        }
+        return;
+    }
+    throw std::runtime_error("chunk arena did not converge");
+}
+
+void rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
+    CUDA_CHECK(cudaSetDevice(m->device));
+    if (m->kind == Matrix::BRWT) brwt_rows_device(m, ws, d_rows, n, col_bytes, total_out);
+    else colmajor_rows_device(m, ws, d_rows, n, col_bytes, total_out);
+    m->last_probes = ws->last_probes;
+}
+
+struct RowsResult {
+    const Matrix *m;
+    Workspace *ws;   // owns the pinned staging the pointers below refer to
+    u64 n, total;
+    const u64 *offsets, *cols;
+};
+
+}  // namespace ggq
+
+// ==========================================================================================
+// C ABI
+// ==========================================================================================
+using namespace ggq;
+
+struct ggq_matrix : ggq::Matrix {};
+struct ggq_workspace : ggq::Workspace { using ggq::Workspace::Workspace; };
+struct ggq_rows_result : ggq::RowsResult {};
+
+#define GGQ_TRY try {
+#define GGQ_CATCH                                                                   \
+    } catch (const ggq::ParseError &e) { return fail(GGQ_ERR_FORMAT, e.what());     \
+    } catch (const ggq::LimitError &e) { return fail(GGQ_ERR_LIMIT, e.what());      \
+    } catch (const ggq::CudaError &e) { return fail(GGQ_ERR_CUDA, e.what());        \
+    } catch (const std::bad_alloc &) { return fail(GGQ_ERR_OOM, "out of memory");   \
+    } catch (const std::exception &e) { return fail(GGQ_ERR_INTERNAL, e.what()); }
+
+extern "C" {
+
+const char *ggq_last_error(void) { return g_last_error.c_str(); }
+
+int ggq_device_count(int *count) {
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) { *count = 0; return fail(GGQ_ERR_CUDA, cudaGetErrorString(e)); }
+    *count = c;
+    return GGQ_OK;
+}
+
+static int brwt_load_reader(Reader &in, int device, ggq_matrix **out) {
+    GGQ_TRY
+    if (!out) return fail(GGQ_ERR_ARG, "null out");
+    ParsedNode root;
+    load_brwt_node(in, &root);
+    FlatTree t;
+    flatten_parsed(std::move(root), &t);
+    *out = static_cast<ggq_matrix *>(upload_brwt(std::move(t), device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_brwt_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out) {
+    if (!read) return fail(GGQ_ERR_ARG, "null reader");
+    Reader in(read, ctx);
+    return brwt_load_reader(in, device, out);
+}
+
+int ggq_brwt_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_matrix **out) {
+    if (!buf && len) return fail(GGQ_ERR_ARG, "null buffer");
+    Reader in(buf, len);
+    int rc = brwt_load_reader(in, device, out);
+    if (consumed) *consumed = in.consumed();
+    return rc;
+}
+
+int ggq_colmajor_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out) {
+    if (!read) return fail(GGQ_ERR_ARG, "null reader");
+    GGQ_TRY
+    Reader in(read, ctx);
+    *out = static_cast<ggq_matrix *>(colmajor_load(in, device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_colmajor_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_matrix **out) {
+    if (!buf && len) return fail(GGQ_ERR_ARG, "null buffer");
+    GGQ_TRY
+    Reader in(buf, len);
+    *out = static_cast<ggq_matrix *>(colmajor_load(in, device));
+    if (consumed) *consumed = in.consumed();
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_brwt_synthesize(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed, uint32_t arity,
+                        int device, ggq_matrix **out) {
+    GGQ_TRY
+    if (!out || arity < 2) return fail(GGQ_ERR_ARG, "bad argument");
+    if (n_cols >= (1ull << 31)) return fail(GGQ_ERR_LIMIT, "too many columns");
+    *out = static_cast<ggq_matrix *>(synthesize_brwt(n_rows, u32(n_cols), threshold, seed, arity, device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+void ggq_free(ggq_matrix *m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    delete static_cast<ggq::Matrix *>(m);
+}
+
+uint64_t ggq_num_rows(const ggq_matrix *m) { return m->tree.n_rows; }
+uint64_t ggq_num_columns(const ggq_matrix *m) { return m->tree.n_cols; }
+uint64_t ggq_num_relations(const ggq_matrix *m) { return m->num_relations; }
+uint64_t ggq_num_nodes(const ggq_matrix *m) { return m->n_nodes; }
+uint64_t ggq_total_column_size(const ggq_matrix *m) { return m->total_column_size; }
+uint64_t ggq_device_bytes(const ggq_matrix *m) { return m->device_bytes; }
+uint64_t ggq_last_probe_count(const ggq_matrix *m) { return m->last_probes; }
+
+int ggq_workspace_create(const ggq_matrix *m, ggq_workspace **out) {
+    GGQ_TRY
+    *out = new ggq_workspace(m);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+void ggq_workspace_free(ggq_workspace *ws) { delete ws; }
+void *ggq_workspace_stream(ggq_workspace *ws) { return ws->stream; }
+
+int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n, int col_bytes,
+                        const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols) {
+    GGQ_TRY
+    if (!m || !ws || (!d_rows && n) || (col_bytes != 4 && col_bytes != 8)) return fail(GGQ_ERR_ARG, "bad argument");
+    u64 total = 0;
+    rows_device(m, ws, reinterpret_cast<const u64 *>(d_rows), n, col_bytes, &total);
+    if (d_offsets) *d_offsets = reinterpret_cast<const uint64_t *>(ws->d_offsets.p);
+    if (d_cols) *d_cols = ws->d_out.p;
+    if (n_cols) *n_cols = total;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+// host rows -> device query -> host CSR in the workspace's pinned staging buffer
+static void rows_host(const ggq_matrix *m, Workspace *ws, const uint64_t *rows, u64 n, u64 *total) {
+    CUDA_CHECK(cudaSetDevice(m->device));
+    ws->reserve_rows(n);
+    if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
+    rows_device(m, ws, ws->d_rows.p, n, 8, total);
+}
+
+int ggq_get_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ggq_rows_result **out) {
+    GGQ_TRY
+    if (!m || !out || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    Workspace *ws = m->acquire();
+    try {
+        u64 total = 0;
+        rows_host(m, ws, rows, n, &total);
+        size_t off_bytes = (n + 1) * 8, col_bytes = total * 8;
+        ws->stage_reserve(off_bytes + col_bytes + 8);
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_stage, ws->d_offsets.p, off_bytes, cudaMemcpyDeviceToHost, ws->stream));
+        if (total)
+            CUDA_CHECK(cudaMemcpyAsync(ws->h_stage + off_bytes, ws->d_out.p, col_bytes, cudaMemcpyDeviceToHost, ws->stream));
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        ggq_rows_result *r = new ggq_rows_result();
+        r->m = m; r->ws = ws; r->n = n; r->total = total;
+        r->offsets = reinterpret_cast<const u64 *>(ws->h_stage);
+        r->cols = reinterpret_cast<const u64 *>(ws->h_stage + off_bytes);
+        *out = r;
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+const uint64_t *ggq_rows_offsets(const ggq_rows_result *r) { return reinterpret_cast<const uint64_t *>(r->offsets); }
+const uint64_t *ggq_rows_columns(const ggq_rows_result *r) { return reinterpret_cast<const uint64_t *>(r->cols); }
+uint64_t ggq_rows_count(const ggq_rows_result *r) { return r->n; }
+void ggq_rows_result_free(ggq_rows_result *r) {
+    if (!r) return;
+    r->m->release(r->ws);
+    delete r;
+}
+
+int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint64_t *cols,
+                      uint64_t cols_capacity, uint64_t *n_cols) {
+    GGQ_TRY
+    if (!m || !offsets || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    Workspace *ws = m->acquire();
+    int rc = GGQ_OK;
+    try {
+        u64 total = 0;
+        rows_host(m, ws, rows, n, &total);
+        if (n_cols) *n_cols = total;
+        CUDA_CHECK(cudaMemcpyAsync(offsets, ws->d_offsets.p, (n + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
+        if (total > cols_capacity || (total && !cols)) {
+            rc = fail(GGQ_ERR_ARG, "cols_capacity too small");
+        } else if (total) {
+            CUDA_CHECK(cudaMemcpyAsync(cols, ws->d_out.p, total * 8, cudaMemcpyDeviceToHost, ws->stream));
+        }
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return rc;
+    GGQ_CATCH
+}
+
+int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len) {
+    GGQ_TRY
+    if (!m || !out || !out_len || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    Workspace *ws = m->acquire();
+    try {
+        CUDA_CHECK(cudaSetDevice(m->device));
+        ws->reserve_rows(n);
+        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
+        u64 total = 0;
+        rows_device(m, ws, ws->d_rows.p, n, 4, &total);
+        u64 len = total + n;
+        DeviceBuf<u64> d_slice;
+        d_slice.alloc(std::max<u64>(len, 1));
+        if (n) {
+            slice_rows_kernel<<<u32((n + 255) / 256), 256, 0, ws->stream>>>(
+                ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p), n, d_slice.p);
+            CUDA_CHECK(cudaGetLastError());
+        }
+        uint64_t *h = static_cast<uint64_t *>(std::malloc(std::max<u64>(len, 1) * 8));
+        if (!h) throw std::bad_alloc();
+        if (len) CUDA_CHECK(cudaMemcpyAsync(h, d_slice.p, len * 8, cudaMemcpyDeviceToHost, ws->stream));
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        *out = h;
+        *out_len = len;
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+void ggq_buffer_free(void *p) { std::free(p); }
+
+static int get_cells(const ggq_matrix *m, const uint64_t *rows, const uint64_t *cols, u64 fixed_col, u64 n, uint8_t *out) {
+    GGQ_TRY
+    if (!m || (!rows && n) || (!out && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (!n) return GGQ_OK;
+    Workspace *ws = m->acquire();
+    try {
+        CUDA_CHECK(cudaSetDevice(m->device));
+        ws->reserve_rows(n);
+        cudaStream_t st = ws->stream;
+        CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+        const u64 *d_cols = nullptr;
+        if (cols) {
+            CUDA_CHECK(cudaMemcpyAsync(ws->d_row_tmp_off.p, cols, n * 8, cudaMemcpyHostToDevice, st));
+            d_cols = ws->d_row_tmp_off.p;
+        }
+        unsigned char *d_res = reinterpret_cast<unsigned char *>(ws->d_bytes8.p);
+        if (m->kind == Matrix::BRWT)
+            brwt_get_kernel<<<u32((n + 255) / 256), 256, 0, st>>>(m->img, ws->d_rows.p, d_cols, fixed_col, n, d_res);
+        else
+            colmajor_get_launch(m, ws->d_rows.p, d_cols, fixed_col, n, d_res, st);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemcpyAsync(out, d_res, n, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_get(const ggq_matrix *m, const uint64_t *rows, const uint64_t *cols, uint64_t n, uint8_t *out) {
+    if (!cols && n) return fail(GGQ_ERR_ARG, "null cols");
+    return get_cells(m, rows, cols, 0, n, out);
+}
+
+int ggq_has_column(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t col, uint8_t *out) {
+    if (m && col >= m->tree.n_cols && m->kind == Matrix::BRWT) return fail(GGQ_ERR_ARG, "column out of range");
+    return get_cells(m, rows, nullptr, col, n, out);
+}
+
+int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t *n_rows) {
+    GGQ_TRY
+    if (!m || !rows || !n_rows) return fail(GGQ_ERR_ARG, "bad argument");
+    if (col >= ggq_num_columns(m)) return fail(GGQ_ERR_ARG, "column out of range");
+    Workspace *ws = m->acquire();
+    try {
+        CUDA_CHECK(cudaSetDevice(m->device));
+        cudaStream_t st = ws->stream;
+        u64 cnt = 0;
+        DeviceBuf<u64> d_res;
+        if (m->kind == Matrix::BRWT) {
+            const FlatTree &t = m->tree;
+            u32 p0 = t.col_path_off[col], p1 = t.col_path_off[col + 1];
+            u32 leaf_li = t.col_path[p1 - 1];
+            cnt = t.nodes[t.lane_node[leaf_li]].ones;
+            // an empty ancestor makes the column empty (BRWT.cpp:58-62); an empty leaf too
+            d_res.alloc(std::max<u64>(cnt, 1));
+            if (cnt) {
+                u64 nb = t.group_nblocks[leaf_li >> 2];
+                lane_enumerate_kernel<<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res.p);
+                for (u32 p = p1 - 1; p-- > p0;) {
+                    u32 li = t.col_path[p];
+                    const FlatNode &a = t.nodes[t.lane_node[li]];
+                    if (a.ones == a.size) continue;  // all ones: identity (BRWT.cpp:77-78)
+                    lane_select_kernel<<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res.p, cnt);
+                }
+                CUDA_CHECK(cudaGetLastError());
+            }
+        } else {
+            colmajor_get_column(m, ws, col, &d_res, &cnt);
+        }
+        uint64_t *h = static_cast<uint64_t *>(std::malloc(std::max<u64>(cnt, 1) * 8));
+        if (!h) throw std::bad_alloc();
+        if (cnt) CUDA_CHECK(cudaMemcpyAsync(h, d_res.p, cnt * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        *rows = h;
+        *n_rows = cnt;
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+}  // extern "C"
+
+#include "ggq_bv_capi.inl"

@@ -1,0 +1,115 @@
+// Host-side objects behind the opaque C handles.
+#pragma once
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "ggq_device.cuh"
+#include "ggq_tree.hpp"
+
+namespace ggq {
+
+struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
+struct LimitError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+int fail(int code, const std::string &msg);
+
+#define CUDA_CHECK(expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            if (_e == cudaErrorMemoryAllocation) { cudaGetLastError(); throw std::bad_alloc(); }  \
+            throw ggq::CudaError(std::string(#expr) + ": " + cudaGetErrorString(_e));             \
+        }                                                                                         \
+    } while (0)
+
+template <typename T>
+struct DeviceBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    DeviceBuf() = default;
+    DeviceBuf(const DeviceBuf &) = delete;
+    DeviceBuf &operator=(const DeviceBuf &) = delete;
+    DeviceBuf(DeviceBuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DeviceBuf &operator=(DeviceBuf &&o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~DeviceBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void alloc(size_t count) {
+        release();
+        if (!count) count = 1;
+        CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&p), count * sizeof(T)));
+        n = count;
+    }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+struct Workspace;
+struct ColMajorImage;
+
+struct Matrix {
+    enum Kind { BRWT = 0, COLMAJOR = 1 } kind = BRWT;
+    int device = 0;
+    int sm_count = 148;
+    FlatTree tree;   // host copy of the structure (bits dropped after upload)
+
+    // device image
+    DeviceBuf<uint4> slots;
+    DeviceBuf<u64> group_hot, group_nblocks, lane_sel_off, lane_ones, sb_base;
+    DeviceBuf<u32> lane_info, lane_aux, lane_sb_off, sel, leaf_col, col_path_off, col_path;
+    Img img{};
+
+    // stats
+    u64 n_nodes = 0, total_column_size = 0, num_relations = 0, device_bytes = 0;
+    mutable u64 last_probes = 0;
+
+    // descent kernel configuration
+    u32 bm_words = 1, rb = 8, cap_s = 64, cap_spill = 0, rows_grid = 148;
+    size_t rows_smem = 0;
+
+    ColMajorImage *cm = nullptr;  // column-major matrices
+
+    mutable std::mutex pool_mu;
+    mutable std::vector<Workspace *> pool;
+
+    Matrix() = default;
+    ~Matrix();
+    void upload_tables(const FlatTree &t);
+    void finalize_arena(const FlatTree &t, bool ones_known);
+    void refresh_img();
+    void derive_stats();
+    Workspace *acquire() const;
+    void release(Workspace *w) const;
+};
+
+// Per-caller scratch: one stream, device buffers that grow to the high-water mark, pinned staging.
+struct Workspace {
+    const Matrix *m;
+    cudaStream_t stream = nullptr;
+    DeviceBuf<u64> d_rows, d_row_tmp_off, d_offsets, d_bytes8, d_ctrl, d_spill;
+    DeviceBuf<u32> d_row_cnt, d_tmp;
+    DeviceBuf<int> d_err;
+    DeviceBuf<unsigned char> d_out, d_cub;
+    size_t cub_bytes = 0;
+    u64 cap_rows = 0;
+    u64 *h_ctrl = nullptr;
+    unsigned char *h_stage = nullptr;
+    size_t h_stage_bytes = 0;
+    u64 last_probes = 0;
+    int launches = 0;
+
+    explicit Workspace(const Matrix *m_);
+    ~Workspace();
+    void reserve_rows(u64 n);
+    void stage_reserve(size_t bytes);
+};
+
+void build_chunk_table(const FlatTree &t, std::vector<u32> *chunk_lane, std::vector<u32> *chunk_first,
+                       std::vector<u32> *lane_chunk_off);
+
+}  // namespace ggq

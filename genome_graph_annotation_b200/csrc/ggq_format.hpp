@@ -1,0 +1,362 @@
+// Host-side readers for the reference's on-disk formats (no sdsl / libmaus2 dependency).
+//
+// What is parsed, and where the reference writes it:
+//   * u64 big-endian numbers            libmaus2 NumberSerialisation (common/serialization.cpp:27-36)
+//   * sdsl::int_vector<> / bit_vector   sdsl/int_vector.hpp:593-609,1565-1598 (LE u64 bit size, [u8 width], LE words)
+//   * utils::RangePartition             common/utils.cpp:702-725
+//   * sdsl::rrr_vector<63>              sdsl/rrr_vector.hpp:350-373 (m_size, bt, btnr, btnrp, rank, invert)
+//   * sdsl::sd_vector<> + inverted byte sdsl/sd_vector.hpp:404-432, common/bit_vector.cpp:725-756
+//   * bit_vector_stat                   common/bit_vector.cpp:346-385
+//   * BRWT node, pre-order              annotation/hierarchical_annotation/BRWT.cpp:87-128
+//   * ColMajorCompressed                annotation/column_compressed/column_major.cpp:58-88
+//
+// Everything is decoded to PLAIN bits here; the device layout is built from those
+// (ggq_engine.cu).  Errors are reported by throwing ParseError; the C ABI maps it to
+// GGQ_ERR_FORMAT, and the BinaryMatrix adapter maps that to load() == false.
+#pragma once
+
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace ggq {
+
+struct ParseError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+// Pull-style byte source: memory buffer or a caller-provided callback (std::istream in the adapter).
+class Reader {
+  public:
+    typedef size_t (*read_fn)(void *ctx, void *dst, size_t n);
+
+    Reader(const uint8_t *buf, size_t len) : buf_(buf), len_(len) {}
+    Reader(read_fn fn, void *ctx) : fn_(fn), ctx_(ctx) {}
+
+    void read(void *dst, size_t n) {
+        if (!n) return;
+        if (fn_) {
+            if (fn_(ctx_, dst, n) != n) throw ParseError("unexpected end of stream");
+        } else {
+            if (n > len_ - pos_) throw ParseError("unexpected end of buffer");
+            std::memcpy(dst, buf_ + pos_, n);
+        }
+        pos_ += n;
+    }
+    // bytes still available if known (memory source), otherwise "unknown" = huge
+    uint64_t remaining() const { return fn_ ? ~uint64_t(0) : len_ - pos_; }
+    uint64_t consumed() const { return pos_; }
+
+    uint8_t u8() { uint8_t v; read(&v, 1); return v; }
+    uint64_t u64le() { uint64_t v; read(&v, 8); return v; }  // host is little-endian (x86-64)
+    uint64_t u64be() {
+        uint8_t b[8];
+        read(b, 8);
+        uint64_t v = 0;
+        for (int i = 0; i < 8; ++i) v = (v << 8) | b[i];
+        return v;
+    }
+
+  private:
+    const uint8_t *buf_ = nullptr;
+    size_t len_ = 0, pos_ = 0;
+    read_fn fn_ = nullptr;
+    void *ctx_ = nullptr;
+};
+
+// sdsl::int_vector<0> (has_width = true) or int_vector<t_width> with fixed width (bit_vector: 1, <64>: 64).
+struct IntVector {
+    uint64_t bit_size = 0;
+    uint8_t width = 1;
+    std::vector<uint64_t> words;
+
+    uint64_t size() const { return width ? bit_size / width : 0; }
+
+    // value of element i (width <= 64); same bit addressing as sdsl::bits::read_int
+    uint64_t get(uint64_t i) const { return get_bits(i * width, width); }
+
+    uint64_t get_bits(uint64_t bit_pos, unsigned len) const {
+        if (!len) return 0;
+        uint64_t w = bit_pos >> 6;
+        unsigned off = bit_pos & 63;
+        uint64_t v = words[w] >> off;
+        if (off + len > 64) v |= words[w + 1] << (64 - off);
+        return len == 64 ? v : v & ((uint64_t(1) << len) - 1);
+    }
+    bool bit(uint64_t i) const { return (words[i >> 6] >> (i & 63)) & 1; }
+
+    void load(Reader &in, bool has_width, uint8_t fixed_width = 1) {
+        bit_size = in.u64le();
+        width = has_width ? in.u8() : fixed_width;
+        uint64_t n_words = (bit_size + 63) >> 6;
+        if (n_words < (bit_size >> 6)) throw ParseError("int_vector size overflow");
+        if (n_words > in.remaining() / 8 && in.remaining() != ~uint64_t(0))
+            throw ParseError("int_vector larger than the stream");
+        if (n_words > (uint64_t(1) << 40)) throw ParseError("int_vector implausibly large");
+        words.assign(n_words + 1, 0);  // +1 pad word so that get_bits may peek one word ahead
+        in.read(words.data(), n_words * 8);
+        if (has_width && bit_size && (width == 0 || width > 64)) throw ParseError("bad int_vector width");
+    }
+};
+
+// Plain bits of one vector, as u32 words (bit i -> word i/32, bit i%32), zero padded.
+struct PlainBits {
+    uint64_t size = 0;  // in bits
+    uint64_t ones = 0;
+    std::vector<uint32_t> w;
+
+    void resize(uint64_t n_bits) {
+        size = n_bits;
+        w.assign((n_bits + 31) / 32 + 4, 0);
+    }
+    void set(uint64_t i) { w[i >> 5] |= uint32_t(1) << (i & 31); }
+    bool get(uint64_t i) const { return (w[i >> 5] >> (i & 31)) & 1; }
+    // OR `len` (<= 64) bits of v at bit position pos
+    void or_bits(uint64_t pos, uint64_t v, unsigned len) {
+        if (!len) return;
+        if (len < 64) v &= (uint64_t(1) << len) - 1;
+        uint64_t wi = pos >> 5;
+        unsigned off = pos & 31;
+        w[wi] |= uint32_t(v << off);
+        v >>= (32 - off);
+        w[wi + 1] |= uint32_t(v);
+        if (off + len > 64) w[wi + 2] |= uint32_t(v >> 32);
+    }
+    void count() {
+        ones = 0;
+        for (uint32_t x : w) ones += __builtin_popcount(x);
+    }
+};
+
+// ---------------------------------------------------------------------------------------
+// rrr_vector<63, int_vector<>, 32>
+// ---------------------------------------------------------------------------------------
+struct Binomial63 {
+    uint64_t c[64][64];   // c[n][k], n,k <= 63
+    uint8_t space[64];    // bits used to store the block number of a block with k ones (sdsl rrr_helper.hpp:267-272)
+    Binomial63() {
+        for (int n = 0; n < 64; ++n)
+            for (int k = 0; k < 64; ++k)
+                c[n][k] = (k == 0) ? 1 : 0;
+        for (int n = 1; n < 64; ++n)
+            for (int k = 1; k <= n; ++k)
+                c[n][k] = c[n - 1][k - 1] + c[n - 1][k];
+        for (int k = 0; k < 64; ++k) {
+            uint64_t b = c[63][k];
+            space[k] = (b == 1) ? 0 : uint8_t(64 - __builtin_clzll(b));
+        }
+    }
+    static const Binomial63 &get() {
+        static const Binomial63 t;
+        return t;
+    }
+    // Inverse of sdsl's bin_to_nr (rrr_helper.hpp:295-312): bit i of the block is set iff
+    // nr >= C(62 - i, k) at the moment i is visited.
+    uint64_t decode(unsigned k, uint64_t nr) const {
+        if (k == 0) return 0;
+        if (k == 63) return (uint64_t(1) << 63) - 1;
+        uint64_t bits = 0;
+        unsigned nn = 63;
+        unsigned i = 0;
+        while (k > 1) {
+            if (nn == 0) throw ParseError("corrupt rrr block");
+            if (nr >= c[nn - 1][k]) {
+                nr -= c[nn - 1][k];
+                --k;
+                bits |= uint64_t(1) << i;
+            }
+            --nn;
+            ++i;
+        }
+        if (nr > 62) throw ParseError("corrupt rrr block");
+        uint64_t last = 62 - nr;  // position of the final one: n - nr - 1
+        bits |= uint64_t(1) << last;
+        return bits;
+    }
+};
+
+inline void load_rrr63(Reader &in, PlainBits *out) {
+    const unsigned BS = 63, K = 32;
+    uint64_t m_size = in.u64le();
+    IntVector bt, btnr, btnrp, rank, invert;
+    bt.load(in, true);
+    btnr.load(in, false, 1);
+    btnrp.load(in, true);
+    rank.load(in, true);
+    invert.load(in, false, 1);
+    if (m_size == 0 && bt.bit_size == 0) {  // default-constructed rrr_vector (empty matrix)
+        out->resize(0);
+        return;
+    }
+    uint64_t n_blocks = (m_size + BS) / BS;  // includes the trailing dummy/partial block
+    if (bt.width < 6 || bt.size() != n_blocks) throw ParseError("rrr: bad block-type array");
+    uint64_t n_sb = (n_blocks + K - 1) / K;
+    if (invert.bit_size < n_sb || btnrp.size() < n_sb) throw ParseError("rrr: bad superblock arrays");
+    const Binomial63 &B = Binomial63::get();
+    out->resize(m_size);
+    uint64_t pos = 0;
+    for (uint64_t b = 0; b < n_blocks; ++b) {
+        if (b % K == 0) {
+            pos = btnrp.get(b / K);
+        }
+        unsigned stored = unsigned(bt.get(b));
+        if (stored > BS) throw ParseError("rrr: block type out of range");
+        unsigned sp = B.space[stored];  // space[k] == space[63-k]
+        unsigned k = invert.bit(b / K) ? BS - stored : stored;
+        uint64_t start = b * BS;
+        unsigned len = unsigned(std::min<uint64_t>(BS, m_size - std::min(m_size, start)));
+        if (sp) {
+            if (pos + sp > btnr.bit_size) throw ParseError("rrr: btnr overrun");
+            uint64_t nr = btnr.get_bits(pos, sp);
+            uint64_t bits = B.decode(k, nr);
+            if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");
+            out->or_bits(start, bits, len);
+        } else if (k == BS) {
+            if (len < BS) throw ParseError("rrr: bits beyond the end");
+            out->or_bits(start, ~uint64_t(0), len);
+        }
+        pos += sp;
+    }
+    out->count();
+}
+
+// ---------------------------------------------------------------------------------------
+// sd_vector<> followed by the reference's `inverted` byte  (bit_vector_sd)
+// ---------------------------------------------------------------------------------------
+inline void skip_select_mcl(Reader &in) {
+    uint64_t arg_cnt = in.u64le();
+    if (!arg_cnt) return;
+    uint64_t sb = (arg_cnt + 4095) >> 12;
+    IntVector tmp;
+    tmp.load(in, true);  // superblock
+    IntVector mini_or_long;
+    mini_or_long.load(in, false, 1);
+    if (mini_or_long.bit_size && mini_or_long.bit_size < sb) throw ParseError("select_mcl: bad indicator");
+    for (uint64_t i = 0; i < sb; ++i)
+        tmp.load(in, true);  // long superblock or miniblock — both int_vector<0>
+}
+
+struct SdColumn {
+    uint64_t size = 0;
+    bool inverted = false;            // stored vector is the complement (common/bit_vector.cpp:572-590)
+    std::vector<uint64_t> positions;  // ascending positions of the ones of the STORED vector
+};
+
+inline void load_sd(Reader &in, SdColumn *out) {
+    out->size = in.u64le();
+    uint8_t wl = in.u8();
+    IntVector low, high;
+    low.load(in, true);
+    high.load(in, false, 1);
+    skip_select_mcl(in);  // select_support_mcl<1>
+    skip_select_mcl(in);  // select_support_mcl<0>
+    // the trailing byte distinguishes bit_vector_sd from a bare sd_vector (tests/test_bit_vector.cpp:432-461)
+    uint8_t inv = in.u8();
+    if (inv > 1) throw ParseError("bit_vector_sd: bad inverted flag");
+    out->inverted = inv;
+    uint64_t m = low.size();
+    if (low.bit_size && low.width != wl) throw ParseError("sd: low width mismatch");
+    if (wl >= 64) throw ParseError("sd: bad wl");
+    out->positions.clear();
+    out->positions.reserve(m);
+    uint64_t i = 0;
+    for (uint64_t hp = 0; hp < high.bit_size && i < m; ++hp) {
+        if (high.bit(hp)) {
+            uint64_t hv = hp - i;
+            uint64_t p = (hv << wl) | (wl ? low.get(i) : 0);
+            if (p >= out->size || (i && p <= out->positions.back())) throw ParseError("sd: positions not ascending");
+            out->positions.push_back(p);
+            ++i;
+        }
+    }
+    if (i != m) throw ParseError("sd: high/low mismatch");
+}
+
+// logical bits of a bit_vector_sd
+inline void sd_to_plain(const SdColumn &c, PlainBits *out) {
+    out->resize(c.size);
+    if (c.inverted) {
+        for (uint64_t i = 0; i < c.size; ++i) out->set(i);
+        for (uint64_t p : c.positions) out->w[p >> 5] &= ~(uint32_t(1) << (p & 31));
+    } else {
+        for (uint64_t p : c.positions) out->set(p);
+    }
+    out->count();
+}
+
+// bit_vector_stat: plain sdsl::bit_vector + BE popcount + rank_support_v5 + select_support_mcl
+// (the supports may be missing: common/bit_vector.cpp:367-380 — tolerated the same way).
+inline void load_stat(Reader &in, PlainBits *out) {
+    IntVector v;
+    v.load(in, false, 1);
+    out->resize(v.bit_size);
+    for (uint64_t i = 0; i < (v.bit_size + 63) / 64; ++i) {
+        out->w[2 * i] = uint32_t(v.words[i]);
+        out->w[2 * i + 1] = uint32_t(v.words[i] >> 32);
+    }
+    if (v.bit_size % 64) {  // clear padding
+        uint64_t last = v.bit_size / 64;
+        uint64_t mask = (uint64_t(1) << (v.bit_size % 64)) - 1;
+        uint64_t x = v.words[last] & mask;
+        out->w[2 * last] = uint32_t(x);
+        out->w[2 * last + 1] = uint32_t(x >> 32);
+    }
+    out->count();
+    try {
+        (void)in.u64be();  // num_set_bits
+        IntVector rk;
+        rk.load(in, false, 64);
+        skip_select_mcl(in);
+    } catch (const ParseError &) {
+        // supports absent: the reference rebuilds them; nothing to do here
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// BRWT stream
+// ---------------------------------------------------------------------------------------
+struct ParsedNode {
+    std::vector<std::vector<uint32_t>> partition;  // RangePartition::partition_
+    uint64_t n_cols = 0;
+    PlainBits bits;                                // nonzero_rows_
+    std::vector<ParsedNode> children;
+};
+
+inline void load_range_partition(Reader &in, ParsedNode *node) {
+    uint64_t n_groups = in.u64be();
+    if (n_groups > (uint64_t(1) << 32)) throw ParseError("RangePartition: too many groups");
+    node->partition.assign(n_groups, {});
+    uint64_t total = 0;
+    for (auto &g : node->partition) {
+        IntVector v;
+        v.load(in, true);
+        uint64_t k = v.size();
+        if (!k) throw ParseError("RangePartition: empty group");  // utils.cpp:655-659
+        g.resize(k);
+        for (uint64_t i = 0; i < k; ++i) g[i] = uint32_t(v.get(i));
+        total += k;
+    }
+    // initialize_groups_and_ranks (utils.cpp:651-680): must be a permutation of [0, total)
+    std::vector<uint8_t> seen(total, 0);
+    for (auto &g : node->partition)
+        for (uint32_t c : g) {
+            if (c >= total || seen[c]) throw ParseError("RangePartition: not a partition");
+            seen[c] = 1;
+        }
+    node->n_cols = total;
+}
+
+inline void load_brwt_node(Reader &in, ParsedNode *node, int depth = 0) {
+    if (depth > 4096) throw ParseError("BRWT: implausible depth");
+    load_range_partition(in, node);
+    load_rrr63(in, &node->bits);
+    uint64_t n_children = in.u64be();
+    if (n_children && n_children != node->partition.size())
+        throw ParseError("BRWT: children do not match the partition");  // BRWT.cpp:106-107
+    node->children.resize(n_children);
+    for (auto &c : node->children) load_brwt_node(in, &c, depth + 1);
+}
+
+}  // namespace ggq

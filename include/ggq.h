@@ -1,0 +1,150 @@
+/* ggq — C ABI of the B200-native annotation-matrix query engine (libggq.so).
+ *
+ * This is the drop-in boundary for the hot path of ratschlab/genome_graph_annotation:
+ * every entry point replaces the reference call cited beside it.  Plain pointers and sizes
+ * only; no C++ types, no exceptions cross this boundary.  All functions return GGQ_OK (0) or a
+ * negative ggq_status; ggq_last_error() gives the message for the calling thread.
+ *
+ * Host C++ adapters with the reference's own class interface (BinaryMatrix) are in
+ * include/ggq/gpu_matrix.hpp; INTEGRATION.md shows how a maintainer wires them in.
+ *
+ * The library needs a CUDA device (sm_100a).  There is NO CPU fallback: without a usable
+ * device every compute entry point fails with GGQ_ERR_CUDA.
+ */
+#ifndef GGQ_H_
+#define GGQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum ggq_status {
+    GGQ_OK = 0,
+    GGQ_ERR_FORMAT = -1,   /* stream is not a valid serialized matrix (reference load() == false) */
+    GGQ_ERR_CUDA = -2,     /* CUDA runtime failure, or no device */
+    GGQ_ERR_OOM = -3,      /* host or device allocation failed */
+    GGQ_ERR_ARG = -4,      /* invalid argument (null pointer, column out of range, ...) */
+    GGQ_ERR_LIMIT = -5,    /* matrix exceeds an engine limit (see DESIGN.md "Limits") */
+    GGQ_ERR_INTERNAL = -6
+} ggq_status;
+
+typedef struct ggq_matrix ggq_matrix;            /* GPU-resident BinaryMatrix (BRWT or column-major) */
+typedef struct ggq_bv ggq_bv;                    /* GPU-resident bit vector with rank/select */
+typedef struct ggq_workspace ggq_workspace;      /* per-caller stream + scratch (device-resident API) */
+typedef struct ggq_rows_result ggq_rows_result;  /* host-resident CSR result of ggq_get_rows */
+
+/* Pull reader used by the stream loaders: must copy exactly n bytes to dst and return n, or return
+ * fewer on EOF/error.  Lets BinaryMatrix::load(std::istream&) consume exactly the matrix' bytes. */
+typedef size_t (*ggq_read_fn)(void *ctx, void *dst, size_t n);
+
+const char *ggq_last_error(void);
+int ggq_device_count(int *count);
+
+/* ------------------------------------------------------------------ load / upload ------------ */
+
+/* BRWT::load (annotation/hierarchical_annotation/BRWT.cpp:87-111): parses the reference's
+ * serialized BRWT / Multi-BRWT stream (pre-order nodes: RangePartition, rrr_vector<63>, children),
+ * flattens it into level-order sibling-interleaved arrays and uploads it once to `device`. */
+int ggq_brwt_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out);
+int ggq_brwt_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_matrix **out);
+
+/* ColMajorCompressed::load (annotation/column_compressed/column_major.cpp:58-79): BE u64 column
+ * count + bit_vector_sd streams. */
+int ggq_colmajor_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out);
+int ggq_colmajor_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_matrix **out);
+
+/* Benchmark harness: builds ON THE DEVICE the BRWT that
+ * BRWTBottomUpBuilder::build(columns, get_basic_partitioner(arity)) (BRWT_builders.cpp:19-31,
+ * 122-163) would produce for the implicit matrix  M[i][j] = mix64(seed*0x9E3779B97F4A7C15 + i*n_cols + j) < threshold. */
+int ggq_brwt_synthesize(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed,
+                        uint32_t arity, int device, ggq_matrix **out);
+
+void ggq_free(ggq_matrix *m);
+
+/* BinaryMatrix::num_rows / num_columns / num_relations (common/binary_matrix.hpp:16-28) */
+uint64_t ggq_num_rows(const ggq_matrix *m);
+uint64_t ggq_num_columns(const ggq_matrix *m);
+uint64_t ggq_num_relations(const ggq_matrix *m);
+/* BRWT stats (BRWT.hpp:44-49); 0 for column-major */
+uint64_t ggq_num_nodes(const ggq_matrix *m);
+uint64_t ggq_total_column_size(const ggq_matrix *m);
+uint64_t ggq_device_bytes(const ggq_matrix *m);
+/* Algorithmic work of the last ggq_get_rows* call on this workspace/matrix: number of sibling-group
+ * probes (one 16/32/64-byte block read each).  For roofline accounting. */
+uint64_t ggq_last_probe_count(const ggq_matrix *m);
+
+/* ------------------------------------------------------------------ row queries -------------- */
+
+/* get_rows(R)[t] == BRWT::get_row(R[t]) (BRWT.cpp:26-53) / ColMajorCompressed::get_row
+ * (column_major.cpp:34-47): for every row id the set columns in the reference's order (DFS over
+ * children for BRWT, ascending for column-major).  Host buffers in, host CSR out.
+ * Row ids >= num_rows (undefined behaviour in the reference, assert only) yield empty rows. */
+int ggq_get_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ggq_rows_result **out);
+const uint64_t *ggq_rows_offsets(const ggq_rows_result *r);  /* n + 1 entries */
+const uint64_t *ggq_rows_columns(const ggq_rows_result *r);  /* offsets[n] entries */
+uint64_t ggq_rows_count(const ggq_rows_result *r);
+void ggq_rows_result_free(ggq_rows_result *r);
+
+/* Same query, caller-provided host output (cols_capacity entries).  *n_cols receives the number of
+ * column ids; if it exceeds cols_capacity nothing is written to cols and GGQ_ERR_ARG is returned. */
+int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
+                      uint64_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
+
+/* slice_rows: concatenation of get_row(R[t]) each followed by UINT64_MAX (SURVEY.md "Three facts" 1). */
+int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len);
+void ggq_buffer_free(void *p);
+
+/* Device-resident variant: d_rows is device memory on the matrix' device; the CSR stays on the
+ * device in buffers owned by the workspace (valid until the next call on that workspace).
+ * col_bytes = 4 or 8 selects u32 / u64 column ids.  Runs on the workspace's stream; synchronizes
+ * once to learn the result size. */
+int ggq_workspace_create(const ggq_matrix *m, ggq_workspace **out);
+void ggq_workspace_free(ggq_workspace *ws);
+void *ggq_workspace_stream(ggq_workspace *ws);  /* cudaStream_t */
+int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
+                        int col_bytes, const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols);
+
+/* ------------------------------------------------------------------ cells / columns ---------- */
+
+/* out[t] = BinaryMatrix::get(rows[t], cols[t]) (BRWT.cpp:9-24, column_major.cpp:27-32). */
+int ggq_get(const ggq_matrix *m, const uint64_t *rows, const uint64_t *cols, uint64_t n, uint8_t *out);
+/* has_column(R, j)[t] == get(R[t], j) */
+int ggq_has_column(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t col, uint8_t *out);
+/* BinaryMatrix::get_column (BRWT.cpp:55-85, column_major.cpp:49-56): ascending row ids.
+ * *rows is malloc'ed by the engine; release with ggq_buffer_free. */
+int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t *n_rows);
+
+/* ------------------------------------------------------------------ bit vectors -------------- */
+
+enum { GGQ_BV_STAT = 0, GGQ_BV_SD = 1, GGQ_BV_RRR = 2 };
+
+/* bit_vector_{stat,sd,rrr<63>}::load (common/bit_vector.cpp:360-385, 725-745, 906-925). */
+int ggq_bv_load_buffer(int kind, const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_bv **out);
+/* Same device layouts from plain bits (LSB-first u64 words), as the reference's constructors from
+ * sdsl::bit_vector do (common/bit_vector.cpp:253-262, 572-590, 806-812). */
+int ggq_bv_build(int kind, const uint64_t *words, uint64_t n_bits, int device, ggq_bv **out);
+/* Benchmark harness (config C3): bit i set iff mix64(seed*0x9E3779B97F4A7C15 + i) < threshold, generated on device. */
+int ggq_bv_synthesize(int kind, uint64_t n_bits, uint64_t threshold, uint64_t seed, int device, ggq_bv **out);
+void ggq_bv_free(ggq_bv *v);
+uint64_t ggq_bv_size(const ggq_bv *v);
+uint64_t ggq_bv_num_set_bits(const ggq_bv *v);
+int ggq_bv_is_inverted(const ggq_bv *v);  /* bit_vector_sd::is_inverted (bit_vector.hpp:171) */
+uint64_t ggq_bv_device_bytes(const ggq_bv *v);
+
+/* rank1: ones in [0, id], id >= size clamps (bit_vector.hpp:16-17, bit_vector.cpp:285,692,860).
+ * select1: position of the i-th one, i in [1, num_set_bits] (bit_vector.hpp:19-20).
+ * get: operator[].  Host arrays; `device` variants take device pointers and a cudaStream_t. */
+int ggq_bv_rank1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
+int ggq_bv_select1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
+int ggq_bv_get(const ggq_bv *v, const uint64_t *q, uint64_t n, uint8_t *out);
+int ggq_bv_rank1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
+int ggq_bv_select1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
+int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t *d_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGQ_H_ */
