@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""Headline benchmark (BASELINE.json: "Multi-BRWT get_rows rows/s at 1/2/4/8 B200").
+
+Workload (config 4 of BASELINE.json, SURVEY.md §8d "C4"): Kingsford-shaped synthetic matrix
+3.7e9 x 2652, density 0.3 %, defined implicitly by the portable generator
+M[i][j] = mix64(42*0x9E3779B97F4A7C15 + i*m + j) < floor(d*2^64); BRWT built on the device with the basic
+partitioner, arity 4 (shape-equivalent of Multi-BRWT, measured avg arity ~4); one step = one batch of
+2^24 uniformly random row ids per GPU answered by get_rows (CSR out).  Replicas, batch-sharded: every
+GPU holds the whole structure, no collective on the query path => "scaling": "weak".
+
+  python bench.py --gpus N --steps K --warmup W          # ours (libggq.so, CUDA)
+  python bench.py --impl reference ...                   # the reference's own BRWT::get_row on host cores
+
+`value`  : device-resident rows/s (row ids and CSR in HBM), CUDA events on the query stream, max over ranks.
+`e2e`    : same metric through the host-buffer C-ABI call ggq_get_rows_into (pinned host row ids in,
+           host CSR out; H2D and D2H inside the timed region).
+`roofline`: brwt_rows_kernel (the descent), algorithmic bytes per SURVEY.md §8(d) / its event-timed duration.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "multi_brwt_get_rows_rows_per_s"
+UNIT = "rows/s"
+SEED = 42
+L2_BYTES = 126e6
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=float, default=3.7e9, help="matrix rows (C4: 3.7e9)")
+    ap.add_argument("--cols", type=int, default=2652)
+    ap.add_argument("--density", type=float, default=0.003)
+    ap.add_argument("--arity", type=int, default=4)
+    ap.add_argument("--batch", type=int, default=1 << 24, help="row ids per GPU per step")
+    ap.add_argument("--cpu-rows", type=float, default=1e6, help="rows of the sub-shape the CPU reference is built on")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 50 ms DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is not None:
+            self.p.terminate()
+            try:
+                self.p.wait(timeout=5)
+            except Exception:
+                self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the reference's own BRWT::get_row (BRWT.cpp:26-53), unmodified, under
+# `omp parallel for` over row ids (oracle/ref_capi.cpp) on all host threads, on an n'-row sub-shape of
+# the same generator (the reference builder cannot make 3.7e9 rows: SURVEY.md §7b(d)).
+# --------------------------------------------------------------------------------------------
+def build_cpu_reference(args):
+    from oracle import ref_binding as R  # checker / baseline only
+    import genome_graph_annotation_b200 as g
+    if not R.available():
+        return None
+    n = int(args.cpu_rows)
+    thr = g.density_threshold(args.density)
+    threads = R.max_threads()
+    cw = R.gen_implicit(n, args.cols, thr, SEED)
+    rm = R.RefMatrix.build_brwt(cw, n, arity=args.arity, threads=threads)
+    del cw
+    return R, rm, n, threads
+
+
+def cpu_sample_rate(rm, n, threads, seconds):
+    """rows/s of omp-parallel reference get_row on a bounded random sample sized for ~`seconds`."""
+    rng = np.random.default_rng(SEED)
+    probe = rng.integers(0, n, 1 << 14).astype(np.uint64)
+    s, _ = rm.time_get_rows(probe, threads)
+    rate = probe.size / max(s, 1e-9)
+    cnt = int(min(1 << 22, max(1 << 14, rate * seconds)))
+    rows = rng.integers(0, n, cnt).astype(np.uint64)
+    s, _ = rm.time_get_rows(rows, threads)
+    return cnt / s, cnt, s
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    built = build_cpu_reference(args)
+    line = {"metric": METRIC, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic"}
+    if built is None:
+        line["unavailable"] = "oracle/_ref/libggref.so (the unmodified reference) is not built on this box"
+        print(json.dumps(line))
+        return
+    R, rm, n, threads = built
+    rng = np.random.default_rng(SEED)
+    probe = rng.integers(0, n, 1 << 14).astype(np.uint64)
+    s, _ = rm.time_get_rows(probe, threads)
+    rate = probe.size / max(s, 1e-9)
+    budget = 90.0 / max(1, args.steps + args.warmup)
+    cnt = int(min(1 << 22, max(1 << 12, rate * budget)))
+    times = []
+    for it in range(args.warmup + args.steps):
+        rows = rng.integers(0, n, cnt).astype(np.uint64)
+        s, _ = rm.time_get_rows(rows, threads)
+        if it >= args.warmup:
+            times.append(s)
+    ms = 1e3 * float(np.mean(times))
+    v = cnt / (ms / 1e3)
+    sample = ("%d random row ids per step on a %d x %d d=%g sub-shape of the same generator (reference builder, "
+              "basic partitioner arity %d); unmodified BRWT::get_row under omp parallel for" %
+              (cnt, n, args.cols, args.density, args.arity))
+    line.update({"value": v, "ms_per_step": ms,
+                 "config": workload_config(args, 1, sub_rows=n),
+                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
+                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    print(json.dumps(line))
+
+
+def workload_config(args, n_gpus, sub_rows=None):
+    c = {"workload": "C4 Kingsford-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner; "
+                     "get_rows over %d uniformly random row ids per GPU per step" %
+                     (args.rows, args.cols, args.density, args.arity, args.batch),
+         "rows": int(args.rows), "cols": args.cols, "density": args.density, "arity": args.arity,
+         "batch_rows_per_gpu": args.batch, "seed": SEED,
+         "parallelism": "replicas x%d, batch-sharded, no data-path collective" % n_gpus,
+         "l2": "inputs larger than L2 (random gathers over the whole device image)"}
+    if sub_rows is not None:
+        c["cpu_sub_shape_rows"] = sub_rows
+    return c
+
+
+# --------------------------------------------------------------------------------------------
+# ours
+# --------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import genome_graph_annotation_b200 as g
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available() or g.device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    n = int(args.rows)
+    B = args.batch
+    K, W = args.steps, args.warmup
+    t0 = time.time()
+    gm = g.GpuMatrix.synthesize_brwt(n, args.cols, args.density, seed=SEED, arity=args.arity, device=local)
+    torch.cuda.synchronize()
+    build_s = time.time() - t0
+    ws = gm.workspace()
+    stream = torch.cuda.ExternalStream(ws.stream, device=torch.device("cuda", local))
+
+    # distinct batches of row ids (seeded per rank); cycled if K + W exceeds the pool
+    n_pool = min(K + W, 6)
+    gen = torch.Generator(device="cuda")
+    batches = []
+    for b in range(n_pool):
+        gen.manual_seed(SEED + 1000 * rank + b)
+        batches.append(torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen))
+    torch.cuda.synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step(i):
+        return ws.get_rows_device(batches[i % n_pool].data_ptr(), B, 8)
+
+    # ---- device-resident number ----------------------------------------------------------
+    for i in range(W):
+        device_step(i)
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kern_ms, touches, probes, ids, launches = [], 0, 0, 0, 0
+    with torch.cuda.stream(stream):
+        e0.record()
+    for i in range(K):
+        _, _, total = device_step(W + i)
+        kern_ms.append(ws.stat("kernel_ms"))
+        touches += int(ws.stat("touches"))
+        probes += int(ws.stat("probes"))
+        launches += int(ws.stat("launches"))
+        ids += total
+    with torch.cuda.stream(stream):
+        e1.record()
+    barrier()
+    clk = clocks.stop()
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / K
+    value = world * B / (ms_step / 1e3)
+
+    # ---- end to end through the host-buffer C ABI ------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        cap = int(ids / K * 1.05) + 1024
+        h_rows = [b.cpu().pin_memory() for b in batches[:min(n_pool, 3)]]
+        h_off = torch.empty(B + 1, dtype=torch.int64).pin_memory()
+        h_cols = torch.empty(cap, dtype=torch.int64).pin_memory()
+        np_rows = [r.numpy().view(np.uint64) for r in h_rows]
+        np_off, np_cols = h_off.numpy().view(np.uint64), h_cols.numpy().view(np.uint64)
+        Ke, We = max(3, min(K, 5)), 2
+        for i in range(We):
+            gm.get_rows_into(np_rows[i % len(np_rows)], np_off, np_cols)
+        barrier()
+        tw = time.perf_counter()
+        d2h = 0
+        for i in range(Ke):
+            total = gm.get_rows_into(np_rows[(We + i) % len(np_rows)], np_off, np_cols)
+            d2h += (B + 1) * 8 + total * 8
+        torch.cuda.synchronize()
+        te = torch.tensor([time.perf_counter() - tw], device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * B * Ke / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": B * 8,
+               "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
+               "api": "ggq_get_rows_into (host row ids in, host CSR offsets + u64 column ids out)"}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the descent kernel (8 + 8 + 8 k_t + 32 V_t bytes per row) ---
+    peak, peak_src = peaks()
+    k_ms = float(np.mean(kern_ms))
+    alg_bytes = (16.0 * B * K + 8.0 * ids + 32.0 * touches) / K
+    layout_bytes = (8.0 * B * K + 4.0 * ids + 64.0 * probes) / K   # what this layout must move: 64-B sibling blocks
+    achieved = alg_bytes / (k_ms / 1e3) / 1e9
+    roof = {"bound": "hbm", "kernel": "brwt_rows_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "kernel_ms": k_ms,
+            "algorithmic_bytes_per_launch": alg_bytes,
+            "bytes_per_row": alg_bytes / B, "node_touches_per_row": touches / (B * K),
+            "layout_bytes_per_launch": layout_bytes, "layout_achieved": layout_bytes / (k_ms / 1e3) / 1e9,
+            "layout_frac": layout_bytes / (k_ms / 1e3) / 1e9 / peak,
+            "kernel_share_of_step": k_ms / ms_step}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            roof["traffic"] = json.load(open(tr)).get("brwt_rows_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic", "config": workload_config(args, world),
+            "clocks": clk, "roofline": roof, "gpu_launches": launches,
+            "build_seconds": build_s, "device_image_gb": gm.device_bytes / 1e9,
+            "column_ids_per_row": ids / (B * K)}
+    if e2e is not None:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        built = build_cpu_reference(args)
+        if built is not None:
+            R, rm, sub_n, threads = built
+            rate, cnt, secs = cpu_sample_rate(rm, sub_n, threads, 15.0)
+            line["cpu_baseline"] = {
+                "value": rate, "unit": UNIT, "cores": threads, "kind": "reference",
+                "sample": "%d random rows in %.1f s on a %d x %d d=%g sub-shape (same generator; the reference "
+                          "builder cannot make the full shape); unmodified BRWT::get_row under omp parallel for" %
+                          (cnt, secs, sub_n, args.cols, args.density)}
+    print(json.dumps(line))
+    ws.close()
+    gm.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -71,6 +71,7 @@ def lib():
         "ggq_workspace_create": (C.c_int, [vp, C.POINTER(vp)]),
         "ggq_workspace_free": (None, [vp]),
         "ggq_workspace_stream": (vp, [vp]),
+        "ggq_workspace_stat": (C.c_double, [vp, C.c_int]),
         "ggq_get_rows_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_get": (C.c_int, [vp, u64p, u64p, C.c_uint64, u8p]),
         "ggq_has_column": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u8p]),
@@ -281,6 +282,10 @@ class Workspace:
     @property
     def stream(self):
         return lib().ggq_workspace_stream(self._h)
+
+    def stat(self, what):
+        """what: 'kernel_ms' | 'probes' | 'touches' | 'launches' of the last query on this workspace."""
+        return lib().ggq_workspace_stat(self._h, {"kernel_ms": 0, "probes": 1, "touches": 2, "launches": 3}[what])
 
     def get_rows_device(self, d_rows_ptr, n, col_bytes=4):
         """d_rows_ptr: device pointer (int).  -> (d_offsets_ptr, d_cols_ptr, n_cols), owned by the workspace."""

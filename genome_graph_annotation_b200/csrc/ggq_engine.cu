@@ -249,12 +249,16 @@ Workspace::Workspace(const Matrix *m_) : m(m_) {
     d_ctrl.alloc(8);
     d_err.alloc(1);
     CUDA_CHECK(cudaMallocHost(&h_ctrl, 8 * sizeof(u64)));
+    CUDA_CHECK(cudaEventCreate(&ev0));
+    CUDA_CHECK(cudaEventCreate(&ev1));
     if (m->kind == Matrix::BRWT && m->cap_spill)
         d_spill.alloc(size_t(m->rows_grid) * kRowsWarps * m->cap_spill);
 }
 
 Workspace::~Workspace() {
     cudaSetDevice(m->device);
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
     if (stream) cudaStreamDestroy(stream);
     if (h_ctrl) cudaFreeHost(h_ctrl);
     if (h_stage) cudaFreeHost(h_stage);
@@ -327,18 +331,22 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         a.bm_words = m->bm_words; a.rb = m->rb; a.err = ws->d_err.p;
         u64 batches = (n + m->rb - 1) / m->rb;
         u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+        CUDA_CHECK(cudaEventRecord(ws->ev0, st));
         brwt_rows_kernel<<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
         CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaEventRecord(ws->ev1, st));
         size_t cb = ws->cub_bytes;
         // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
         CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
         cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
-        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 3 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 4 * sizeof(u64), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 4, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
         if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) throw std::runtime_error("descent stack overflow (engine bug)");
         u64 total = ws->h_ctrl[0];
         ws->last_probes = ws->h_ctrl[2];
+        ws->last_touches = ws->h_ctrl[3];
+        ws->kernel_timed = true;
         ws->launches = 3;  // descent + 2 scan kernels
         if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo (steady state never does)
             ws->d_tmp.alloc(total + total / 8 + 1024);
@@ -486,6 +494,19 @@ int ggq_workspace_create(const ggq_matrix *m, ggq_workspace **out) {
 }
 void ggq_workspace_free(ggq_workspace *ws) { delete ws; }
 void *ggq_workspace_stream(ggq_workspace *ws) { return ws->stream; }
+double ggq_workspace_stat(const ggq_workspace *ws, int what) {
+    switch (what) {
+        case GGQ_STAT_KERNEL_MS: {
+            float ms = 0.f;
+            if (!ws->kernel_timed || cudaEventElapsedTime(&ms, ws->ev0, ws->ev1) != cudaSuccess) return -1.0;
+            return ms;
+        }
+        case GGQ_STAT_PROBES: return double(ws->last_probes);
+        case GGQ_STAT_TOUCHES: return double(ws->last_touches);
+        case GGQ_STAT_LAUNCHES: return double(ws->launches);
+        default: return -1.0;
+    }
+}
 
 int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n, int col_bytes,
                         const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols) {

@@ -100,8 +100,10 @@ struct Workspace {
     u64 *h_ctrl = nullptr;
     unsigned char *h_stage = nullptr;
     size_t h_stage_bytes = 0;
-    u64 last_probes = 0;
+    u64 last_probes = 0, last_touches = 0;
     int launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
+    bool kernel_timed = false;
 
     explicit Workspace(const Matrix *m_);
     ~Workspace();

@@ -172,7 +172,7 @@ struct RowsArgs {
     u64 n;                    // number of queries
     u32 *tmp_cols;            // unordered chunk arena
     u64 tmp_cap;
-    u64 *cursor;              // [0] chunk cursor, [1] batch ticket, [2] probe counter
+    u64 *cursor;              // [0] chunk cursor, [1] batch ticket, [2] probe counter, [3] (node,row) touches
     u64 *row_tmp_off;         // per query: start in tmp_cols
     u32 *row_cnt;             // per query: number of columns
     u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
@@ -202,6 +202,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     const u32 cap_total = a.cap_s + a.cap_spill;
     const u32 bm_total = a.rb * a.bm_words;
     u64 probes = 0;
+    u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
 
     for (;;) {
         u64 batch = 0;
@@ -267,6 +268,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             top = new_top + nc + __popc(child_mask);
             if (top > cap_total) top = cap_total;  // overflow already flagged in *err
             if (lane == 0) probes += c;
+            if (active && j == 0) touches += cnt;
             __syncwarp();
         }
 
@@ -320,6 +322,8 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         __syncwarp();
     }
     if (lane == 0 && probes) atomicAdd(a.cursor + 2, probes);
+    touches = __reduce_add_sync(0xffffffffu, touches);
+    if (lane == 0 && touches) atomicAdd(a.cursor + 3, u64(touches));
 }
 
 // One warp per batch of `rb` rows: the batch is contiguous both in the chunk arena and in the CSR.

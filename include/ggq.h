@@ -104,6 +104,11 @@ void ggq_buffer_free(void *p);
 int ggq_workspace_create(const ggq_matrix *m, ggq_workspace **out);
 void ggq_workspace_free(ggq_workspace *ws);
 void *ggq_workspace_stream(ggq_workspace *ws);  /* cudaStream_t */
+/* Measurements of the last query on this workspace (for roofline accounting, DESIGN.md "Measurement"):
+ * device time of the dominant kernel between two CUDA events on the workspace stream; sibling-group
+ * probes (one 16/32/64-byte block each); (node,row) bit tests (V_t of SURVEY.md 8d); kernel launches. */
+enum { GGQ_STAT_KERNEL_MS = 0, GGQ_STAT_PROBES = 1, GGQ_STAT_TOUCHES = 2, GGQ_STAT_LAUNCHES = 3 };
+double ggq_workspace_stat(const ggq_workspace *ws, int what);
 int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
                         int col_bytes, const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols);
 

@@ -79,6 +79,7 @@ def lib():
     L.ggref_gen_norepl.argtypes = [C.c_uint64, C.c_uint64, C.c_double, C.c_int, u64p]
     L.ggref_gen_uniform_rows.argtypes = [C.c_uint64, C.c_uint64, C.c_double, C.c_uint64, C.c_int, u64p]
     L.ggref_gen_random_ints.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, u64p]
+    L.ggref_gen_implicit.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p]
     L.ggref_max_threads.restype = C.c_int
     _lib = L
     return L
@@ -265,6 +266,13 @@ def gen_uniform_rows(n, m, d, n_unique, seed=42):
 def gen_random_ints(count, begin, end, seed=42):
     out = np.empty(count, dtype=np.uint64)
     lib().ggref_gen_random_ints(count, begin, end, seed, _p(out))
+    return out
+
+
+def gen_implicit(n, m, threshold, seed=42):
+    """Portable implicit matrix, column-major words."""
+    out = np.zeros((m, (n + 63) // 64), dtype=np.uint64)
+    lib().ggref_gen_implicit(n, m, threshold, seed, _p(out))
     return out
 
 

@@ -315,6 +315,30 @@ void ggref_gen_random_ints(uint64_t count, uint64_t begin, uint64_t end, int see
     std::memcpy(out, v.data(), count * 8);
 }
 
+// Portable implicit matrix of SURVEY.md §8(d) (configs C4/C5): cell (i, j) is set iff
+// mix64(seed * 0x9E3779B97F4A7C15 + i * m + j) < threshold.  Column-major words, wpc = ceil(n/64).
+static inline uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ULL;
+    x ^= x >> 27; x *= 0x94d049bb133111ebULL;
+    x ^= x >> 31;
+    return x;
+}
+void ggref_gen_implicit(uint64_t n, uint64_t m, uint64_t threshold, uint64_t seed, uint64_t *out_words) {
+    const uint64_t wpc = (n + 63) / 64;
+    const uint64_t base = seed * 0x9E3779B97F4A7C15ULL;
+    #pragma omp parallel for schedule(static)
+    for (uint64_t j = 0; j < m; ++j) {
+        uint64_t *dst = out_words + j * wpc;
+        for (uint64_t w = 0; w < wpc; ++w) {
+            uint64_t word = 0;
+            const uint64_t i0 = w * 64, i1 = std::min<uint64_t>(n, i0 + 64);
+            for (uint64_t i = i0; i < i1; ++i)
+                word |= uint64_t(mix64(base + i * m + j) < threshold) << (i - i0);
+            dst[w] = word;
+        }
+    }
+}
+
 int ggref_max_threads() { return omp_get_max_threads(); }
 
 }  // extern "C"
