@@ -1,0 +1,245 @@
+// Host object + query kernels + C ABI of the bit vectors (include/ggq.h "bit vectors").
+#pragma once
+
+namespace ggq {
+
+enum BvOp { OP_RANK1 = 0, OP_SELECT1 = 1, OP_GET = 2 };
+
+struct BvImg {
+    int kind;
+    u64 n_bits, n_ones;
+    RbImg stat;
+    SdImg sd;
+    RrrImg rrr;
+};
+
+// One thread per query, grid-stride.  OutT = u64 (rank/select) or unsigned char (get).
+template <int KIND, int OP, typename OutT>
+__global__ void __launch_bounds__(256) bv_query_kernel(BvImg v, const u64 *q, u64 n, OutT *out) {
+    __shared__ RrrTables T;
+    if (KIND == GGQ_BV_RRR) {
+        const u64 *src = reinterpret_cast<const u64 *>(&g_rrr_tables);
+        u64 *dst = reinterpret_cast<u64 *>(&T);
+        for (u32 i = threadIdx.x; i < sizeof(RrrTables) / 8; i += blockDim.x) dst[i] = src[i];
+        __syncthreads();
+    }
+    for (u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += u64(gridDim.x) * blockDim.x) {
+        u64 x = q[t];
+        u64 res = 0;
+        if (OP == OP_SELECT1) {
+            // k in [1, n_ones]; anything else is undefined in the reference (assert only): return n_bits
+            if (x < 1 || x > v.n_ones) res = v.n_bits;
+            else if (KIND == GGQ_BV_STAT) res = rb_select<false>(v.stat, x - 1);
+            else if (KIND == GGQ_BV_SD) res = sd_select1(v.sd, x);
+            else res = rrr_select(v.rrr, T, x - 1);
+        } else if (OP == OP_RANK1) {
+            if (v.n_bits == 0) res = 0;
+            else {
+                u64 i = x < v.n_bits ? x : v.n_bits - 1;   // clamp (bit_vector.cpp:285,692,860)
+                bool bit;
+                if (KIND == GGQ_BV_STAT) { res = rb_rank_excl_bit(v.stat, i, &bit); res += bit; }
+                else if (KIND == GGQ_BV_SD) res = sd_rank1(v.sd, i);
+                else res = rrr_rank_incl_bit(v.rrr, T, i, &bit);
+            }
+        } else {
+            bool bit = false;
+            if (x < v.n_bits) {
+                if (KIND == GGQ_BV_STAT) rb_rank_excl_bit(v.stat, x, &bit);
+                else if (KIND == GGQ_BV_SD) bit = sd_get(v.sd, x);
+                else rrr_rank_incl_bit(v.rrr, T, x, &bit);
+            }
+            res = bit;
+        }
+        out[t] = OutT(res);
+    }
+}
+
+// bit i set iff mix64(seed_mul + i) < threshold  (SURVEY.md 8d portable generator)
+__global__ void synth_bits_kernel(u64 *words, u64 n_words, u64 n_bits, u64 threshold, u64 seed_mul) {
+    u64 w = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    u64 x = 0;
+    u64 base = w * 64;
+    for (u32 b = 0; b < 64; ++b) {
+        u64 i = base + b;
+        if (i < n_bits && mix64(seed_mul + i) < threshold) x |= 1ull << b;
+    }
+    words[w] = x;
+}
+
+struct BitVec {
+    int kind = 0, device = 0;
+    u64 n_bits = 0, n_ones = 0;
+    RbBuf stat;
+    SdBuf sd;
+    RrrBuf rrr;
+    BvImg img{};
+    cudaStream_t stream = nullptr;
+    DeviceBuf<u64> d_q, d_out;
+    std::mutex mu;
+
+    ~BitVec() { if (stream) cudaStreamDestroy(stream); }
+
+    size_t bytes() const { return stat.bytes() + sd.bytes() + rrr.bytes(); }
+
+    void build_from_device(int kind_, const u64 *d_plain, u64 n, int force_inverted) {
+        kind = kind_;
+        n_bits = n;
+        CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        if (kind == GGQ_BV_STAT) { rb_build(&stat, d_plain, n, false, stream); n_ones = stat.img.n_ones; }
+        else if (kind == GGQ_BV_SD) {
+            sd_build(&sd, d_plain, n, force_inverted, stream);
+            n_ones = sd.img.inverted ? n - sd.img.m : sd.img.m;
+        } else if (kind == GGQ_BV_RRR) { rrr_build(&rrr, d_plain, n, stream); n_ones = rrr.img.n_ones; }
+        else throw std::runtime_error("unknown bit vector kind");
+        img.kind = kind; img.n_bits = n_bits; img.n_ones = n_ones;
+        img.stat = stat.img; img.sd = sd.img; img.rrr = rrr.img;
+    }
+
+    template <int KIND>
+    void launch_kind(int op, const u64 *q, u64 n, void *out, cudaStream_t st) const {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        u32 grid = u32(std::min<u64>((n + 255) / 256, u64(sms) * (KIND == GGQ_BV_RRR ? 6 : 8) * 4));
+        if (!grid) return;
+        if (op == OP_RANK1) bv_query_kernel<KIND, OP_RANK1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));
+        else if (op == OP_SELECT1) bv_query_kernel<KIND, OP_SELECT1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));
+        else bv_query_kernel<KIND, OP_GET, unsigned char><<<grid, 256, 0, st>>>(img, q, n, static_cast<unsigned char *>(out));
+        CUDA_CHECK(cudaGetLastError());
+    }
+
+    void launch(int op, const u64 *q, u64 n, void *out, cudaStream_t st) const {
+        if (kind == GGQ_BV_STAT) launch_kind<GGQ_BV_STAT>(op, q, n, out, st);
+        else if (kind == GGQ_BV_SD) launch_kind<GGQ_BV_SD>(op, q, n, out, st);
+        else launch_kind<GGQ_BV_RRR>(op, q, n, out, st);
+    }
+
+    void query_host(int op, const u64 *q, u64 n, void *out) {
+        if (!n) return;
+        std::lock_guard<std::mutex> lk(mu);
+        CUDA_CHECK(cudaSetDevice(device));
+        if (d_q.n < n) { d_q.alloc(n); d_out.alloc(n); }
+        CUDA_CHECK(cudaMemcpyAsync(d_q.p, q, n * 8, cudaMemcpyHostToDevice, stream));
+        launch(op, d_q.p, n, d_out.p, stream);
+        CUDA_CHECK(cudaMemcpyAsync(out, d_out.p, op == OP_GET ? n : n * 8, cudaMemcpyDeviceToHost, stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
+};
+
+inline BitVec *bv_from_host_words(int kind, const u64 *words, u64 n_bits, int device, int force_inverted) {
+    CUDA_CHECK(cudaSetDevice(device));
+    std::unique_ptr<BitVec> v(new BitVec());
+    v->device = device;
+    u64 n_words = (n_bits + 63) / 64;
+    DeviceBuf<u64> plain;
+    plain.alloc(std::max<u64>(n_words, 1));
+    if (n_words) {
+        CUDA_CHECK(cudaMemcpy(plain.p, words, n_words * 8, cudaMemcpyHostToDevice));
+        if (n_bits & 63) {  // clear padding
+            u64 last = words[n_words - 1] & ((1ull << (n_bits & 63)) - 1ull);
+            CUDA_CHECK(cudaMemcpy(plain.p + n_words - 1, &last, 8, cudaMemcpyHostToDevice));
+        }
+    }
+    v->build_from_device(kind, plain.p, n_bits, force_inverted);
+    return v.release();
+}
+
+inline std::vector<u64> plain_to_words64(const PlainBits &b) {
+    u64 n_words = (b.size + 63) / 64;
+    std::vector<u64> w(std::max<u64>(n_words, 1), 0);
+    for (u64 i = 0; i < n_words; ++i) {
+        u64 lo = b.w[2 * i], hi = (2 * i + 1 < b.w.size()) ? b.w[2 * i + 1] : 0;
+        w[i] = lo | (hi << 32);
+    }
+    return w;
+}
+
+}  // namespace ggq
+
+struct ggq_bv : ggq::BitVec {};
+
+extern "C" {
+
+int ggq_bv_build(int kind, const uint64_t *words, uint64_t n_bits, int device, ggq_bv **out) {
+    GGQ_TRY
+    if (!out || (!words && n_bits) || kind < 0 || kind > 2) return fail(GGQ_ERR_ARG, "bad argument");
+    *out = static_cast<ggq_bv *>(bv_from_host_words(kind, reinterpret_cast<const u64 *>(words), n_bits, device, -1));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_bv_load_buffer(int kind, const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_bv **out) {
+    GGQ_TRY
+    if (!out || (!buf && len) || kind < 0 || kind > 2) return fail(GGQ_ERR_ARG, "bad argument");
+    Reader in(buf, len);
+    PlainBits bits;
+    int force_inv = -1;
+    if (kind == GGQ_BV_STAT) load_stat(in, &bits);
+    else if (kind == GGQ_BV_RRR) load_rrr63(in, &bits);
+    else {
+        SdColumn c;
+        load_sd(in, &c);
+        sd_to_plain(c, &bits);
+        force_inv = c.inverted ? 1 : 0;   // keep the file's representation choice (is_inverted())
+    }
+    if (consumed) *consumed = in.consumed();
+    std::vector<u64> w = plain_to_words64(bits);
+    *out = static_cast<ggq_bv *>(bv_from_host_words(kind, w.data(), bits.size, device, force_inv));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_bv_synthesize(int kind, uint64_t n_bits, uint64_t threshold, uint64_t seed, int device, ggq_bv **out) {
+    GGQ_TRY
+    if (!out || kind < 0 || kind > 2) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(device));
+    std::unique_ptr<BitVec> v(new BitVec());
+    v->device = device;
+    u64 n_words = (n_bits + 63) / 64;
+    DeviceBuf<u64> plain;
+    plain.alloc(std::max<u64>(n_words, 1));
+    if (n_words) {
+        synth_bits_kernel<<<u32((n_words + 255) / 256), 256>>>(plain.p, n_words, n_bits, threshold, seed * 0x9E3779B97F4A7C15ULL);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaDeviceSynchronize());
+    }
+    v->build_from_device(kind, plain.p, n_bits, -1);
+    *out = static_cast<ggq_bv *>(v.release());
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+void ggq_bv_free(ggq_bv *v) {
+    if (!v) return;
+    cudaSetDevice(v->device);
+    delete static_cast<ggq::BitVec *>(v);
+}
+uint64_t ggq_bv_size(const ggq_bv *v) { return v->n_bits; }
+uint64_t ggq_bv_num_set_bits(const ggq_bv *v) { return v->n_ones; }
+int ggq_bv_is_inverted(const ggq_bv *v) { return v->kind == GGQ_BV_SD ? int(v->sd.img.inverted) : 0; }
+uint64_t ggq_bv_device_bytes(const ggq_bv *v) { return v->bytes(); }
+
+static int bv_host(const ggq_bv *v, int op, const uint64_t *q, uint64_t n, void *out) {
+    GGQ_TRY
+    if (!v || (!q && n) || (!out && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    const_cast<ggq_bv *>(v)->query_host(op, reinterpret_cast<const u64 *>(q), n, out);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+int ggq_bv_rank1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_RANK1, q, n, out); }
+int ggq_bv_select1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_SELECT1, q, n, out); }
+int ggq_bv_get(const ggq_bv *v, const uint64_t *q, uint64_t n, uint8_t *out) { return bv_host(v, OP_GET, q, n, out); }
+
+static int bv_dev(const ggq_bv *v, int op, const uint64_t *d_q, uint64_t n, void *d_out, void *stream) {
+    GGQ_TRY
+    if (!v || (!d_q && n) || (!d_out && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(v->device));
+    v->launch(op, reinterpret_cast<const u64 *>(d_q), n, d_out, static_cast<cudaStream_t>(stream));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+int ggq_bv_rank1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_RANK1, d_q, n, d_out, stream); }
+int ggq_bv_select1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_SELECT1, d_q, n, d_out, stream); }
+int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t *d_out, void *stream) { return bv_dev(v, OP_GET, d_q, n, d_out, stream); }
+
+}  // extern "C"

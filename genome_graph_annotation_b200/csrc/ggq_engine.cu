@@ -715,4 +715,4 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
 
 }  // extern "C"
 
-#include "ggq_bv_capi.inl"
+#include "ggq_bv_api.cuh"
