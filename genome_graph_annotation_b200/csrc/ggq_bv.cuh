@@ -219,6 +219,17 @@ inline void rb_build(RbBuf *out, const u64 *d_plain, u64 n_bits, bool want_sel0,
     CUDA_CHECK(cudaStreamSynchronize(st));
 }
 
+// PlainBits (u32 words, host parsers) -> LSB-first u64 words
+inline std::vector<u64> plain_to_words64(const PlainBits &b) {
+    u64 n_words = (b.size + 63) / 64;
+    std::vector<u64> w(std::max<u64>(n_words, 1), 0);
+    for (u64 i = 0; i < n_words; ++i) {
+        u64 lo = b.w[2 * i], hi = (2 * i + 1 < b.w.size()) ? b.w[2 * i + 1] : 0;
+        w[i] = lo | (hi << 32);
+    }
+    return w;
+}
+
 }  // namespace ggq
 
 #include "ggq_bv_sd.cuh"

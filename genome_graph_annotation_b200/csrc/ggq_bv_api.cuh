@@ -144,16 +144,6 @@ inline BitVec *bv_from_host_words(int kind, const u64 *words, u64 n_bits, int de
     return v.release();
 }
 
-inline std::vector<u64> plain_to_words64(const PlainBits &b) {
-    u64 n_words = (b.size + 63) / 64;
-    std::vector<u64> w(std::max<u64>(n_words, 1), 0);
-    for (u64 i = 0; i < n_words; ++i) {
-        u64 lo = b.w[2 * i], hi = (2 * i + 1 < b.w.size()) ? b.w[2 * i + 1] : 0;
-        w[i] = lo | (hi << 32);
-    }
-    return w;
-}
-
 }  // namespace ggq
 
 struct ggq_bv : ggq::BitVec {};

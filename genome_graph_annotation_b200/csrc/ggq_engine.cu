@@ -303,6 +303,7 @@ void Matrix::release(Workspace *w) const {
 }
 Matrix::~Matrix() {
     for (Workspace *w : pool) delete w;
+    delete cm;
 }
 
 // ------------------------------------------------------------------------------------------
