@@ -53,6 +53,8 @@ def lib():
         "ggq_colmajor_load_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.POINTER(vp)]),
         "ggq_brwt_synthesize": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(vp)]),
         "ggq_free": (None, [vp]),
+        "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
+        "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
         "ggq_num_rows": (C.c_uint64, [vp]),
         "ggq_num_columns": (C.c_uint64, [vp]),
         "ggq_num_relations": (C.c_uint64, [vp]),
@@ -135,6 +137,25 @@ def density_threshold(d):
 
 
 SEED_MUL = 0x9E3779B97F4A7C15
+
+
+def inspect_brwt(data):
+    """Host-only parse + flatten of a serialized BRWT (no GPU needed) -> dict of stats."""
+    stats = (C.c_uint64 * 8)()
+    used = C.c_size_t()
+    _check(lib().ggq_brwt_inspect_buffer(data, len(data), C.byref(used), stats))
+    keys = ["num_rows", "num_columns", "num_nodes", "num_relations", "total_column_size", "groups",
+            "device_bytes", "max_depth"]
+    d = dict(zip(keys, [int(x) for x in stats]))
+    d["consumed"] = used.value
+    m = d["num_columns"]
+    dfs = np.zeros(max(m, 1), dtype=np.uint32)
+    dep = np.zeros(max(m, 1), dtype=np.uint32)
+    _check(lib().ggq_brwt_inspect_columns(data, len(data), dfs.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                          dep.ctypes.data_as(C.POINTER(C.c_uint32))))
+    d["dfs_columns"] = dfs[:m].copy()
+    d["column_depth"] = dep[:m].copy()
+    return d
 
 
 class GpuMatrix:

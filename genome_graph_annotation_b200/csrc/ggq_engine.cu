@@ -473,6 +473,45 @@ int ggq_brwt_synthesize(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, ui
     GGQ_CATCH
 }
 
+int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t stats[8]) {
+    GGQ_TRY
+    if ((!buf && len) || !stats) return fail(GGQ_ERR_ARG, "bad argument");
+    Reader in(buf, len);
+    ParsedNode root;
+    load_brwt_node(in, &root);
+    if (consumed) *consumed = in.consumed();
+    FlatTree t;
+    flatten_parsed(std::move(root), &t);
+    assign_groups(&t);
+    assign_geometry(&t);
+    u64 rel = 0, tcs = 0;
+    for (const FlatNode &n : t.nodes) {
+        tcs += n.size;
+        if (n.children.empty()) rel += n.ones * n.cols.size();
+    }
+    stats[0] = t.n_rows; stats[1] = t.n_cols; stats[2] = t.nodes.size(); stats[3] = rel; stats[4] = tcs;
+    stats[5] = t.n_groups(); stats[6] = t.total_slots * 16 + t.total_sel * 4 + t.total_sb * 8; stats[7] = t.max_depth;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_brwt_inspect_columns(const uint8_t *buf, size_t len, uint32_t *dfs_cols, uint32_t *depth) {
+    GGQ_TRY
+    if (!buf && len) return fail(GGQ_ERR_ARG, "bad argument");
+    Reader in(buf, len);
+    ParsedNode root;
+    load_brwt_node(in, &root);
+    FlatTree t;
+    flatten_parsed(std::move(root), &t);
+    assign_groups(&t);
+    if (dfs_cols)
+        for (size_t i = 0; i < t.leaf_col.size(); ++i) dfs_cols[i] = t.leaf_col[i];
+    if (depth)
+        for (u64 c = 0; c < t.n_cols; ++c) depth[c] = t.col_path_off[c + 1] - t.col_path_off[c] - 1;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 void ggq_free(ggq_matrix *m) {
     if (!m) return;
     cudaSetDevice(m->device);

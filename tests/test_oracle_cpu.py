@@ -1,0 +1,146 @@
+"""CPU suite (no GPU): pins the oracle.
+
+* the plain-C restatement (oracle/brwt_oracle.c) against the committed golden fixtures — the reference's
+  own serialized streams and the reference's own answers (tests/golden/make_golden.py);
+* the restatement against the live reference (oracle/_ref/libggref.so) on seeded random inputs, when the
+  reference build is present;
+* the reference's own gtest files for the path (tests/test_{BRWT,BRWT_optimizer,bit_vector,column_major}.cpp)
+  run against the oracle build, when /root/reference is present.
+"""
+import glob
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, random_dense
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def load_gold(name):
+    return np.load(os.path.join(GOLD, name + ".npz"))
+
+
+MATS = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "brwt_*.npz")))
+BVS = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "bv_*.npz")))
+
+
+def test_fixtures_exist():
+    assert len(MATS) >= 6 and len(BVS) >= 5
+
+
+@pytest.mark.parametrize("name", MATS)
+def test_c_oracle_brwt_vs_golden(orc, name):
+    g = load_gold(name)
+    data = g["stream"].tobytes()
+    m = orc.OrcBRWT(data)
+    assert m.consumed == len(data)
+    n, ncol, rel, nodes, tcs = [int(x) for x in g["stats"]]
+    assert (m.num_rows, m.num_columns, m.num_relations, m.num_nodes, m.total_column_size) == (n, ncol, rel, nodes, tcs)
+    off, cols = g["row_offsets"], g["row_cols"]
+    shape = tuple(int(x) for x in g["shape"])
+    dense = np.unpackbits(g["dense"])[: shape[0] * shape[1]].reshape(shape) if shape[0] * shape[1] else np.zeros(shape, np.uint8)
+    touches = 0
+    for r in range(n):
+        got = m.get_row(r)
+        assert np.array_equal(got, cols[off[r]:off[r + 1]]), r          # order included
+        assert set(got.tolist()) == set(np.nonzero(dense[r])[0].tolist())
+        touches += m.row_touches(r)
+    assert touches == tcs   # SURVEY §6 identity: every bit of every node vector is visited exactly once
+    coff, crows = g["col_offsets"], g["col_rows"]
+    for c in range(ncol):
+        assert np.array_equal(m.get_column(c), crows[coff[c]:coff[c + 1]]), c
+        for r in range(0, n, 7):
+            assert m.get(r, c) == bool(dense[r, c])
+
+
+def test_c_oracle_colmajor_vs_golden(orc):
+    g = load_gold("colmajor_200x30")
+    data = g["stream"].tobytes()
+    m = orc.OrcColMajor(data)
+    n, ncol, rel = [int(x) for x in g["stats"]]
+    assert (m.consumed, m.num_rows, m.num_columns, m.num_relations) == (len(data), n, ncol, rel)
+    off, cols = g["row_offsets"], g["row_cols"]
+    for r in range(n):
+        assert np.array_equal(m.get_row(r), cols[off[r]:off[r + 1]])
+    coff, crows = g["col_offsets"], g["col_rows"]
+    for c in range(ncol):
+        assert np.array_equal(m.get_column(c), crows[coff[c]:coff[c + 1]])
+
+
+@pytest.mark.parametrize("name", BVS)
+@pytest.mark.parametrize("kind", ["stat", "sd", "rrr"])
+def test_c_oracle_bitvector_vs_golden(orc, name, kind):
+    g = load_gold(name)
+    n = int(g["n"][0])
+    data = g["stream_" + kind].tobytes()
+    v = orc.OrcBits.load(kind, data)
+    assert v.consumed == len(data) and v.size == n
+    pos = np.arange(n + 3, dtype=np.uint64)
+    assert np.array_equal(v.rank1(pos), g["rank1_" + kind])
+    if n:
+        assert np.array_equal(v.get(pos[:n]), g["get_" + kind])
+    sel = g["select1_" + kind]
+    if sel.size:
+        assert np.array_equal(v.select1(np.arange(1, sel.size + 1)), sel)
+    assert v.num_set_bits == sel.size
+    if kind == "sd":
+        assert int(v.is_inverted) == int(g["inverted_sd"][0])
+
+
+def test_golden16_known_answers(orc):
+    # tests/test_bit_vector.cpp:88-94: the 16-bit pattern and its hand-checkable answers
+    bits = [0, 1, 0, 1, 1, 1, 1, 0, 0, 1, 0, 0, 0, 0, 1, 1]
+    g = load_gold("bv_golden16")
+    for kind in ("stat", "sd", "rrr"):
+        assert g["rank1_" + kind][:16].tolist() == np.cumsum(bits).tolist()
+        assert g["rank1_" + kind][16:].tolist() == [8, 8, 8]          # clamped beyond the end
+        assert g["select1_" + kind].tolist() == [i for i, b in enumerate(bits) if b]
+
+
+@pytest.mark.parametrize("n,m,d,kw", [
+    (500, 17, 0.3, dict(arity=2)), (2000, 64, 0.05, dict(arity=4, greedy=True, relax=5)),
+    (300, 1, 0.5, dict(arity=2)), (100, 7, 1.0, dict(arity=3)), (100, 7, 0.0, dict(arity=3)),
+    (1500, 130, 0.02, dict(arity=2, greedy=True, relax=9)),
+])
+def test_c_oracle_vs_live_reference(orc, ref, n, m, d, kw):
+    dense = random_dense(n, m, d, seed=n + m)
+    rm = ref.RefMatrix.build_brwt(ref.pack_columns(dense), n, **kw)
+    data = rm.serialize()
+    om = orc.OrcBRWT(data)
+    assert (om.num_nodes, om.total_column_size, om.num_relations) == (rm.num_nodes, rm.total_column_size, rm.num_relations)
+    for r in range(0, n, max(1, n // 300)):
+        assert np.array_equal(om.get_row(r), rm.get_row(r))
+    for c in range(m):
+        assert np.array_equal(om.get_column(c), rm.get_column(c))
+
+
+def test_synth_generator_agrees(orc, ref, ggq):
+    # the portable implicit matrix: C oracle row == reference-side generator == numpy mix64
+    n, m, d = 300, 50, 0.1
+    thr = ggq.density_threshold(d)
+    cw = ref.gen_implicit(n, m, thr, 42)
+    dense = ref.unpack_columns(cw, n)
+    for r in (0, 1, 150, 299):
+        assert np.array_equal(orc.synth_row(m, thr, 42, r), np.nonzero(dense[r])[0].astype(np.uint64))
+    with np.errstate(over="ignore"):
+        x = np.uint64((42 * ggq.SEED_MUL) % 2**64) + np.uint64(5) * np.uint64(m) + np.arange(m, dtype=np.uint64)
+    assert np.array_equal((ggq.mix64(x) < np.uint64(thr)).astype(np.uint8), dense[5])
+    assert orc.mix64(12345) == int(ggq.mix64(np.array([12345], dtype=np.uint64))[0])
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference sources absent")
+def test_reference_unit_tests_pass_on_oracle_build():
+    """The reference's own 94 gtest cases for the path, compiled against the oracle build."""
+    odir = os.path.join(ROOT, "oracle")
+    p = subprocess.run(["make", "-C", odir, "-j8", "ref_tests"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert p.returncode == 0, p.stdout[-3000:]
+    run = os.path.join(odir, "_ref", "run")
+    os.makedirs(run, exist_ok=True)
+    p = subprocess.run(["../ref_unit_tests"], cwd=run, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                       text=True, timeout=900)
+    tail = p.stdout[-2000:]
+    assert p.returncode == 0, tail
+    assert "PASSED" in tail and "FAILED" not in tail, tail
