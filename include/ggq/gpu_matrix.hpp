@@ -1,0 +1,165 @@
+// Host C++17 adapters: GPU-resident drop-ins for the reference's BinaryMatrix implementations.
+//
+//   GpuBRWT      replaces  BRWT                 (annotation/hierarchical_annotation/BRWT.hpp:18-61)
+//   GpuColMajor  replaces  ColMajorCompressed   (annotation/column_compressed/column_major.hpp:10-37)
+//
+// Both derive from the reference's own `BinaryMatrix` (common/binary_matrix.hpp:9-29) — this header is
+// compiled INSIDE the reference tree (it includes "binary_matrix.hpp" from the reference's include path)
+// and links against libggq.so.  Same names, argument meaning and error behaviour as the reference:
+// load() returns false on any failure and never throws (BRWT.cpp:88-110); serialize() throws
+// std::ofstream::failure on a bad stream (BRWT.cpp:114-115); results are returned by value; const
+// queries are safe from concurrent threads (the engine keeps a per-call stream + scratch pool).
+// Batched calls named by the north star and absent in the reference are defined by composition:
+//   get_rows(R)[t] == get_row(R[t]);  slice_rows(R) == concat_t(get_row(R[t]) ++ [UINT64_MAX]);
+//   has_column(R, j)[t] == get(R[t], j).
+// Runtime CUDA failures surface as std::runtime_error (there is no CPU fallback to hide them).
+#ifndef GGQ_GPU_MATRIX_HPP_
+#define GGQ_GPU_MATRIX_HPP_
+
+#include <fstream>
+#include <istream>
+#include <memory>
+#include <ostream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "binary_matrix.hpp"  // the reference's interface (common/binary_matrix.hpp)
+#include "../ggq.h"
+
+namespace ggq {
+
+class GpuMatrixBase : public BinaryMatrix {
+  public:
+    explicit GpuMatrixBase(int device = 0) : device_(device) {}
+
+    uint64_t num_columns() const override { return h_ ? ggq_num_columns(h_.get()) : 0; }
+    uint64_t num_rows() const override { return h_ ? ggq_num_rows(h_.get()) : 0; }
+    uint64_t num_relations() const override { return h_ ? ggq_num_relations(h_.get()) : 0; }
+
+    bool get(Row row, Column column) const override {
+        uint8_t out = 0;
+        check(ggq_get(handle(), &row, &column, 1, &out));
+        return out;
+    }
+
+    std::vector<Column> get_row(Row row) const override {
+        std::vector<std::vector<Column>> r = get_rows(std::vector<Row>{row});
+        return std::move(r[0]);
+    }
+
+    std::vector<Row> get_column(Column column) const override {
+        uint64_t *rows = nullptr, n = 0;
+        check(ggq_get_column(handle(), column, &rows, &n));
+        std::vector<Row> out(rows, rows + n);
+        ggq_buffer_free(rows);
+        return out;
+    }
+
+    // ---- batched extensions ----------------------------------------------------------------
+    std::vector<std::vector<Column>> get_rows(const std::vector<Row> &rows) const {
+        ggq_rows_result *res = nullptr;
+        check(ggq_get_rows(handle(), rows.data(), rows.size(), &res));
+        const uint64_t *off = ggq_rows_offsets(res), *cols = ggq_rows_columns(res);
+        std::vector<std::vector<Column>> out(rows.size());
+        for (size_t t = 0; t < rows.size(); ++t) out[t].assign(cols + off[t], cols + off[t + 1]);
+        ggq_rows_result_free(res);
+        return out;
+    }
+
+    // CSR form of get_rows: offsets has rows.size() + 1 entries
+    void get_rows_csr(const std::vector<Row> &rows, std::vector<uint64_t> *offsets, std::vector<Column> *cols) const {
+        ggq_rows_result *res = nullptr;
+        check(ggq_get_rows(handle(), rows.data(), rows.size(), &res));
+        const uint64_t *off = ggq_rows_offsets(res);
+        offsets->assign(off, off + rows.size() + 1);
+        cols->assign(ggq_rows_columns(res), ggq_rows_columns(res) + off[rows.size()]);
+        ggq_rows_result_free(res);
+    }
+
+    std::vector<Column> slice_rows(const std::vector<Row> &rows) const {
+        uint64_t *buf = nullptr, n = 0;
+        check(ggq_slice_rows(handle(), rows.data(), rows.size(), &buf, &n));
+        std::vector<Column> out(buf, buf + n);
+        ggq_buffer_free(buf);
+        return out;
+    }
+
+    std::vector<bool> has_column(const std::vector<Row> &rows, Column column) const {
+        std::vector<uint8_t> tmp(rows.size());
+        check(ggq_has_column(handle(), rows.data(), rows.size(), column, tmp.data()));
+        return std::vector<bool>(tmp.begin(), tmp.end());
+    }
+
+    // The matrix streams it was loaded from are kept on the host so that serialize() reproduces them
+    // byte for byte (the device image is a different, query-oriented layout).
+    void serialize(std::ostream &out) const override {
+        if (!out.good()) throw std::ofstream::failure("Error when dumping the matrix");
+        out.write(stream_.data(), std::streamsize(stream_.size()));
+    }
+
+    int device() const { return device_; }
+    uint64_t device_bytes() const { return h_ ? ggq_device_bytes(h_.get()) : 0; }
+    const ggq_matrix *raw() const { return h_.get(); }
+
+  protected:
+    typedef int (*loader_fn)(ggq_read_fn, void *, int, ggq_matrix **);
+
+    struct Tap {
+        std::istream *in;
+        std::string *copy;
+    };
+    static size_t read_cb(void *ctx, void *dst, size_t n) {
+        Tap *t = static_cast<Tap *>(ctx);
+        t->in->read(static_cast<char *>(dst), std::streamsize(n));
+        size_t got = size_t(t->in->gcount());
+        t->copy->append(static_cast<const char *>(dst), got);
+        return got;
+    }
+
+    bool load_with(loader_fn fn, std::istream &in) {
+        if (!in.good()) return false;
+        try {
+            std::string bytes;
+            Tap tap{&in, &bytes};
+            ggq_matrix *m = nullptr;
+            if (fn(&read_cb, &tap, device_, &m) != GGQ_OK) return false;
+            h_.reset(m, [](ggq_matrix *p) { ggq_free(p); });
+            stream_.swap(bytes);
+            return true;
+        } catch (...) {
+            return false;
+        }
+    }
+
+    const ggq_matrix *handle() const {
+        if (!h_) throw std::runtime_error("ggq: matrix is not loaded");
+        return h_.get();
+    }
+    static void check(int rc) {
+        if (rc != GGQ_OK) throw std::runtime_error(std::string("ggq: ") + ggq_last_error());
+    }
+
+    int device_;
+    std::shared_ptr<ggq_matrix> h_;   // copies share the immutable device image
+    std::string stream_;
+};
+
+class GpuBRWT final : public GpuMatrixBase {
+  public:
+    using GpuMatrixBase::GpuMatrixBase;
+    bool load(std::istream &in) override { return load_with(&ggq_brwt_load, in); }
+    // BRWT stats (BRWT.hpp:44-49)
+    uint64_t num_nodes() const { return h_ ? ggq_num_nodes(h_.get()) : 0; }
+    uint64_t total_column_size() const { return h_ ? ggq_total_column_size(h_.get()) : 0; }
+};
+
+class GpuColMajor final : public GpuMatrixBase {
+  public:
+    using GpuMatrixBase::GpuMatrixBase;
+    bool load(std::istream &in) override { return load_with(&ggq_colmajor_load, in); }
+};
+
+}  // namespace ggq
+
+#endif  // GGQ_GPU_MATRIX_HPP_

@@ -1,0 +1,143 @@
+// TEST INFRASTRUCTURE — the reference-side drop-in check, in C++, at the BinaryMatrix boundary.
+//
+// Compiled INSIDE the reference's include path (oracle/Makefile target `adapter_test`), linked against
+// the unmodified reference objects and libggq.so.  For a grid of matrices it builds the reference BRWT /
+// ColMajorCompressed, serializes it with the reference's own serialize(), loads the stream into
+// ggq::GpuBRWT / ggq::GpuColMajor (include/ggq/gpu_matrix.hpp) through BinaryMatrix::load(std::istream&),
+// and requires IDENTICAL answers through the BinaryMatrix interface — the same triple check as the
+// reference's test_brwt() helper (tests/test_BRWT.cpp:92-150), but with vector equality (order included),
+// plus serialize() byte equality and the batched extensions.
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+#include <sstream>
+
+#include "BRWT.hpp"
+#include "BRWT_builders.hpp"
+#include "column_major.hpp"
+#include "ggq/gpu_matrix.hpp"
+
+static int g_fail = 0;
+#define REQUIRE(cond)                                                                   \
+    do {                                                                                \
+        if (!(cond)) {                                                                  \
+            std::fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond);      \
+            ++g_fail;                                                                   \
+            return;                                                                     \
+        }                                                                               \
+    } while (0)
+
+typedef std::vector<std::unique_ptr<bit_vector>> Columns;
+
+static Columns make_columns(uint64_t n, uint64_t m, double d, unsigned seed) {
+    std::mt19937 gen(seed);
+    std::bernoulli_distribution bern(d);
+    Columns cols;
+    for (uint64_t j = 0; j < m; ++j) {
+        sdsl::bit_vector bv(n, 0);
+        for (uint64_t i = 0; i < n; ++i) bv[i] = bern(gen);
+        cols.emplace_back(new bit_vector_stat(std::move(bv)));
+    }
+    return cols;
+}
+
+static void compare(const BinaryMatrix &ref, const ggq::GpuMatrixBase &gpu, const std::string &stream) {
+    REQUIRE(ref.num_rows() == gpu.num_rows());
+    REQUIRE(ref.num_columns() == gpu.num_columns());
+    REQUIRE(ref.num_relations() == gpu.num_relations());
+    const uint64_t n = ref.num_rows(), m = ref.num_columns();
+    std::vector<uint64_t> rows(n);
+    for (uint64_t i = 0; i < n; ++i) rows[i] = i;
+    auto batched = gpu.get_rows(rows);
+    auto sliced = gpu.slice_rows(rows);
+    size_t sp = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        auto e = ref.get_row(i);
+        REQUIRE(batched[i] == e);
+        if (i % 17 == 0) REQUIRE(gpu.get_row(i) == e);
+        for (auto c : e) REQUIRE(sliced[sp++] == c);
+        REQUIRE(sliced[sp++] == ~uint64_t(0));
+    }
+    REQUIRE(sp == sliced.size());
+    for (uint64_t j = 0; j < m; ++j) {
+        REQUIRE(gpu.get_column(j) == ref.get_column(j));
+        auto hc = gpu.has_column(rows, j);
+        for (uint64_t i = 0; i < n; i += 7) {
+            REQUIRE(hc[i] == ref.get(i, j));
+            REQUIRE(gpu.get(i, j) == ref.get(i, j));
+        }
+    }
+    std::ostringstream out;
+    gpu.serialize(out);
+    REQUIRE(out.str() == stream);
+}
+
+static void check_brwt(Columns &&cols, int arity, bool relax) {
+    BRWT ref = BRWTBottomUpBuilder::build(std::move(cols), BRWTBottomUpBuilder::get_basic_partitioner(arity));
+    if (relax) BRWTOptimizer::relax(&ref, 7);
+    std::ostringstream out;
+    ref.serialize(out);
+    std::string stream = out.str();
+    std::istringstream in(stream + "tail");
+    ggq::GpuBRWT gpu;
+    REQUIRE(gpu.load(in));
+    REQUIRE(size_t(in.tellg()) == stream.size());   // load() consumed exactly the matrix
+    REQUIRE(gpu.num_nodes() == ref.num_nodes());
+    REQUIRE(gpu.total_column_size() == ref.total_column_size());
+    compare(ref, gpu, stream);
+    ggq::GpuBRWT copy = gpu;  // copies share the device image (BRWT is copyable, BRWT.hpp:27-31)
+    REQUIRE(copy.get_column(0) == ref.get_column(0));
+}
+
+static void check_colmajor(uint64_t n, uint64_t m, double d, unsigned seed) {
+    std::mt19937 gen(seed);
+    std::bernoulli_distribution bern(d);
+    std::vector<std::unique_ptr<bit_vector_sd>> cols;
+    for (uint64_t j = 0; j < m; ++j) {
+        sdsl::bit_vector bv(n, 0);
+        for (uint64_t i = 0; i < n; ++i) bv[i] = bern(gen);
+        cols.emplace_back(new bit_vector_sd(bv));
+    }
+    ColMajorCompressed ref(std::move(cols));
+    std::ostringstream out;
+    ref.serialize(out);
+    std::string stream = out.str();
+    std::istringstream in(stream);
+    ggq::GpuColMajor gpu;
+    REQUIRE(gpu.load(in));
+    compare(ref, gpu, stream);
+}
+
+static void check_bad_streams() {
+    ggq::GpuBRWT gpu;
+    std::istringstream empty("");
+    REQUIRE(!gpu.load(empty));
+    std::istringstream junk(std::string(64, '\xff'));
+    REQUIRE(!gpu.load(junk));
+    bool threw = false;
+    try { gpu.get_row(0); } catch (const std::runtime_error &) { threw = true; }
+    REQUIRE(threw);
+}
+
+int main() {
+    int n_dev = 0;
+    if (ggq_device_count(&n_dev) != GGQ_OK || n_dev < 1) {
+        std::fprintf(stderr, "adapter_test: no CUDA device (the engine has no CPU fallback)\n");
+        return 2;
+    }
+    for (uint64_t m : {1, 2, 5, 19, 64, 100})
+        for (uint64_t n : {1, 19, 500})
+            for (double d : {0.0, 0.1, 1.0})
+                check_brwt(make_columns(n, m, d, unsigned(n * 131 + m)), m % 3 + 2, m > 5);
+    check_brwt(make_columns(3000, 300, 0.02, 7), 4, true);
+    check_colmajor(500, 20, 0.1, 1);
+    check_colmajor(500, 20, 0.9, 2);
+    check_colmajor(64, 3, 0.0, 3);
+    check_bad_streams();
+    if (g_fail) {
+        std::fprintf(stderr, "adapter_test: %d check(s) FAILED\n", g_fail);
+        return 1;
+    }
+    std::printf("adapter_test: all checks passed\n");
+    return 0;
+}
