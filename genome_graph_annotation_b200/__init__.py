@@ -62,6 +62,7 @@ def lib():
         "ggq_total_column_size": (C.c_uint64, [vp]),
         "ggq_device_bytes": (C.c_uint64, [vp]),
         "ggq_last_probe_count": (C.c_uint64, [vp]),
+        "ggq_set_option": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
         "ggq_get_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(vp)]),
         "ggq_rows_offsets": (u64p, [vp]),
         "ggq_rows_columns": (u64p, [vp]),
@@ -217,6 +218,10 @@ class GpuMatrix:
     total_column_size = property(lambda s: lib().ggq_total_column_size(s._h))
     device_bytes = property(lambda s: lib().ggq_device_bytes(s._h))
     last_probe_count = property(lambda s: lib().ggq_last_probe_count(s._h))
+
+    def set_option(self, name, value):
+        """Tuning knob of the row-query path (ggq_set_option): rows_per_warp, sort_bits, sort_min_rows."""
+        _check(lib().ggq_set_option(self._h, name.encode(), int(value)))
 
     # -- queries (host buffers) ---------------------------------------------------------------
     def get_rows_csr(self, rows):

@@ -14,6 +14,7 @@ typedef unsigned int u32;
 struct Img {
     const uint4 *slots;
     const u64 *group_hot;
+    const uint4 *group_rec;   // [g*2 + half] = { hot.lo, hot.hi, lane_info[4g+2*half], lane_info[4g+2*half+1] }
     const u64 *group_nblocks;
     const u32 *lane_info;
     const u32 *lane_aux;
@@ -38,6 +39,34 @@ __device__ __forceinline__ uint4 ld_slot(const uint4 *p) {
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                  : "l"(p));
     return r;
+}
+
+// Streaming 32-byte read of two adjacent slots (one DRAM sector) — the 256-bit load of sm_100.
+// `p` must be 32-byte aligned.  GGQ_L2_64B adds the .L2::64B qualifier: without it every L2 miss
+// fetches 128 bytes from DRAM (measured: profiles/r01/mb_gather_ncu_dram_bytes.csv).
+#ifndef GGQ_L2_64B
+#define GGQ_L2_64B 1
+#endif
+__device__ __forceinline__ void ld_slot2(const uint4 *p, uint4 &a, uint4 &b) {
+#if GGQ_L2_64B
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+#else
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+#endif
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
+
+// r / 96 and r % 96.  Fast path (r < 2^37, i.e. every vector shorter than 1.4e11 positions): one 32-bit mulhi.
+__device__ __forceinline__ void div96(u64 r, u64 &blk, u32 &bit) {
+    if (r < (1ull << 37)) {
+        u32 q = __umulhi(u32(r >> 5), 0xAAAAAAABu) >> 1;
+        blk = q;
+        bit = u32(r) - q * kSlotBits;
+    } else {
+        blk = r / kSlotBits;
+        bit = u32(r - blk * kSlotBits);
+    }
 }
 
 // Cached variant for data with spatial reuse inside a warp (sorted select queries, streaming scans).

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/ggq.h"
@@ -121,6 +122,14 @@ void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
 void Matrix::upload_tables(const FlatTree &t) {
     upload_vec(group_hot, t.group_hot);
     upload_vec(group_nblocks, t.group_nblocks);
+    {
+        std::vector<uint4> rec(size_t(t.n_groups()) * 2);
+        for (u32 g = 0; g < t.n_groups(); ++g)
+            for (u32 h = 0; h < 2; ++h)
+                rec[2 * g + h] = make_uint4(u32(t.group_hot[g]), u32(t.group_hot[g] >> 32), t.lane_info[4 * g + 2 * h],
+                                            t.lane_info[4 * g + 2 * h + 1]);
+        upload_vec(group_rec, rec);
+    }
     upload_vec(lane_info, t.lane_info);
     upload_vec(lane_aux, t.lane_aux);
     upload_vec(lane_sb_off, t.lane_sb_off);
@@ -137,6 +146,7 @@ void Matrix::upload_tables(const FlatTree &t) {
 void Matrix::refresh_img() {
     img.slots = slots.p;
     img.group_hot = group_hot.p;
+    img.group_rec = group_rec.p;
     img.group_nblocks = group_nblocks.p;
     img.lane_info = lane_info.p;
     img.lane_aux = lane_aux.p;
@@ -154,6 +164,48 @@ void Matrix::refresh_img() {
     img.multi_leaf = tree.multi_column_leaves;
 }
 
+// Descent kernel configuration: rows per warp batch, stack capacity, grid, query ordering.
+void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
+    // descent kernel configuration
+    bm_words = u32((tree.leaf_col.size() + 31) / 32);
+    if (bm_words == 0) bm_words = 1;
+    int max_smem = 0;
+    CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    // rows per warp batch: as many as fit a ~5.5 KB/warp bitmap budget, at most 16 (kItemTBits)
+    auto env_u32 = [](const char *name, u32 dflt) {
+        const char *v = std::getenv(name);
+        return v && *v ? u32(std::strtoul(v, nullptr, 10)) : dflt;
+    };
+    rb = std::min<u32>(std::max<u32>(rb_request ? rb_request : env_u32("GGQ_RB", 8), 1), kMaxRowsPerWarp);
+    while (rb > 1 && size_t(rb) * bm_words * 4 > 5632) rb >>= 1;
+    for (;;) {
+        u32 worst = simulate_stack(tree, rb, kItemsPerIter) + 8;
+        cap_s = (std::max<u32>(worst, 32) + 1) & ~1u;
+        cap_spill = 0;
+        if (cap_s > 512) { cap_spill = cap_s - 512; cap_s = 512; }   // deep/wide trees: overflow to global memory
+        rows_smem = size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(rb) * bm_words * 4);
+        if (rows_smem <= size_t(max_smem) || rb == 1) break;
+        rb >>= 1;
+    }
+    if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
+    int per_sm = 0;
+    if (cap_spill) {
+        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<true>, kRowsWarps * 32, rows_smem));
+    } else {
+        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<false>, kRowsWarps * 32, rows_smem));
+    }
+    if (per_sm < 1) per_sm = 1;
+    rows_grid = u32(sm_count * per_sm);
+    // query ordering (see K1): sort on the top `sort_bits` bits of the row id
+    row_bits = 1;
+    while (row_bits < 64 && (u64(1) << row_bits) < tree.n_rows) ++row_bits;
+    sort_bits = std::min<u32>(sort_request != ~0u ? sort_request : env_u32("GGQ_SORT_BITS", 16), row_bits);
+    sort_min_n = env_u32("GGQ_SORT_MIN", 4096);
+}
+
 void Matrix::derive_stats() {
     n_nodes = tree.nodes.size();
     total_column_size = 0;
@@ -162,26 +214,7 @@ void Matrix::derive_stats() {
         total_column_size += n.size;
         if (n.children.empty()) num_relations += n.ones * n.cols.size();
     }
-    // descent kernel configuration
-    bm_words = u32((tree.leaf_col.size() + 31) / 32);
-    if (bm_words == 0) bm_words = 1;
-    int max_smem = 0;
-    CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
-    CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
-    // rows per warp batch: as many as fit a ~5 KB/warp bitmap budget, at most 8
-    rb = 8;
-    while (rb > 1 && size_t(rb) * bm_words * 4 > 5 * 1024) rb >>= 1;
-    u32 worst = simulate_stack(tree, rb, kItemsPerIter) + 8;
-    cap_s = std::min<u32>(std::max<u32>(worst, 32), 192);
-    cap_s = (cap_s + 1) & ~1u;
-    cap_spill = worst > cap_s ? worst - cap_s : 0;
-    rows_smem = size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(rb) * bm_words * 4);
-    if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
-    CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
-    int per_sm = 0;
-    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel, kRowsWarps * 32, rows_smem));
-    if (per_sm < 1) per_sm = 1;
-    rows_grid = u32(sm_count * per_sm);
+    configure_rows(0, ~0u);
     device_bytes = slots.bytes() + sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
                    lane_info.bytes() * 3 + lane_sel_off.bytes() * 2 + leaf_col.bytes() + col_path.bytes() + col_path_off.bytes();
 }
@@ -272,6 +305,16 @@ void Workspace::reserve_rows(u64 n) {
     d_row_cnt.alloc(c);
     d_offsets.alloc(c);
     d_bytes8.alloc(c);
+    if (m->kind == Matrix::BRWT && m->sort_bits) {
+        d_iota.alloc(c);
+        d_perm.alloc(c);
+        d_rows_sorted.alloc(c);
+        iota_kernel<<<u32((c + 255) / 256), 256, 0, stream>>>(d_iota.p, c);
+        size_t sneed = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, sneed, d_rows.p, d_rows_sorted.p, d_iota.p, d_perm.p, c, 0, 64, stream);
+        d_sort_tmp.alloc(sneed + 16);
+        sort_tmp_bytes = sneed;
+    }
     size_t need = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, need, d_row_cnt.p, d_offsets.p, c, stream);
     d_cub.alloc(need + 16);
@@ -320,11 +363,25 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         return;
     }
     if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
+    // order the batch by row id (top sort_bits bits): monotone walks through every node vector
+    const u64 *proc_rows = d_rows;
+    const u32 *perm = nullptr;
+    int sort_launches = 0;
+    if (m->sort_bits && n >= m->sort_min_n) {
+        size_t sb = ws->sort_tmp_bytes;
+        int end_bit = int(m->row_bits), begin_bit = int(m->row_bits - m->sort_bits);
+        cub::DeviceRadixSort::SortPairs(ws->d_sort_tmp.p, sb, d_rows, ws->d_rows_sorted.p, ws->d_iota.p, ws->d_perm.p, n,
+                                        begin_bit, end_bit, st);
+        CUDA_CHECK(cudaGetLastError());
+        proc_rows = ws->d_rows_sorted.p;
+        perm = ws->d_perm.p;
+        sort_launches = 1 + (end_bit - begin_bit + 7) / 8;   // cub onesweep: histogram + one kernel per 8-bit digit
+    }
     for (int attempt = 0; attempt < 2; ++attempt) {
         CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
         CUDA_CHECK(cudaMemsetAsync(ws->d_err.p, 0, sizeof(int), st));
         RowsArgs a;
-        a.rows = d_rows; a.n = n;
+        a.rows = proc_rows; a.perm = perm; a.n = n;
         a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
         a.cursor = ws->d_ctrl.p;
         a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
@@ -333,7 +390,8 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         u64 batches = (n + m->rb - 1) / m->rb;
         u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
         CUDA_CHECK(cudaEventRecord(ws->ev0, st));
-        brwt_rows_kernel<<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
+        if (m->cap_spill) brwt_rows_kernel<true><<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
+        else brwt_rows_kernel<false><<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaEventRecord(ws->ev1, st));
         size_t cb = ws->cub_bytes;
@@ -348,7 +406,7 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         ws->last_probes = ws->h_ctrl[2];
         ws->last_touches = ws->h_ctrl[3];
         ws->kernel_timed = true;
-        ws->launches = 3;  // descent + 2 scan kernels
+        ws->launches = 3 + sort_launches;  // descent + 2 scan kernels (+ radix sort)
         if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo (steady state never does)
             ws->d_tmp.alloc(total + total / 8 + 1024);
             continue;
@@ -357,13 +415,12 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         size_t out_bytes = size_t(total) * col_bytes;
         if (ws->d_out.n < out_bytes) ws->d_out.alloc(out_bytes + out_bytes / 8 + 1024);
         if (total) {
-            u64 warps = batches;
-            u32 g = u32((warps * 32 + 255) / 256);
+            u32 g = u32((n * 8 + 255) / 256);
             if (col_bytes == 8)
-                gather_rows_kernel<u64><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n, m->rb,
+                gather_rows_kernel<u64><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
                                                           reinterpret_cast<u64 *>(ws->d_out.p));
             else
-                gather_rows_kernel<u32><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n, m->rb,
+                gather_rows_kernel<u32><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
                                                           reinterpret_cast<u32 *>(ws->d_out.p));
             CUDA_CHECK(cudaGetLastError());
             ws->launches += 1;
@@ -526,6 +583,23 @@ uint64_t ggq_total_column_size(const ggq_matrix *m) { return m->total_column_siz
 uint64_t ggq_device_bytes(const ggq_matrix *m) { return m->device_bytes; }
 uint64_t ggq_last_probe_count(const ggq_matrix *m) { return m->last_probes; }
 
+int ggq_set_option(ggq_matrix *m, const char *name, uint64_t value) {
+    GGQ_TRY
+    if (!m || !name) return fail(GGQ_ERR_ARG, "bad argument");
+    if (m->kind != Matrix::BRWT) return GGQ_OK;
+    std::lock_guard<std::mutex> lk(m->pool_mu);
+    for (Workspace *w : m->pool) delete w;   // scratch sizes depend on the configuration
+    m->pool.clear();
+    CUDA_CHECK(cudaSetDevice(m->device));
+    std::string k(name);
+    if (k == "rows_per_warp") m->configure_rows(u32(value), m->sort_bits);
+    else if (k == "sort_bits") m->configure_rows(m->rb, u32(std::min<uint64_t>(value, 64)));
+    else if (k == "sort_min_rows") m->sort_min_n = value;
+    else return fail(GGQ_ERR_ARG, "unknown option");
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 int ggq_workspace_create(const ggq_matrix *m, ggq_workspace **out) {
     GGQ_TRY
     *out = new ggq_workspace(m);
@@ -604,28 +678,56 @@ void ggq_rows_result_free(ggq_rows_result *r) {
     delete r;
 }
 
+// Large batches are cut into chunks that alternate between two workspaces (streams): while chunk k's CSR
+// travels to the host, chunk k+1 is sorted and descended — the PCIe copy, not the kernel, bounds this call.
+static const u64 kPipelineChunk = u64(1) << 20;
+
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint64_t *cols,
                       uint64_t cols_capacity, uint64_t *n_cols) {
     GGQ_TRY
     if (!m || !offsets || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
-    Workspace *ws = m->acquire();
+    CUDA_CHECK(cudaSetDevice(m->device));
+    Workspace *w[2] = {m->acquire(), nullptr};
     int rc = GGQ_OK;
     try {
-        u64 total = 0;
-        rows_host(m, ws, rows, n, &total);
-        if (n_cols) *n_cols = total;
-        CUDA_CHECK(cudaMemcpyAsync(offsets, ws->d_offsets.p, (n + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
-        if (total > cols_capacity || (total && !cols)) {
-            rc = fail(GGQ_ERR_ARG, "cols_capacity too small");
-        } else if (total) {
-            CUDA_CHECK(cudaMemcpyAsync(cols, ws->d_out.p, total * 8, cudaMemcpyDeviceToHost, ws->stream));
+        if (n > kPipelineChunk) w[1] = m->acquire();
+        u64 base = 0;
+        bool fits = true;
+        int launches = 0;
+        u64 probes = 0, touches = 0;
+        for (u64 r0 = 0, k = 0; r0 < n || k == 0; r0 += kPipelineChunk, ++k) {
+            Workspace *ws = w[1] ? w[k & 1] : w[0];
+            const u64 nc = std::min<u64>(kPipelineChunk, n - r0);
+            ws->reserve_rows(nc);
+            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + r0, nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            u64 total = 0;
+            rows_device(m, ws, ws->d_rows.p, nc, 8, &total);
+            launches += ws->launches; probes += ws->last_probes; touches += ws->last_touches;
+            if (base) {
+                add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
+                CUDA_CHECK(cudaGetLastError());
+                ++launches;
+            }
+            CUDA_CHECK(cudaMemcpyAsync(offsets + r0, ws->d_offsets.p, (nc + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
+            if (base + total > cols_capacity || (total && !cols)) fits = false;
+            if (fits && total)
+                CUDA_CHECK(cudaMemcpyAsync(cols + base, ws->d_out.p, total * 8, cudaMemcpyDeviceToHost, ws->stream));
+            base += total;
+            if (r0 + kPipelineChunk >= n) break;
         }
-        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        for (Workspace *ws : w)
+            if (ws) CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        w[0]->launches = launches; w[0]->last_probes = probes; w[0]->last_touches = touches;
+        m->last_probes = probes;
+        if (n_cols) *n_cols = base;
+        if (!fits) rc = fail(GGQ_ERR_ARG, "cols_capacity too small");
     } catch (...) {
-        m->release(ws);
+        for (Workspace *ws : w)
+            if (ws) { cudaStreamSynchronize(ws->stream); m->release(ws); }
         throw;
     }
-    m->release(ws);
+    for (Workspace *ws : w)
+        if (ws) m->release(ws);
     return rc;
     GGQ_CATCH
 }

@@ -61,6 +61,7 @@ struct Matrix {
     // device image
     DeviceBuf<uint4> slots;
     DeviceBuf<u64> group_hot, group_nblocks, lane_sel_off, lane_ones, sb_base;
+    DeviceBuf<uint4> group_rec;   // per (group, half): hot word + the two children's lane_info (descent kernel)
     DeviceBuf<u32> lane_info, lane_aux, lane_sb_off, sel, leaf_col, col_path_off, col_path;
     Img img{};
 
@@ -71,6 +72,8 @@ struct Matrix {
     // descent kernel configuration
     u32 bm_words = 1, rb = 8, cap_s = 64, cap_spill = 0, rows_grid = 148;
     size_t rows_smem = 0;
+    u32 sort_bits = 0, row_bits = 0;   // query ordering: sort on the top sort_bits of the row_bits-bit row id
+    u64 sort_min_n = 4096;             // batches smaller than this are processed in the caller's order
 
     ColMajorImage *cm = nullptr;  // column-major matrices
 
@@ -83,6 +86,7 @@ struct Matrix {
     void finalize_arena(const FlatTree &t, bool ones_known);
     void refresh_img();
     void derive_stats();
+    void configure_rows(u32 rb_request, u32 sort_request);
     Workspace *acquire() const;
     void release(Workspace *w) const;
 };
@@ -92,7 +96,10 @@ struct Workspace {
     const Matrix *m;
     cudaStream_t stream = nullptr;
     DeviceBuf<u64> d_rows, d_row_tmp_off, d_offsets, d_bytes8, d_ctrl, d_spill;
-    DeviceBuf<u32> d_row_cnt, d_tmp;
+    DeviceBuf<u32> d_row_cnt, d_tmp, d_iota, d_perm;
+    DeviceBuf<u64> d_rows_sorted;
+    DeviceBuf<unsigned char> d_sort_tmp;
+    size_t sort_tmp_bytes = 0;
     DeviceBuf<int> d_err;
     DeviceBuf<unsigned char> d_out, d_cub;
     size_t cub_bytes = 0;

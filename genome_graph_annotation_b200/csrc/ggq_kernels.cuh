@@ -12,7 +12,7 @@
 namespace ggq {
 
 constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
-constexpr int kItemsPerIter = 8;       // work items a warp probes per iteration (4 lanes each)
+constexpr int kItemsPerIter = 16;      // work items a warp probes per iteration (2 lanes each, 2 children per lane)
 
 // ------------------------------------------------------------------------------------------
 // Arena construction
@@ -159,22 +159,26 @@ header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, Chun
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: batched get_row.  One warp owns a batch of RB consecutive query rows and a private LIFO
-// stack of work items (t, group, r) = "probe the sibling group `group` at index r for query t".
-// Per iteration the warp pops up to 8 items; 4 lanes serve one item, lane j reading the 16-byte
-// slot of child j (one coalesced 16/32/64-byte read per item).  A set bit of a leaf child marks the
-// column's DFS rank in the row's bitmap (shared memory); a set bit of an internal child pushes the
-// child's first group with r' = rank1(r) - 1.  When the stack drains, the bitmaps are enumerated in
-// rank order, which IS the reference's output order (DFS over child_nodes_, BRWT.cpp:45-50).
+// K1: batched get_row.  The engine first orders the batch by row id (radix sort of (row, query index)
+// pairs): rank1 is monotone, so sorted rows walk EVERY node vector front to back — TLB- and DRAM-page-local
+// instead of 33 random pages per row — and results are written back under the caller's query index.
+// One warp owns a batch of `rb` consecutive (sorted) rows and a private LIFO stack of work items
+// (t, group, r) = "probe the sibling group `group` at index r for query t".  Per iteration the warp pops up
+// to 16 items; 2 lanes serve one item, each reading with ONE 256-bit load the 32-byte sector that holds the
+// slots of two children (one coalesced 64-byte block per item).  A set bit of a leaf child marks the column's
+// DFS rank in the row's bitmap (shared memory); a set bit of an internal child pushes the child's first group
+// with r' = rank1(r) - 1.  When the stack drains, the bitmaps are enumerated in rank order, which IS the
+// reference's output order (DFS over child_nodes_, BRWT.cpp:45-50).
 // ------------------------------------------------------------------------------------------
 struct RowsArgs {
-    const u64 *rows;          // query row ids
+    const u64 *rows;          // query row ids in PROCESSING order (sorted by the engine, or the caller's order)
+    const u32 *perm;          // processing position -> caller's query index (null: identity)
     u64 n;                    // number of queries
     u32 *tmp_cols;            // unordered chunk arena
     u64 tmp_cap;
     u64 *cursor;              // [0] chunk cursor, [1] batch ticket, [2] probe counter, [3] (node,row) touches
-    u64 *row_tmp_off;         // per query: start in tmp_cols
-    u32 *row_cnt;             // per query: number of columns
+    u64 *row_tmp_off;         // per query (caller's index): start in tmp_cols
+    u32 *row_cnt;             // per query (caller's index): number of columns
     u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
     u32 cap_s, cap_spill;     // shared / global stack capacity per warp
     u32 bm_words;             // bitmap words per row
@@ -182,15 +186,42 @@ struct RowsArgs {
     int *err;
 };
 
+// Stack access.  SPILL = false: the shared-memory stack is provably large enough (simulate_stack), no checks.
+template <bool SPILL>
 __device__ __forceinline__ u64 stk_get(const u64 *s_stack, const u64 *spill, u32 cap_s, u32 i) {
+    if (!SPILL) return s_stack[i];
     return i < cap_s ? s_stack[i] : spill[i - cap_s];
 }
+template <bool SPILL>
 __device__ __forceinline__ void stk_set(u64 *s_stack, u64 *spill, u32 cap_s, u32 cap_total, u32 i, u64 v, int *err) {
+    if (!SPILL) { s_stack[i] = v; return; }
     if (i < cap_s) s_stack[i] = v;
     else if (i < cap_total) spill[i - cap_s] = v;
     else *err = 1;
 }
 
+// One child of a probed group: bit test; a set leaf bit marks the row's bitmap, a set internal bit yields the
+// work item of the child's first group with r' = rank1(r) - 1 (BRWT.cpp:43-50).
+__device__ __forceinline__ bool visit_child(const Img &img, const uint4 &s, u32 bit, u64 blk, u32 li, u32 info,
+                                            bool multi_sb, u32 t, u32 *s_bm_row, u64 *child_item) {
+    if (!slot_test(s, bit)) return false;
+    if (info & kLeafFlag) {
+        u32 rank = info & ~kLeafFlag;
+        if (!img.multi_leaf) {
+            atomicOr(s_bm_row + (rank >> 5), 1u << (rank & 31));
+        } else {
+            u32 ncol = __ldg(img.lane_aux + li);
+            for (u32 k = 0; k < ncol; ++k, ++rank) atomicOr(s_bm_row + (rank >> 5), 1u << (rank & 31));
+        }
+        return false;
+    }
+    u64 ones = u64(s.x) + slot_rank_before(s, bit);
+    if (multi_sb) ones += img.sb_base[img.lane_sb_off[li] + (blk >> kSuperShift)];   // entry 0 of a lane is 0
+    *child_item = (ones << kItemRShift) | (u64(t) << kItemGroupBits) | info;
+    return true;
+}
+
+template <bool SPILL>
 __global__ void __launch_bounds__(kRowsWarps * 32)
 brwt_rows_kernel(Img img, RowsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -198,77 +229,76 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     const u32 lt_mask = (1u << lane) - 1u;
     u64 *s_stack = reinterpret_cast<u64 *>(smem_raw) + size_t(warp) * a.cap_s;
     u32 *s_bm = reinterpret_cast<u32 *>(smem_raw + size_t(kRowsWarps) * a.cap_s * 8) + size_t(warp) * a.rb * a.bm_words;
-    u64 *spill = a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill;
+    u64 *spill = SPILL ? a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill : nullptr;
     const u32 cap_total = a.cap_s + a.cap_spill;
     const u32 bm_total = a.rb * a.bm_words;
-    u64 probes = 0;
+    const u32 idx = lane >> 1, half = lane & 1;   // 2 lanes serve one item; lane `half` owns children 2*half, 2*half+1
+    u32 probes = 0;    // lane 0
     u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
 
     for (;;) {
         u64 batch = 0;
         if (lane == 0) batch = atomicAdd(a.cursor + 1, 1ull);
         batch = __shfl_sync(0xffffffffu, batch, 0);
-        u64 row0 = batch * a.rb;
+        const u64 row0 = batch * a.rb;
         if (row0 >= a.n) break;
-        u32 nr = u32(min(u64(a.rb), a.n - row0));
+        const u32 nr = u32(min(u64(a.rb), a.n - row0));
 
         for (u32 i = lane; i < bm_total; i += 32) s_bm[i] = 0;
         // seed the stack with the root probes of the valid rows
         u64 r = 0;
         bool valid = false;
         if (lane < nr) { r = a.rows[row0 + lane]; valid = r < img.n_rows; }
-        u32 vmask = __ballot_sync(0xffffffffu, valid);
+        const u32 vmask = __ballot_sync(0xffffffffu, valid);
         if (valid) s_stack[__popc(vmask & lt_mask)] = (r << kItemRShift) | (u64(lane) << kItemGroupBits);
         u32 top = __popc(vmask);
         __syncwarp();
 
         while (top > 0) {
             const u32 c = min(top, u32(kItemsPerIter));
-            const u32 idx = lane >> 2, j = lane & 3;
             const bool active = idx < c;
             u64 item = 0;
-            if (active) item = stk_get(s_stack, spill, a.cap_s, top - 1 - idx);
+            if (active) item = stk_get<SPILL>(s_stack, spill, a.cap_s, top - 1 - idx);
             __syncwarp();
             const u32 g = u32(item) & (kMaxGroups - 1);
             const u32 t = u32(item >> kItemGroupBits) & (kMaxRowsPerWarp - 1);
             const u64 rr = item >> kItemRShift;
-            u64 hot = 0;
-            if (active) hot = __ldg(img.group_hot + g);
-            const u32 cnt = u32(hot >> kGhCntShift) & 7u;
-            const bool push_cont = active && j == 0 && ((hot >> kGhMoreShift) & 1ull);
-            bool push_child = false;
-            u64 child_item = 0;
-            if (active && j < cnt) {
-                const u64 blk = rr / kSlotBits;
-                const u32 bit = u32(rr - blk * kSlotBits);
-                const uint4 s = ld_slot(slot_addr(img, hot, blk, j));
-                if (slot_test(s, bit)) {
-                    const u32 li = g * 4 + j;
-                    const u32 info = __ldg(img.lane_info + li);
-                    if (info & kLeafFlag) {
-                        u32 rank = info & ~kLeafFlag;
-                        u32 ncol = img.multi_leaf ? __ldg(img.lane_aux + li) : 1u;
-                        for (u32 k = 0; k < ncol; ++k, ++rank)
-                            atomicOr(s_bm + t * a.bm_words + (rank >> 5), 1u << (rank & 31));
-                    } else {
-                        u64 ones = lane_rank_base(img, li, blk, s) + slot_rank_before(s, bit);
-                        child_item = (ones << kItemRShift) | (u64(t) << kItemGroupBits) | info;
-                        push_child = true;
-                    }
+            bool push_cont = false, push0 = false, push1 = false;
+            u64 item0 = 0, item1 = 0;
+            if (active) {
+                const uint4 rec = __ldg(img.group_rec + 2 * g + half);
+                const u32 sl = (rec.y >> (kGhStrideShift - 32)) & 3u;
+                const u32 cnt = (rec.y >> (kGhCntShift - 32)) & 7u;
+                push_cont = half == 0 && ((rec.y >> (kGhMoreShift - 32)) & 1u);
+                const bool multi_sb = (rec.y >> (kGhSuperShift - 32)) & 1u;
+                if (half == 0) touches += cnt;
+                if (2 * half < cnt) {
+                    u64 blk; u32 bit;
+                    div96(rr, blk, bit);
+                    const u64 base = (u64(rec.y & 0xffu) << 32) | rec.x;
+                    const u64 si = base + (blk << sl) + 2 * half;   // slot of child 2*half
+                    uint4 s0, s1;
+                    ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
+                    if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
+                    u32 *bm_row = s_bm + t * a.bm_words;
+                    push0 = visit_child(img, s0, bit, blk, g * 4 + 2 * half, rec.z, multi_sb, t, bm_row, &item0);
+                    if (2 * half + 1 < cnt)
+                        push1 = visit_child(img, s1, bit, blk, g * 4 + 2 * half + 1, rec.w, multi_sb, t, bm_row, &item1);
                 }
             }
             const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
-            const u32 child_mask = __ballot_sync(0xffffffffu, push_child);
-            const u32 new_top = top - c;
-            const u32 nc = __popc(cont_mask);
+            const u32 m0 = __ballot_sync(0xffffffffu, push0);
+            const u32 m1 = __ballot_sync(0xffffffffu, push1);
+            u32 pos = top - c;
             if (push_cont)
-                stk_set(s_stack, spill, a.cap_s, cap_total, new_top + __popc(cont_mask & lt_mask), item + 1, a.err);
-            if (push_child)
-                stk_set(s_stack, spill, a.cap_s, cap_total, new_top + nc + __popc(child_mask & lt_mask), child_item, a.err);
-            top = new_top + nc + __popc(child_mask);
-            if (top > cap_total) top = cap_total;  // overflow already flagged in *err
-            if (lane == 0) probes += c;
-            if (active && j == 0) touches += cnt;
+                stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
+            pos += __popc(cont_mask);
+            if (push0) stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(m0 & lt_mask), item0, a.err);
+            pos += __popc(m0);
+            if (push1) stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(m1 & lt_mask), item1, a.err);
+            top = pos + __popc(m1);
+            if (SPILL && top > cap_total) top = cap_total;  // overflow already flagged in *err
+            probes += c;
             __syncwarp();
         }
 
@@ -278,7 +308,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         for (u32 t = 0; t < nr; ++t) {
             u32 c = 0;
             for (u32 w = lane; w < a.bm_words; w += 32) c += __popc(s_bm[t * a.bm_words + w]);
-            for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            c = __reduce_add_sync(0xffffffffu, c);
             if (lane == t) my_cnt = c;
             total += c;
         }
@@ -293,17 +323,26 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         }
         pre -= my_cnt;
         if (lane < nr) {
-            a.row_tmp_off[row0 + lane] = base + pre;
-            a.row_cnt[row0 + lane] = my_cnt;
+            const u64 q = a.perm ? u64(a.perm[row0 + lane]) : row0 + lane;
+            a.row_tmp_off[q] = base + pre;
+            a.row_cnt[q] = my_cnt;
         }
         const bool fits = base + total <= a.tmp_cap;
-        if (fits) {
+        if (fits && total) {
             for (u32 t = 0; t < nr; ++t) {
                 u64 pos = base + __shfl_sync(0xffffffffu, pre, t);
+                if (__shfl_sync(0xffffffffu, my_cnt, t) == 0) continue;
                 for (u32 w0 = 0; w0 < a.bm_words; w0 += 32) {
                     u32 w = w0 + lane;
                     u32 bits = w < a.bm_words ? s_bm[t * a.bm_words + w] : 0u;
-                    u32 c = __popc(bits);
+                    if (!__any_sync(0xffffffffu, bits != 0)) continue;
+                    const u32 c = __popc(bits);
+                    if (!__any_sync(0xffffffffu, c > 1)) {   // common case: at most one id per word
+                        const u32 nz = __ballot_sync(0xffffffffu, c != 0);
+                        if (c) a.tmp_cols[pos + __popc(nz & lt_mask)] = __ldg(img.leaf_col + w * 32 + __ffs(bits) - 1);
+                        pos += __popc(nz);
+                        continue;
+                    }
                     u32 inc = c;
                     for (int o = 1; o < 32; o <<= 1) {
                         u32 v = __shfl_up_sync(0xffffffffu, inc, o);
@@ -321,24 +360,33 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         }
         __syncwarp();
     }
-    if (lane == 0 && probes) atomicAdd(a.cursor + 2, probes);
+    if (lane == 0 && probes) atomicAdd(a.cursor + 2, u64(probes));
     touches = __reduce_add_sync(0xffffffffu, touches);
     if (lane == 0 && touches) atomicAdd(a.cursor + 3, u64(touches));
 }
 
-// One warp per batch of `rb` rows: the batch is contiguous both in the chunk arena and in the CSR.
+// CSR assembly in the caller's query order: 8 lanes copy one row from its chunk in the arena.
 template <typename OutT>
 __global__ void gather_rows_kernel(const u32 *tmp_cols, const u64 *row_tmp_off, const u64 *offsets,
-                                   u64 n, u32 rb, OutT *out) {
-    u64 warp = (u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-    u32 lane = threadIdx.x & 31;
-    u64 row0 = warp * rb;
-    if (row0 >= n) return;
-    u64 row1 = min(n, row0 + rb);
-    u64 dst0 = offsets[row0], len = offsets[row1] - dst0;
-    if (!len) return;
-    u64 src0 = row_tmp_off[row0];
-    for (u64 i = lane; i < len; i += 32) out[dst0 + i] = OutT(tmp_cols[src0 + i]);
+                                   u64 n, OutT *out) {
+    const u64 q = (u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 3;
+    const u32 sub = threadIdx.x & 7;
+    if (q >= n) return;
+    const u64 dst0 = offsets[q], len = offsets[q + 1] - dst0;
+    const u64 src0 = row_tmp_off[q];
+    for (u64 i = sub; i < len; i += 8) out[dst0 + i] = OutT(tmp_cols[src0 + i]);
+}
+
+// iota for the (row id, query index) sort
+__global__ void iota_kernel(u32 *p, u64 n) {
+    u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = u32(i);
+}
+
+// chunk-local CSR offsets -> global offsets (pipelined host API)
+__global__ void add_base_kernel(u64 *p, u64 n, u64 base) {
+    u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) p[i] += base;
 }
 
 // slice_rows: CSR -> rows separated by UINT64_MAX

@@ -19,10 +19,11 @@ constexpr uint32_t kSelectShift = 10;       // one select sample per 1024 ones
 constexpr uint32_t kLeafFlag = 0x80000000u;
 constexpr uint32_t kChunkBlocks = 256;      // blocks per scan chunk when rank headers are built
 
-// group_hot[g] (u64): slot base (40 bits) | stride_log2 (2) | cnt (3) | more (1)
+// group_hot[g] (u64): slot base (40 bits) | stride_log2 (2) | cnt (3) | more (1) | multi-superblock (1)
 constexpr int kGhStrideShift = 40;
 constexpr int kGhCntShift = 42;
 constexpr int kGhMoreShift = 45;
+constexpr int kGhSuperShift = 46;   // some lane of the group spans more than one superblock (rank needs sb_base)
 constexpr uint64_t kGhBaseMask = (uint64_t(1) << 40) - 1;
 
 inline uint64_t pack_group_hot(uint64_t base, uint32_t stride_log2, uint32_t cnt, uint32_t more) {

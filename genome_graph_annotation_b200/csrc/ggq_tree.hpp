@@ -246,7 +246,7 @@ inline void assign_geometry(FlatTree *t) {
         if (len >= kMaxRows) throw ParseError("vector longer than the engine supports");
         uint64_t nb = len / kSlotBits + 1;  // + sentinel block
         slot = (slot + 3) & ~uint64_t(3);   // 64-byte alignment of every group
-        t->group_hot[g] = pack_group_hot(slot, sl, cnt, more);
+        t->group_hot[g] = pack_group_hot(slot, sl, cnt, more) | (uint64_t(((nb - 1) >> kSuperShift) != 0) << kGhSuperShift);
         t->group_nblocks[g] = nb;
         slot += nb << sl;
         uint64_t n_sb = ((nb - 1) >> kSuperShift) + 1;
@@ -272,23 +272,24 @@ inline void assign_geometry(FlatTree *t) {
 inline uint32_t simulate_stack(const FlatTree &t, uint32_t rows_per_warp, uint32_t items_per_iter) {
     std::vector<uint32_t> st(rows_per_warp, 0);  // group ids; all rows start at the root group
     size_t max_top = st.size();
-    std::vector<uint32_t> conts, kids;
+    std::vector<uint32_t> conts, kids0, kids1;
     while (!st.empty()) {
         size_t c = std::min<size_t>(st.size(), items_per_iter);
-        conts.clear(); kids.clear();
+        conts.clear(); kids0.clear(); kids1.clear();
         for (size_t i = 0; i < c; ++i) {
             uint32_t g = st[st.size() - 1 - i];
             uint64_t hot = t.group_hot[g];
             uint32_t cnt = uint32_t(hot >> kGhCntShift) & 7;
             if ((hot >> kGhMoreShift) & 1) conts.push_back(g + 1);
-            for (uint32_t k = 0; k < cnt; ++k) {
+            for (uint32_t k = 0; k < cnt; ++k) {   // lane `half` pushes child 2*half first, then 2*half+1
                 uint32_t info = t.lane_info[g * 4 + k];
-                if (!(info & kLeafFlag)) kids.push_back(info);
+                if (!(info & kLeafFlag)) ((k & 1) ? kids1 : kids0).push_back(info);
             }
         }
         st.resize(st.size() - c);
         st.insert(st.end(), conts.begin(), conts.end());
-        st.insert(st.end(), kids.begin(), kids.end());
+        st.insert(st.end(), kids0.begin(), kids0.end());
+        st.insert(st.end(), kids1.begin(), kids1.end());
         max_top = std::max(max_top, st.size());
     }
     return uint32_t(max_top);

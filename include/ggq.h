@@ -85,6 +85,12 @@ uint64_t ggq_device_bytes(const ggq_matrix *m);
  * probes (one 16/32/64-byte block read each).  For roofline accounting. */
 uint64_t ggq_last_probe_count(const ggq_matrix *m);
 
+/* Tuning knobs of the row-query path (defaults are chosen per matrix at load time; DESIGN.md "K1").  Call
+ * before creating workspaces on the matrix.  Names: "rows_per_warp" (1..16), "sort_bits" (0 = process queries in
+ * the caller's order; k = order each batch by the top k bits of the row id), "sort_min_rows" (smaller batches are
+ * never reordered).  Results never depend on these. */
+int ggq_set_option(ggq_matrix *m, const char *name, uint64_t value);
+
 /* ------------------------------------------------------------------ row queries -------------- */
 
 /* get_rows(R)[t] == BRWT::get_row(R[t]) (BRWT.cpp:26-53) / ColMajorCompressed::get_row
@@ -98,7 +104,10 @@ uint64_t ggq_rows_count(const ggq_rows_result *r);
 void ggq_rows_result_free(ggq_rows_result *r);
 
 /* Same query, caller-provided host output (cols_capacity entries).  *n_cols receives the number of
- * column ids; if it exceeds cols_capacity nothing is written to cols and GGQ_ERR_ARG is returned. */
+ * column ids; if it exceeds cols_capacity GGQ_ERR_ARG is returned (offsets are complete, the contents of
+ * cols are unspecified).  Batches above 2^20 rows are pipelined in chunks over two streams so that the
+ * device->host copy of one chunk overlaps the descent of the next; page-locked (pinned) caller buffers are
+ * needed for that overlap, pageable ones work but serialise. */
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
                       uint64_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
 

@@ -58,3 +58,63 @@ def test_synth_kingsford_shaped_sample(ggq, orc):
         assert np.array_equal(cols[off[t]:off[t + 1]], e), t
     assert gm.num_nodes == 3538  # SURVEY §6 probe: arity-4 basic tree over 2652 columns
     gm.close()
+
+
+def test_row_query_options_do_not_change_results(ggq, orc):
+    """The engine may reorder a batch internally (radix sort on the top bits of the row id) and pick any
+    rows-per-warp tile; the CSR must stay in the caller's order and bit-identical.  Duplicates and
+    out-of-range ids (empty rows, ggq.h) included."""
+    n, m, d = 30_000, 300, 0.02
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=3)
+    thr = ggq.density_threshold(d)
+    rng = np.random.default_rng(11)
+    rows = rng.integers(0, n, 20_000).astype(np.uint64)
+    rows[::97] = rows[5]                      # duplicates
+    rows[::1013] = np.uint64(n + 12345)       # out of range
+    rows[7] = np.uint64(2**63)
+    base = None
+    try:
+        for sort_bits in (0, 5, 64):
+            for rb in (1, 4, 16):
+                gm.set_option("sort_min_rows", 0)
+                gm.set_option("sort_bits", sort_bits)
+                gm.set_option("rows_per_warp", rb)
+                off, cols = gm.get_rows_csr(rows)
+                if base is None:
+                    base = (off, cols)
+                    for t in range(0, rows.size, 7):
+                        r = int(rows[t])
+                        e = orc.synth_row(m, thr, 42, r) if r < n else np.zeros(0, np.uint64)
+                        assert np.array_equal(cols[off[t]:off[t + 1]], e), t
+                else:
+                    assert np.array_equal(off, base[0]) and np.array_equal(cols, base[1]), (sort_bits, rb)
+                sl = gm.slice_rows(rows[:5000])
+                assert sl.size == int(off[5000]) + 5000
+    finally:
+        gm.close()
+
+
+def test_pipelined_host_api_matches_single_shot(ggq):
+    """ggq_get_rows_into cuts batches above 2^20 rows into chunks on two streams; the CSR must equal the
+    concatenation of the unpipelined answers (ggq_get_rows), global offsets included."""
+    n, m, d = 60_000, 120, 0.03
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=7, arity=4)
+    try:
+        rng = np.random.default_rng(3)
+        rows = rng.integers(0, n, (1 << 21) + 12_345).astype(np.uint64)
+        off = np.empty(rows.size + 1, np.uint64)
+        cols = np.empty(int(rows.size * m * d * 1.3) + 1024, np.uint64)
+        total = gm.get_rows_into(rows, off, cols)
+        assert off[0] == 0 and off[-1] == total
+        assert np.all(np.diff(off.astype(np.int64)) >= 0)
+        for lo in range(0, rows.size, 700_000):
+            hi = min(rows.size, lo + 700_000)
+            eo, ec = gm.get_rows_csr(rows[lo:hi])
+            assert np.array_equal(off[lo:hi + 1] - off[lo], eo)
+            assert np.array_equal(cols[int(off[lo]):int(off[hi])], ec)
+        # capacity too small: error, but the total is still reported
+        small = np.empty(10, np.uint64)
+        with pytest.raises(ggq.GgqError):
+            gm.get_rows_into(rows, off, small)
+    finally:
+        gm.close()
