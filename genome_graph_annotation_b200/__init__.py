@@ -53,6 +53,16 @@ def lib():
         "ggq_colmajor_load_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.POINTER(vp)]),
         "ggq_brwt_synthesize": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(vp)]),
         "ggq_free": (None, [vp]),
+        "ggq_brwt_load_shard": (C.c_int, [READ_FN, vp, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
+        "ggq_brwt_load_shard_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
+        "ggq_brwt_synthesize_shard": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
+        "ggq_brwt_shard_plan_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+        "ggq_shard_info": (C.c_int, [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), u8p]),
+        "ggq_merge_shards_device": (C.c_int, [vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
+        "ggq_comm_unique_id": (C.c_int, [u8p]),
+        "ggq_comm_init": (C.c_int, [u8p, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+        "ggq_comm_free": (None, [vp]),
+        "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
         "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
         "ggq_num_rows": (C.c_uint64, [vp]),
@@ -140,6 +150,38 @@ def density_threshold(d):
 SEED_MUL = 0x9E3779B97F4A7C15
 
 
+def shard_plan(data, n_shards):
+    """Host-only: (col_owner[num_columns], cut_depth) of the column-sharding plan for a serialized BRWT."""
+    st = inspect_brwt(data)
+    owner = np.zeros(max(int(st["num_columns"]), 1), np.uint32)
+    cut = C.c_uint32()
+    _check(lib().ggq_brwt_shard_plan_buffer(data, len(data), n_shards, owner.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                            C.byref(cut)))
+    return owner[:int(st["num_columns"])], cut.value
+
+
+class Comm:
+    """NCCL communicator over the shards of one matrix (ggq_comm_*).  `id_bytes`: 128 bytes made by rank 0 with
+    Comm.unique_id() and shipped to the other ranks (e.g. torch.distributed.broadcast_object_list)."""
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)()
+        _check(lib().ggq_comm_unique_id(buf))
+        return bytes(buf)
+
+    def __init__(self, id_bytes, rank, n_ranks, device):
+        buf = (C.c_uint8 * 128).from_buffer_copy(id_bytes)
+        h = C.c_void_p()
+        _check(lib().ggq_comm_init(buf, rank, n_ranks, device, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if self._h:
+            lib().ggq_comm_free(self._h)
+            self._h = None
+
+
 def inspect_brwt(data):
     """Host-only parse + flatten of a serialized BRWT (no GPU needed) -> dict of stats."""
     stats = (C.c_uint64 * 8)()
@@ -180,6 +222,32 @@ class GpuMatrix:
         m = cls(h.value, "brwt")
         m.consumed = used.value
         return m
+
+    @classmethod
+    def load_brwt_shard(cls, data, shard, n_shards, device=0):
+        """Column shard `shard` of `n_shards` of a serialized BRWT (ggq_brwt_load_shard_buffer)."""
+        h = C.c_void_p()
+        used = C.c_size_t()
+        _check(lib().ggq_brwt_load_shard_buffer(data, len(data), C.byref(used), device, shard, n_shards, C.byref(h)))
+        m = cls(h.value, "brwt")
+        m.consumed = used.value
+        return m
+
+    @classmethod
+    def synthesize_brwt_shard(cls, n_rows, n_cols, density, shard, n_shards, seed=42, arity=4, device=0):
+        h = C.c_void_p()
+        t = density_threshold(density)
+        _check(lib().ggq_brwt_synthesize_shard(n_rows, n_cols, t, seed, arity, device, shard, n_shards, C.byref(h)))
+        m = cls(h.value, "brwt")
+        m.threshold, m.seed = t, seed
+        return m
+
+    def shard_info(self):
+        """-> (shard, n_shards, col_owned[num_columns] as bool array)."""
+        a, b = C.c_uint32(), C.c_uint32()
+        own = np.zeros(max(int(self.num_columns), 1), np.uint8)
+        _check(lib().ggq_shard_info(self._h, C.byref(a), C.byref(b), own.ctypes.data_as(u8p)))
+        return a.value, b.value, own[:int(self.num_columns)].astype(bool)
 
     @classmethod
     def load_colmajor(cls, data, device=0):
@@ -311,7 +379,8 @@ class Workspace:
 
     def stat(self, what):
         """what: 'kernel_ms' | 'probes' | 'touches' | 'launches' of the last query on this workspace."""
-        return lib().ggq_workspace_stat(self._h, {"kernel_ms": 0, "probes": 1, "touches": 2, "launches": 3}[what])
+        return lib().ggq_workspace_stat(self._h, {"kernel_ms": 0, "probes": 1, "touches": 2, "launches": 3,
+                                                  "exchange_ms": 4, "exchange_bytes": 5}[what])
 
     def get_rows_device(self, d_rows_ptr, n, col_bytes=4):
         """d_rows_ptr: device pointer (int).  -> (d_offsets_ptr, d_cols_ptr, n_cols), owned by the workspace."""
@@ -320,6 +389,22 @@ class Workspace:
         total = C.c_uint64()
         _check(lib().ggq_get_rows_device(self.m._h, self._h, C.c_void_p(d_rows_ptr), n, col_bytes,
                                          C.byref(off), C.byref(cols), C.byref(total)))
+        return off.value, cols.value, total.value
+
+    def get_rows_sharded_device(self, comm, d_rows_ptr, n, col_bytes=4):
+        """Collective over all shards (same batch on every rank) -> complete CSR on every rank."""
+        off, cols, total = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        _check(lib().ggq_get_rows_sharded_device(self.m._h, self._h, comm._h, C.c_void_p(d_rows_ptr), n, col_bytes,
+                                                 C.byref(off), C.byref(cols), C.byref(total)))
+        return off.value, cols.value, total.value
+
+    def merge_shards_device(self, n, d_offsets_ptrs, d_cols_ptrs, col_bytes=4):
+        """Merge step alone on device pointers of every shard's partial CSR -> (d_offsets, d_cols, n_cols)."""
+        R = len(d_offsets_ptrs)
+        po = (C.c_void_p * R)(*d_offsets_ptrs)
+        pc = (C.c_void_p * R)(*d_cols_ptrs)
+        off, cols, total = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        _check(lib().ggq_merge_shards_device(self._h, n, R, po, pc, col_bytes, C.byref(off), C.byref(cols), C.byref(total)))
         return off.value, cols.value, total.value
 
     def close(self):

@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
                                 u32 vb = two ? __reduce_or_sync(0xffffffffu, in_b ? (cb << sh) : 0u) : 0u;
                                 if (lane == 0 && (va | vb)) {
                                     const u32 li = a.child_li[ins.arg + k];
+                                    if (li == ~0u) continue;
                                     const u64 hot = a.group_hot[li >> 2];
                                     const u32 sl = u32(hot >> kGhStrideShift) & 3u;
                                     uint4 *base = a.slots + (hot & kGhBaseMask) + (li & 3);
@@ -143,7 +144,8 @@ __global__ void tile_scan_kernel(const unsigned short *tile_cnt, u64 *tile_prefi
     node_ones[i] = run;
 }
 
-inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, u32 arity, int device) {
+inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, u32 arity, int device,
+                               u32 shard = 0, u32 n_shards = 1) {
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
     m->device = device;
@@ -151,6 +153,7 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     FlatTree &t = m->tree;
     build_basic_shape(n_rows, n_cols, arity, &t);
     assign_groups(&t);
+    plan_shards(&t, shard, n_shards);
     if (n_rows >= kMaxRows) throw LimitError("too many rows");
     const bool root_is_leaf = t.nodes[0].children.empty();
 
@@ -181,7 +184,8 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
                 internal_of[f.id] = int(internal_nodes.size());
                 prog.push_back({1u | (ar << 8), u32(child_li.size()), u32(internal_nodes.size()), 0u});
                 internal_nodes.push_back(u32(f.id));
-                for (int c : n.children) child_li.push_back(t.nodes[c].group * 4 + t.nodes[c].lane);
+                for (int c : n.children)   // ~0u: vector held by another shard — evaluated for the OR, never written
+                    child_li.push_back(t.present(u32(c)) ? t.nodes[c].group * 4 + t.nodes[c].lane : ~0u);
                 sp -= ar - 1;
                 st.pop_back();
             }

@@ -24,6 +24,7 @@
 #include "ggq_builder.cuh"
 #include "ggq_bv.cuh"
 #include "ggq_colmajor.cuh"
+#include "ggq_shard.cuh"
 
 namespace ggq {
 
@@ -102,7 +103,7 @@ void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
         for (u32 li = 0; li < n_lanes; ++li) {
             u32 node = mt.lane_node[li];
             mt.lane_sel_off[li] = sel_total;
-            if (node == ~0u) continue;
+            if (node == ~0u || !mt.present(node)) continue;
             mt.nodes[node].ones = ones[li];
             if (!mt.nodes[node].children.empty() || mt.nodes[node].parent < 0)
                 sel_total += ((ones[li] + (1ull << kSelectShift) - 1) >> kSelectShift) + 1;
@@ -191,10 +192,10 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
     int per_sm = 0;
     if (cap_spill) {
-        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
+        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<true>, kRowsWarps * 32, rows_smem));
     } else {
-        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows_smem)));
+        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<false>, kRowsWarps * 32, rows_smem));
     }
     if (per_sm < 1) per_sm = 1;
@@ -212,7 +213,9 @@ void Matrix::derive_stats() {
     num_relations = 0;
     for (const FlatNode &n : tree.nodes) {
         total_column_size += n.size;
-        if (n.children.empty()) num_relations += n.ones * n.cols.size();
+        if (n.children.empty())   // column-sharded: owned columns only
+            for (u32 c : n.cols)
+                if (tree.col_owned.empty() || tree.col_owned[c]) num_relations += n.ones;
     }
     configure_rows(0, ~0u);
     device_bytes = slots.bytes() + sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
@@ -220,7 +223,7 @@ void Matrix::derive_stats() {
 }
 
 // host-parsed tree (plain bits per node) -> device image
-static Matrix *upload_brwt(FlatTree &&tree, int device) {
+static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_shards = 1) {
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
     m->device = device;
@@ -228,6 +231,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device) {
     m->tree = std::move(tree);
     FlatTree &t = m->tree;
     assign_groups(&t);
+    plan_shards(&t, shard, n_shards);
     assign_geometry(&t);
     m->upload_tables(t);
     m->slots.alloc(std::max<u64>(t.total_slots, 4));
@@ -238,7 +242,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device) {
     std::vector<u64> lane_plain_off(n_lanes, 0);
     u64 total_words = 0;
     for (u32 li = 0; li < n_lanes; ++li) {
-        if (t.lane_node[li] == ~0u) continue;
+        if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
         lane_plain_off[li] = total_words;
         total_words += t.nodes[t.lane_node[li]].bits.w.size();
     }
@@ -247,7 +251,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device) {
         DeviceBuf<u64> d_off;
         d_plain.alloc(std::max<u64>(total_words, 1));
         for (u32 li = 0; li < n_lanes; ++li) {
-            if (t.lane_node[li] == ~0u) continue;
+            if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
             const auto &w = t.nodes[t.lane_node[li]].bits.w;
             CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
         }
@@ -281,9 +285,11 @@ Workspace::Workspace(const Matrix *m_) : m(m_) {
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     d_ctrl.alloc(8);
     d_err.alloc(1);
-    CUDA_CHECK(cudaMallocHost(&h_ctrl, 8 * sizeof(u64)));
+    CUDA_CHECK(cudaMallocHost(&h_ctrl, 32 * sizeof(u64)));
     CUDA_CHECK(cudaEventCreate(&ev0));
     CUDA_CHECK(cudaEventCreate(&ev1));
+    CUDA_CHECK(cudaEventCreate(&ev2));
+    CUDA_CHECK(cudaEventCreate(&ev3));
     if (m->kind == Matrix::BRWT && m->cap_spill)
         d_spill.alloc(size_t(m->rows_grid) * kRowsWarps * m->cap_spill);
 }
@@ -292,6 +298,8 @@ Workspace::~Workspace() {
     cudaSetDevice(m->device);
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
+    if (ev2) cudaEventDestroy(ev2);
+    if (ev3) cudaEventDestroy(ev3);
     if (stream) cudaStreamDestroy(stream);
     if (h_ctrl) cudaFreeHost(h_ctrl);
     if (h_stage) cudaFreeHost(h_stage);
@@ -454,12 +462,14 @@ using namespace ggq;
 struct ggq_matrix : ggq::Matrix {};
 struct ggq_workspace : ggq::Workspace { using ggq::Workspace::Workspace; };
 struct ggq_rows_result : ggq::RowsResult {};
+struct ggq_comm : ggq::Comm {};
 
 #define GGQ_TRY try {
 #define GGQ_CATCH                                                                   \
     } catch (const ggq::ParseError &e) { return fail(GGQ_ERR_FORMAT, e.what());     \
     } catch (const ggq::LimitError &e) { return fail(GGQ_ERR_LIMIT, e.what());      \
     } catch (const ggq::CudaError &e) { return fail(GGQ_ERR_CUDA, e.what());        \
+    } catch (const ggq::NcclError &e) { return fail(GGQ_ERR_NCCL, e.what());        \
     } catch (const std::bad_alloc &) { return fail(GGQ_ERR_OOM, "out of memory");   \
     } catch (const std::exception &e) { return fail(GGQ_ERR_INTERNAL, e.what()); }
 
@@ -475,14 +485,15 @@ int ggq_device_count(int *count) {
     return GGQ_OK;
 }
 
-static int brwt_load_reader(Reader &in, int device, ggq_matrix **out) {
+static int brwt_load_reader(Reader &in, int device, ggq_matrix **out, u32 shard = 0, u32 n_shards = 1) {
     GGQ_TRY
     if (!out) return fail(GGQ_ERR_ARG, "null out");
     ParsedNode root;
     load_brwt_node(in, &root);
     FlatTree t;
     flatten_parsed(std::move(root), &t);
-    *out = static_cast<ggq_matrix *>(upload_brwt(std::move(t), device));
+    if (n_shards < 1 || shard >= n_shards) return fail(GGQ_ERR_ARG, "bad shard");
+    *out = static_cast<ggq_matrix *>(upload_brwt(std::move(t), device, shard, n_shards));
     return GGQ_OK;
     GGQ_CATCH
 }
@@ -499,6 +510,57 @@ int ggq_brwt_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int d
     int rc = brwt_load_reader(in, device, out);
     if (consumed) *consumed = in.consumed();
     return rc;
+}
+
+int ggq_brwt_load_shard(ggq_read_fn read, void *ctx, int device, uint32_t shard, uint32_t n_shards, ggq_matrix **out) {
+    if (!read) return fail(GGQ_ERR_ARG, "null reader");
+    Reader in(read, ctx);
+    return brwt_load_reader(in, device, out, shard, n_shards);
+}
+
+int ggq_brwt_load_shard_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, uint32_t shard,
+                               uint32_t n_shards, ggq_matrix **out) {
+    if (!buf && len) return fail(GGQ_ERR_ARG, "null buffer");
+    Reader in(buf, len);
+    int rc = brwt_load_reader(in, device, out, shard, n_shards);
+    if (consumed) *consumed = in.consumed();
+    return rc;
+}
+
+int ggq_brwt_synthesize_shard(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed, uint32_t arity,
+                              int device, uint32_t shard, uint32_t n_shards, ggq_matrix **out) {
+    GGQ_TRY
+    if (!out || arity < 2 || n_shards < 1 || shard >= n_shards) return fail(GGQ_ERR_ARG, "bad argument");
+    if (n_cols >= (1ull << 31)) return fail(GGQ_ERR_LIMIT, "too many columns");
+    *out = static_cast<ggq_matrix *>(synthesize_brwt(n_rows, u32(n_cols), threshold, seed, arity, device, shard, n_shards));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_brwt_shard_plan_buffer(const uint8_t *buf, size_t len, uint32_t n_shards, uint32_t *col_owner, uint32_t *cut_depth) {
+    GGQ_TRY
+    if ((!buf && len) || n_shards < 1) return fail(GGQ_ERR_ARG, "bad argument");
+    Reader in(buf, len);
+    ParsedNode root;
+    load_brwt_node(in, &root);
+    FlatTree t;
+    flatten_parsed(std::move(root), &t);
+    assign_groups(&t);
+    plan_shards(&t, 0, n_shards);
+    if (col_owner)
+        for (u64 c = 0; c < t.n_cols; ++c) col_owner[c] = t.col_owner[c];
+    if (cut_depth) *cut_depth = t.cut_depth;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_shard_info(const ggq_matrix *m, uint32_t *shard, uint32_t *n_shards, uint8_t *col_owned) {
+    if (!m) return fail(GGQ_ERR_ARG, "null matrix");
+    if (shard) *shard = m->tree.shard;
+    if (n_shards) *n_shards = m->tree.n_shards;
+    if (col_owned)
+        for (u64 c = 0; c < m->tree.n_cols; ++c) col_owned[c] = m->tree.col_owned.empty() ? 1 : m->tree.col_owned[c];
+    return GGQ_OK;
 }
 
 int ggq_colmajor_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out) {
@@ -618,6 +680,12 @@ double ggq_workspace_stat(const ggq_workspace *ws, int what) {
         case GGQ_STAT_PROBES: return double(ws->last_probes);
         case GGQ_STAT_TOUCHES: return double(ws->last_touches);
         case GGQ_STAT_LAUNCHES: return double(ws->launches);
+        case GGQ_STAT_EXCHANGE_MS: {
+            float ms = 0.f;
+            if (!ws->exchange_timed || cudaEventElapsedTime(&ms, ws->ev2, ws->ev3) != cudaSuccess) return -1.0;
+            return ms;
+        }
+        case GGQ_STAT_EXCHANGE_BYTES: return double(ws->exchange_bytes);
         default: return -1.0;
     }
 }
@@ -630,6 +698,70 @@ int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *
     rows_device(m, ws, reinterpret_cast<const u64 *>(d_rows), n, col_bytes, &total);
     if (d_offsets) *d_offsets = reinterpret_cast<const uint64_t *>(ws->d_offsets.p);
     if (d_cols) *d_cols = ws->d_out.p;
+    if (n_cols) *n_cols = total;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_merge_shards_device(ggq_workspace *ws, uint64_t n, int n_shards, const uint64_t *const *d_offsets,
+                            const uint32_t *const *d_cols, int col_bytes, const uint64_t **d_out_offsets,
+                            const void **d_out_cols, uint64_t *n_cols) {
+    GGQ_TRY
+    if (!ws || n_shards < 1 || n_shards > kMaxShards || !d_offsets || !d_cols || (col_bytes != 4 && col_bytes != 8))
+        return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(ws->m->device));
+    ShardPtrs p;
+    p.n = n_shards;
+    for (int r = 0; r < n_shards; ++r) { p.off[r] = reinterpret_cast<const u64 *>(d_offsets[r]); p.cols[r] = d_cols[r]; }
+    u64 total = 0;
+    merge_shards(ws, p, n, col_bytes, &total);
+    if (d_out_offsets) *d_out_offsets = reinterpret_cast<const uint64_t *>(ws->m_off.p);
+    if (d_out_cols) *d_out_cols = ws->m_out.p;
+    if (n_cols) *n_cols = total;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_comm_unique_id(uint8_t id[128]) {
+    GGQ_TRY
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclUniqueId u;
+    NCCL_CHECK(NcclApi::get().GetUniqueId(&u));
+    std::memcpy(id, &u, 128);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_comm_init(const uint8_t id[128], int rank, int n_ranks, int device, ggq_comm **out) {
+    GGQ_TRY
+    if (!id || !out || rank < 0 || rank >= n_ranks) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(device));
+    std::unique_ptr<ggq_comm> c(new ggq_comm());
+    ncclUniqueId u;
+    std::memcpy(&u, id, 128);
+    NCCL_CHECK(NcclApi::get().CommInitRank(&c->comm, n_ranks, u, rank));
+    c->rank = rank; c->n_ranks = n_ranks; c->device = device;
+    *out = c.release();
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+void ggq_comm_free(ggq_comm *c) {
+    if (!c) return;
+    if (c->comm) NcclApi::get().CommDestroy(c->comm);
+    delete c;
+}
+
+int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
+                                uint64_t *n_cols) {
+    GGQ_TRY
+    if (!m || !ws || !comm || (!d_rows && n) || (col_bytes != 4 && col_bytes != 8)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (m->kind != Matrix::BRWT) return fail(GGQ_ERR_ARG, "not a BRWT");
+    u64 total = 0;
+    rows_sharded_device(m, ws, comm, reinterpret_cast<const u64 *>(d_rows), n, col_bytes, &total);
+    if (d_offsets) *d_offsets = reinterpret_cast<const uint64_t *>(ws->m_off.p);
+    if (d_cols) *d_cols = ws->m_out.p;
     if (n_cols) *n_cols = total;
     return GGQ_OK;
     GGQ_CATCH
@@ -771,6 +903,13 @@ static int get_cells(const ggq_matrix *m, const uint64_t *rows, const uint64_t *
     GGQ_TRY
     if (!m || (!rows && n) || (!out && n)) return fail(GGQ_ERR_ARG, "bad argument");
     if (!n) return GGQ_OK;
+    if (m->kind == Matrix::BRWT && !m->tree.col_owned.empty()) {   // column-sharded: only owned columns can be answered
+        const std::vector<uint8_t> &own = m->tree.col_owned;
+        if (!cols && fixed_col < own.size() && !own[fixed_col]) return fail(GGQ_ERR_ARG, "column is held by another shard");
+        if (cols)
+            for (u64 i = 0; i < n; ++i)
+                if (cols[i] < own.size() && !own[cols[i]]) return fail(GGQ_ERR_ARG, "column is held by another shard");
+    }
     Workspace *ws = m->acquire();
     try {
         CUDA_CHECK(cudaSetDevice(m->device));
@@ -813,6 +952,8 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
     GGQ_TRY
     if (!m || !rows || !n_rows) return fail(GGQ_ERR_ARG, "bad argument");
     if (col >= ggq_num_columns(m)) return fail(GGQ_ERR_ARG, "column out of range");
+    if (m->kind == Matrix::BRWT && !m->tree.col_owned.empty() && !m->tree.col_owned[col])
+        return fail(GGQ_ERR_ARG, "column is held by another shard");
     Workspace *ws = m->acquire();
     try {
         CUDA_CHECK(cudaSetDevice(m->device));

@@ -14,6 +14,7 @@ namespace ggq {
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
 struct LimitError : std::runtime_error { using std::runtime_error::runtime_error; };
+struct NcclError : std::runtime_error { using std::runtime_error::runtime_error; };
 
 int fail(int code, const std::string &msg);
 
@@ -111,6 +112,13 @@ struct Workspace {
     int launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
     bool kernel_timed = false;
+    // column-sharded queries: gathered partial CSRs of all shards, merged result, exchange timing
+    DeviceBuf<u64> g_off, g_tot, m_off;
+    DeviceBuf<u32> g_cols;
+    DeviceBuf<unsigned char> m_out;
+    cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+    bool exchange_timed = false;
+    u64 exchange_bytes = 0;
 
     explicit Workspace(const Matrix *m_);
     ~Workspace();

@@ -206,6 +206,7 @@ __device__ __forceinline__ bool visit_child(const Img &img, const uint4 &s, u32 
                                             bool multi_sb, u32 t, u32 *s_bm_row, u64 *child_item) {
     if (!slot_test(s, bit)) return false;
     if (info & kLeafFlag) {
+        if (info == kRemoteLane) return false;   // held by another shard (column sharding)
         u32 rank = info & ~kLeafFlag;
         if (!img.multi_leaf) {
             atomicOr(s_bm_row + (rank >> 5), 1u << (rank & 31));

@@ -17,6 +17,7 @@ constexpr uint32_t kGroupLanes = 4;         // sibling vectors interleaved per g
 constexpr uint32_t kSuperShift = 25;        // superblock = 2^25 blocks = 96 * 2^25 positions (< 2^32 ones)
 constexpr uint32_t kSelectShift = 10;       // one select sample per 1024 ones
 constexpr uint32_t kLeafFlag = 0x80000000u;
+constexpr uint32_t kRemoteLane = 0xFFFFFFFFu;  // lane_info of a subtree / leaf held by another shard: never descended
 constexpr uint32_t kChunkBlocks = 256;      // blocks per scan chunk when rank headers are built
 
 // group_hot[g] (u64): slot base (40 bits) | stride_log2 (2) | cnt (3) | more (1) | multi-superblock (1)

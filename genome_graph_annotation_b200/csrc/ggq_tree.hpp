@@ -48,6 +48,12 @@ struct FlatTree {
     uint64_t total_slots = 0, total_sb = 0, total_sel = 0;
     uint32_t max_depth = 0;
     bool multi_column_leaves = false;
+    // column sharding: nodes above the cut are replicated, subtrees below it are dealt to shards
+    uint32_t shard = 0, n_shards = 1, cut_depth = 0;
+    std::vector<uint8_t> node_present;    // empty = everything present
+    std::vector<uint8_t> col_owned;       // per global column; empty = all
+    std::vector<uint32_t> col_owner;      // per global column: owning shard (filled by plan_shards)
+    bool present(uint32_t node) const { return node_present.empty() || node_present[node]; }
 
     uint32_t n_groups() const { return uint32_t(group_hot.size()); }
 };
@@ -229,6 +235,60 @@ inline void assign_groups(FlatTree *t) {
     t->col_path_off[t->n_cols] = uint32_t(t->col_path.size());
 }
 
+// ---- step 2b: column sharding plan -----------------------------------------------------------
+// Cut the tree at the smallest depth D whose frontier (nodes at depth D plus leaves above it, in DFS order) has
+// at least 4 elements per shard; deal the frontier to shards in CONTIGUOUS DFS runs balanced by column count.
+// Every rank derives the same plan from the tree alone.  Nodes at depth <= D stay on every shard; a deeper node
+// is present only on the shard owning its depth-D ancestor.  Concatenating the shards' rows in shard order
+// reproduces the reference's DFS output order (BRWT.cpp:45-50).
+inline void plan_shards(FlatTree *t, uint32_t shard, uint32_t n_shards) {
+    auto &N = t->nodes;
+    t->shard = shard; t->n_shards = n_shards;
+    t->col_owner.assign(t->n_cols, 0);
+    if (n_shards <= 1) { t->node_present.clear(); t->col_owned.clear(); t->cut_depth = 0; return; }
+    // DFS order of nodes
+    std::vector<int> dfs;
+    {
+        std::vector<int> st = {0};
+        while (!st.empty()) {
+            int id = st.back(); st.pop_back();
+            dfs.push_back(id);
+            for (size_t i = N[id].children.size(); i-- > 0;) st.push_back(N[id].children[i]);
+        }
+    }
+    uint32_t D = 1;
+    std::vector<int> frontier;
+    for (;; ++D) {
+        frontier.clear();
+        for (int id : dfs)
+            if (uint32_t(N[id].depth) == D || (N[id].children.empty() && uint32_t(N[id].depth) < D)) frontier.push_back(id);
+        if (frontier.size() >= size_t(4) * n_shards || D >= t->max_depth) break;
+    }
+    t->cut_depth = D;
+    // owner of every frontier element: contiguous runs balanced by columns
+    std::vector<int> owner_of_node(N.size(), -1);
+    uint64_t before = 0, m = std::max<uint64_t>(t->n_cols, 1);
+    for (int id : frontier) {
+        uint64_t w = N[id].cols.size();
+        uint64_t o = std::min<uint64_t>(n_shards - 1, (2 * before + w) * n_shards / (2 * m));
+        owner_of_node[id] = int(o);
+        before += w;
+    }
+    t->node_present.assign(N.size(), 0);
+    t->col_owned.assign(t->n_cols, 0);
+    for (size_t id = 0; id < N.size(); ++id) {   // BFS order: parents first
+        FlatNode &n = N[id];
+        if (owner_of_node[id] < 0 && uint32_t(n.depth) > D) owner_of_node[id] = owner_of_node[n.parent];
+        bool above = uint32_t(n.depth) <= D;
+        t->node_present[id] = above || owner_of_node[id] == int(shard);
+        if (n.children.empty())
+            for (uint32_t c : n.cols) { t->col_owner[c] = uint32_t(owner_of_node[id]); t->col_owned[c] = owner_of_node[id] == int(shard); }
+        // frontier elements (and leaves above the cut) held by another shard: never descended / never reported
+        if (owner_of_node[id] >= 0 && owner_of_node[id] != int(shard) && above)
+            t->lane_info[n.group * 4 + n.lane] = kRemoteLane;
+    }
+}
+
 // ---- step 3: arena geometry, once every node's size (= parent's ones) is known -------------
 inline void assign_geometry(FlatTree *t) {
     auto &N = t->nodes;
@@ -242,20 +302,21 @@ inline void assign_geometry(FlatTree *t) {
         uint32_t sl = uint32_t(hot >> kGhStrideShift) & 3;
         uint32_t cnt = uint32_t(hot >> kGhCntShift) & 7;
         uint32_t more = uint32_t(hot >> kGhMoreShift) & 1;
-        uint64_t len = N[t->lane_node[g * 4]].size;
+        const bool g_present = t->present(t->lane_node[g * 4]);
+        uint64_t len = g_present ? N[t->lane_node[g * 4]].size : 0;
         if (len >= kMaxRows) throw ParseError("vector longer than the engine supports");
-        uint64_t nb = len / kSlotBits + 1;  // + sentinel block
+        uint64_t nb = g_present ? len / kSlotBits + 1 : 0;  // + sentinel block
         slot = (slot + 3) & ~uint64_t(3);   // 64-byte alignment of every group
-        t->group_hot[g] = pack_group_hot(slot, sl, cnt, more) | (uint64_t(((nb - 1) >> kSuperShift) != 0) << kGhSuperShift);
+        t->group_hot[g] = pack_group_hot(slot, sl, cnt, more) | (uint64_t(nb && ((nb - 1) >> kSuperShift) != 0) << kGhSuperShift);
         t->group_nblocks[g] = nb;
         slot += nb << sl;
-        uint64_t n_sb = ((nb - 1) >> kSuperShift) + 1;
+        uint64_t n_sb = nb ? ((nb - 1) >> kSuperShift) + 1 : 1;
         for (uint32_t k = 0; k < cnt; ++k) {
             const FlatNode &n = N[t->lane_node[g * 4 + k]];
             t->lane_sb_off[g * 4 + k] = uint32_t(sb);
             sb += n_sb;
             t->lane_sel_off[g * 4 + k] = sel;
-            if (!n.children.empty() || n.parent < 0)  // select is only ever needed on internal nodes
+            if (g_present && (!n.children.empty() || n.parent < 0))  // select is only ever needed on internal nodes
                 sel += ((n.ones + (uint64_t(1) << kSelectShift) - 1) >> kSelectShift) + 1;
         }
     }

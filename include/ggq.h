@@ -28,12 +28,14 @@ typedef enum ggq_status {
     GGQ_ERR_OOM = -3,      /* host or device allocation failed */
     GGQ_ERR_ARG = -4,      /* invalid argument (null pointer, column out of range, ...) */
     GGQ_ERR_LIMIT = -5,    /* matrix exceeds an engine limit (see DESIGN.md "Limits") */
-    GGQ_ERR_INTERNAL = -6
+    GGQ_ERR_INTERNAL = -6,
+    GGQ_ERR_NCCL = -7      /* NCCL failure in a column-sharded query */
 } ggq_status;
 
 typedef struct ggq_matrix ggq_matrix;            /* GPU-resident BinaryMatrix (BRWT or column-major) */
 typedef struct ggq_bv ggq_bv;                    /* GPU-resident bit vector with rank/select */
 typedef struct ggq_workspace ggq_workspace;      /* per-caller stream + scratch (device-resident API) */
+typedef struct ggq_comm ggq_comm;                /* NCCL communicator of the shards of one matrix */
 typedef struct ggq_rows_result ggq_rows_result;  /* host-resident CSR result of ggq_get_rows */
 
 /* Pull reader used by the stream loaders: must copy exactly n bytes to dst and return n, or return
@@ -125,10 +127,48 @@ void *ggq_workspace_stream(ggq_workspace *ws);  /* cudaStream_t */
 /* Measurements of the last query on this workspace (for roofline accounting, DESIGN.md "Measurement"):
  * device time of the dominant kernel between two CUDA events on the workspace stream; sibling-group
  * probes (one 16/32/64-byte block each); (node,row) bit tests (V_t of SURVEY.md 8d); kernel launches. */
-enum { GGQ_STAT_KERNEL_MS = 0, GGQ_STAT_PROBES = 1, GGQ_STAT_TOUCHES = 2, GGQ_STAT_LAUNCHES = 3 };
+enum { GGQ_STAT_KERNEL_MS = 0, GGQ_STAT_PROBES = 1, GGQ_STAT_TOUCHES = 2, GGQ_STAT_LAUNCHES = 3,
+       GGQ_STAT_EXCHANGE_MS = 4 /* NCCL exchange of the last sharded query */, GGQ_STAT_EXCHANGE_BYTES = 5 };
 double ggq_workspace_stat(const ggq_workspace *ws, int what);
 int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
                         int col_bytes, const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols);
+
+/* ------------------------------------------------------------------ column sharding ---------- */
+/* SURVEY.md 8(e) "root-subtree column sharding" (config C5: the image does not fit one GPU).  The tree is cut at
+ * the smallest depth whose frontier has >= 4 elements per shard; the frontier is dealt to shards in contiguous
+ * DFS runs balanced by column count (every rank derives the same plan from the tree alone).  Levels above the
+ * cut are replicated, a deeper subtree lives only on its owner.  A shard answers get_rows with the owned columns
+ * only; concatenating the shards' rows in shard order IS BRWT::get_row's order (BRWT.cpp:45-50).
+ * get / has_column / get_column work on the owning shard and fail with GGQ_ERR_ARG elsewhere;
+ * num_relations counts owned columns only. */
+int ggq_brwt_load_shard(ggq_read_fn read, void *ctx, int device, uint32_t shard, uint32_t n_shards, ggq_matrix **out);
+int ggq_brwt_load_shard_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, uint32_t shard,
+                               uint32_t n_shards, ggq_matrix **out);
+int ggq_brwt_synthesize_shard(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed, uint32_t arity,
+                              int device, uint32_t shard, uint32_t n_shards, ggq_matrix **out);
+/* Host-only: the plan for a serialized BRWT.  col_owner: num_columns entries (may be NULL). */
+int ggq_brwt_shard_plan_buffer(const uint8_t *buf, size_t len, uint32_t n_shards, uint32_t *col_owner, uint32_t *cut_depth);
+/* col_owned: num_columns bytes (may be NULL) */
+int ggq_shard_info(const ggq_matrix *m, uint32_t *shard, uint32_t *n_shards, uint8_t *col_owned);
+
+/* Merge step alone: per query, concatenate the shards' partial rows in shard order.  d_offsets[s] (n + 1 u64) and
+ * d_cols[s] (u32 ids) are device pointers readable from the workspace's device — local buffers filled by the
+ * caller's own collective, or peer memory.  Result in buffers owned by the workspace. */
+int ggq_merge_shards_device(ggq_workspace *ws, uint64_t n, int n_shards, const uint64_t *const *d_offsets,
+                            const uint32_t *const *d_cols, int col_bytes, const uint64_t **d_out_offsets,
+                            const void **d_out_cols, uint64_t *n_cols);
+
+/* NCCL plumbing: rank 0 calls ggq_comm_unique_id and ships the 128 bytes to the other ranks by any means; every
+ * rank (one process per GPU) then calls ggq_comm_init — collective. */
+int ggq_comm_unique_id(uint8_t id[128]);
+int ggq_comm_init(const uint8_t id[128], int rank, int n_ranks, int device, ggq_comm **out);
+void ggq_comm_free(ggq_comm *c);
+/* Collective over the shards of one matrix: every rank passes the SAME batch (device memory) and ends with the
+ * complete CSR: local descent, ncclAllGather of partial offsets + grouped ncclBroadcast of partial column ids over
+ * NVLink, merge kernel.  Runs on the workspace stream. */
+int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
+                                uint64_t *n_cols);
 
 /* ------------------------------------------------------------------ cells / columns ---------- */
 

@@ -1,0 +1,55 @@
+"""Two (or more) ranks, one process per GPU: column-sharded get_rows through NCCL (ggq_get_rows_sharded_device)
+must equal the unsharded answer.  Launched by tests/test_shard_gpu.py::test_nccl_two_ranks and by hand:
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 scripts/shard_nccl_check.py"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import genome_graph_annotation_b200 as g  # noqa: E402
+
+
+def d2h(ptr, nbytes, dtype):
+    from cuda.bindings import runtime as rt
+    out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+    if nbytes:
+        (err,) = rt.cudaMemcpy(out.ctypes.data, ptr, nbytes, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+        assert int(err) == 0, err
+    return out
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ids = [g.Comm.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    comm = g.Comm(ids[0], rank, world, local)
+    n, m, d = 200_000, 500, 0.02
+    sm = g.GpuMatrix.synthesize_brwt_shard(n, m, d, rank, world, seed=42, arity=4, device=local)
+    ws = sm.workspace()
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(1234)   # the same batch on every rank
+    for B in (1, 1000, 300_000):
+        rows = torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen)
+        off, cols, total = ws.get_rows_sharded_device(comm, rows.data_ptr(), B, 8)
+        h_off, h_cols = d2h(off, (B + 1) * 8, np.uint64), d2h(cols, total * 8, np.uint64)
+        if rank == 0:
+            whole = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local)
+            eoff, ecols = whole.get_rows_csr(rows.cpu().numpy().view(np.uint64))
+            whole.close()
+            assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), B
+        print("rank %d B=%d total=%d exchange %.3f ms %.1f MB" % (rank, B, total, ws.stat("exchange_ms"),
+                                                                  ws.stat("exchange_bytes") / 1e6), flush=True)
+    dist.barrier()
+    ws.close(); sm.close(); comm.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("SHARD_NCCL_OK")
+
+
+if __name__ == "__main__":
+    main()

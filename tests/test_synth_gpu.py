@@ -118,3 +118,16 @@ def test_pipelined_host_api_matches_single_shot(ggq):
             gm.get_rows_into(rows, off, small)
     finally:
         gm.close()
+
+
+def test_two_matrices_with_different_shapes_coexist(ggq):
+    """Kernel attributes (dynamic shared memory limit) are per function, not per matrix: a wide matrix must
+    still answer after a narrow one was created (regression)."""
+    wide = ggq.GpuMatrix.synthesize_brwt(5000, 2500, 0.01, seed=1, arity=4)
+    rows = np.arange(0, 5000, 3, dtype=np.uint64)
+    a = wide.get_rows_csr(rows)
+    narrow = ggq.GpuMatrix.synthesize_brwt(5000, 8, 0.2, seed=1, arity=2)
+    narrow.get_rows_csr(rows)
+    b = wide.get_rows_csr(rows)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    wide.close(); narrow.close()
