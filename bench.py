@@ -299,6 +299,25 @@ def run_ours(args):
                "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
                "api": "ggq_get_rows_into (host row ids in, host CSR offsets + u64 column ids out)"}
 
+    # ---- the call `annograph classify` really makes: count_labels (annotate_static.cpp:149-162), fused on device ----
+    cl = None
+    if not args.no_e2e:
+        h_rows_cl = batches[0].cpu().pin_memory().numpy().view(np.uint64)
+        gm.count_labels(h_rows_cl)
+        barrier()
+        tw = time.perf_counter()
+        Kc = 3
+        for i in range(Kc):
+            cnt = gm.count_labels(h_rows_cl)
+        torch.cuda.synchronize()
+        tc = torch.tensor([time.perf_counter() - tw], device="cuda", dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+        cl = {"value": world * B * Kc / float(tc.item()), "unit": UNIT, "h2d_bytes_per_step": B * 8,
+              "d2h_bytes_per_step": int(cnt.size) * 8, "steps": Kc,
+              "api": "ggq_count_labels (host row ids in, per-column counters out; row sets never leave the device)",
+              "labels_counted_per_step": int(cnt.sum())}
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -332,6 +351,8 @@ def run_ours(args):
             "column_ids_per_row": ids / (B * K)}
     if e2e is not None:
         line["e2e"] = e2e
+    if cl is not None:
+        line["count_labels_e2e"] = cl
     if world == 1 and not args.no_cpu_baseline:
         built = build_cpu_reference(args)
         if built is not None:

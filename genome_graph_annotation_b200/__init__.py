@@ -79,6 +79,8 @@ def lib():
         "ggq_rows_count": (C.c_uint64, [vp]),
         "ggq_rows_result_free": (None, [vp]),
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_count_labels": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
+        "ggq_count_labels_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.POINTER(vp)]),
         "ggq_slice_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(u64p), u64p]),
         "ggq_buffer_free": (None, [vp]),
         "ggq_workspace_create": (C.c_int, [vp, C.POINTER(vp)]),
@@ -324,6 +326,13 @@ class GpuMatrix:
     def get_row(self, row):
         return self.get_rows_csr([row])[1]
 
+    def count_labels(self, rows):
+        """Histogram of set columns over the multiset `rows` (ggq_count_labels) -> uint64[num_columns]."""
+        rows, rp = _u64(rows)
+        out = np.zeros(max(int(self.num_columns), 1), np.uint64)
+        _check(lib().ggq_count_labels(self._h, rp, rows.size, out.ctypes.data_as(u64p)))
+        return out[:int(self.num_columns)]
+
     def slice_rows(self, rows):
         rows, rp = _u64(rows)
         out = u64p()
@@ -390,6 +399,12 @@ class Workspace:
         _check(lib().ggq_get_rows_device(self.m._h, self._h, C.c_void_p(d_rows_ptr), n, col_bytes,
                                          C.byref(off), C.byref(cols), C.byref(total)))
         return off.value, cols.value, total.value
+
+    def count_labels_device(self, d_rows_ptr, n):
+        """-> device pointer to uint64[num_columns] counts, owned by the workspace."""
+        out = C.c_void_p()
+        _check(lib().ggq_count_labels_device(self.m._h, self._h, C.c_void_p(d_rows_ptr), n, C.byref(out)))
+        return out.value
 
     def get_rows_sharded_device(self, comm, d_rows_ptr, n, col_bytes=4):
         """Collective over all shards (same batch on every rank) -> complete CSR on every rank."""

@@ -54,6 +54,58 @@ __global__ void __launch_bounds__(256) bv_query_kernel(BvImg v, const u64 *q, u6
     }
 }
 
+// bit_vector_stat fast paths (config C3).  The generic kernel reads the whole 64-byte block from one thread
+// (4 x 16-byte loads per lane: the slow L1 pattern of scripts/mb_gather.cu, 15 G queries/s).
+// get: the one data word, 8 bytes per lane.
+__global__ void __launch_bounds__(256) stat_get_kernel(RbImg v, const u64 *q, u64 n, unsigned char *out) {
+    for (u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += u64(gridDim.x) * blockDim.x) {
+        const u64 x = q[t];
+        bool bit = false;
+        if (x < v.n_bits) {
+            const u64 b = x / kRbBits;
+            const u32 o = u32(x - b * kRbBits);
+            u64 w;
+            asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u64 %0, [%1];" : "=l"(w) : "l"(v.blk + b * kRbWords + 1 + (o >> 6)));
+            bit = (w >> (o & 63)) & 1ull;
+        }
+        out[t] = bit;
+    }
+}
+
+// rank1: 2 lanes per query, each reads one 32-byte sector of the block with a 256-bit load
+// (lane 0: header + words 0..2, lane 1: words 3..6), partial popcounts meet in one shuffle.
+__global__ void __launch_bounds__(256) stat_rank_kernel(RbImg v, const u64 *q, u64 n, u64 *out) {
+    const u32 half = threadIdx.x & 1;
+    const u64 stride = (u64(gridDim.x) * blockDim.x) >> 1;
+    for (u64 t0 = (u64(blockIdx.x) * blockDim.x + (threadIdx.x & ~31u)) >> 1; t0 < n; t0 += stride) {
+        const u64 t = t0 + ((threadIdx.x & 31) >> 1);
+        const bool valid = t < n && v.n_bits != 0;
+        u64 part = 0;
+        if (valid) {
+            const u64 x = q[t];
+            const u64 i = x < v.n_bits ? x : v.n_bits - 1;   // clamp (bit_vector.cpp:285)
+            const u64 b = i / kRbBits;
+            const u32 o = u32(i - b * kRbBits), wi = o >> 6;
+            u32 r0, r1, r2, r3, r4, r5, r6, r7;
+            asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                         : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7)
+                         : "l"(v.blk + b * kRbWords + 4 * half));
+            const u64 w[4] = {u64(r1) << 32 | r0, u64(r3) << 32 | r2, u64(r5) << 32 | r4, u64(r7) << 32 | r6};
+            const u64 incl = (2ull << (o & 63)) - 1ull;       // bits 0..(o & 63)
+#pragma unroll
+            for (u32 k = 0; k < 4; ++k) {
+                if (half == 0 && k == 0) { part = w[0]; continue; }   // the block's rank header
+                const u32 word = 4 * half + k - 1;                     // data word index 0..6
+                if (word < wi) part += __popcll(w[k]);
+                else if (word == wi) part += __popcll(w[k] & incl);
+            }
+        }
+        const u64 other = __shfl_xor_sync(0xffffffffu, part, 1);
+        if (valid && half == 0) out[t] = part + other;
+        if (t < n && v.n_bits == 0 && half == 0) out[t] = 0;
+    }
+}
+
 // bit i set iff mix64(seed_mul + i) < threshold  (SURVEY.md 8d portable generator)
 __global__ void synth_bits_kernel(u64 *words, u64 n_words, u64 n_bits, u64 threshold, u64 seed_mul) {
     u64 w = u64(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -102,6 +154,12 @@ struct BitVec {
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         u32 grid = u32(std::min<u64>((n + 255) / 256, u64(sms) * (KIND == GGQ_BV_RRR ? 6 : 8) * 4));
         if (!grid) return;
+        if (KIND == GGQ_BV_STAT && op == OP_GET) {
+            stat_get_kernel<<<grid, 256, 0, st>>>(img.stat, q, n, static_cast<unsigned char *>(out));
+        } else if (KIND == GGQ_BV_STAT && op == OP_RANK1) {
+            u32 g2 = u32(std::min<u64>((2 * n + 255) / 256, u64(sms) * 32));
+            stat_rank_kernel<<<g2, 256, 0, st>>>(img.stat, q, n, static_cast<u64 *>(out));
+        } else
         if (op == OP_RANK1) bv_query_kernel<KIND, OP_RANK1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));
         else if (op == OP_SELECT1) bv_query_kernel<KIND, OP_SELECT1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));
         else bv_query_kernel<KIND, OP_GET, unsigned char><<<grid, 256, 0, st>>>(img, q, n, static_cast<unsigned char *>(out));

@@ -420,6 +420,7 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
             continue;
         }
         *total_out = total;
+        if (ws->hist_mode) return;   // ids stay in the chunk arena (order is irrelevant to a histogram)
         size_t out_bytes = size_t(total) * col_bytes;
         if (ws->d_out.n < out_bytes) ws->d_out.alloc(out_bytes + out_bytes / 8 + 1024);
         if (total) {
@@ -861,6 +862,64 @@ int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uin
     for (Workspace *ws : w)
         if (ws) m->release(ws);
     return rc;
+    GGQ_CATCH
+}
+
+// device part of count_labels: counts (u64 x num_columns) in ws->d_counts
+static void count_labels_device(const ggq_matrix *m, Workspace *ws, const u64 *d_rows, u64 n) {
+    const u64 nc = std::max<u64>(m->tree.n_cols, 1);
+    if (ws->d_counts.n < nc) ws->d_counts.alloc(nc);
+    CUDA_CHECK(cudaMemsetAsync(ws->d_counts.p, 0, nc * 8, ws->stream));
+    u64 total = 0;
+    const u32 *ids = nullptr;
+    if (m->kind == Matrix::BRWT) {
+        ws->hist_mode = true;
+        try { rows_device(m, ws, d_rows, n, 4, &total); } catch (...) { ws->hist_mode = false; throw; }
+        ws->hist_mode = false;
+        ids = ws->d_tmp.p;
+    } else {
+        rows_device(m, ws, d_rows, n, 4, &total);
+        ids = reinterpret_cast<const u32 *>(ws->d_out.p);
+    }
+    if (total) {
+        const u32 smem_cols = 12288;   // 48 KB of u32 counters
+        const size_t smem = nc <= smem_cols ? nc * 4 : 0;
+        const u32 grid = u32(std::min<u64>(u64(m->sm_count) * 4, (total + 511) / 512));
+        col_hist_kernel<<<grid, 512, smem, ws->stream>>>(ids, total, u32(nc), smem_cols, ws->d_counts.p);
+        CUDA_CHECK(cudaGetLastError());
+        ws->launches += 1;
+    }
+}
+
+int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts) {
+    GGQ_TRY
+    if (!m || (!rows && n) || !counts) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    Workspace *ws = m->acquire();
+    try {
+        ws->reserve_rows(n);
+        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
+        count_labels_device(m, ws, ws->d_rows.p, n);
+        if (m->tree.n_cols)
+            CUDA_CHECK(cudaMemcpyAsync(counts, ws->d_counts.p, m->tree.n_cols * 8, cudaMemcpyDeviceToHost, ws->stream));
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_count_labels_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
+                            const uint64_t **d_counts) {
+    GGQ_TRY
+    if (!m || !ws || (!d_rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    count_labels_device(m, ws, reinterpret_cast<const u64 *>(d_rows), n);
+    if (d_counts) *d_counts = reinterpret_cast<const uint64_t *>(ws->d_counts.p);
+    return GGQ_OK;
     GGQ_CATCH
 }
 

@@ -112,6 +112,8 @@ struct Workspace {
     int launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
     bool kernel_timed = false;
+    bool hist_mode = false;          // count_labels: skip CSR assembly, the ids stay unordered in d_tmp
+    DeviceBuf<u64> d_counts;
     // column-sharded queries: gathered partial CSRs of all shards, merged result, exchange timing
     DeviceBuf<u64> g_off, g_tot, m_off;
     DeviceBuf<u32> g_cols;

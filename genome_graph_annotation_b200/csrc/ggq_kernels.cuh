@@ -384,6 +384,31 @@ __global__ void iota_kernel(u32 *p, u64 n) {
     if (i < n) p[i] = u32(i);
 }
 
+// count_labels: histogram of column ids (StaticBinRelAnnotator::count_labels, annotate_static.cpp:149-162).
+// Privatised in shared memory when the matrix has at most `smem_cols` columns, else straight global atomics.
+__global__ void __launch_bounds__(512)
+col_hist_kernel(const u32 *ids, u64 n_ids, u32 n_cols, u32 smem_cols, u64 *counts) {
+    extern __shared__ u32 s_hist[];
+    const bool priv = n_cols <= smem_cols;
+    if (priv) {
+        for (u32 i = threadIdx.x; i < n_cols; i += blockDim.x) s_hist[i] = 0;
+        __syncthreads();
+    }
+    const u64 stride = u64(gridDim.x) * blockDim.x;
+    for (u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x; i < n_ids; i += stride) {
+        const u32 c = ids[i];
+        if (priv) atomicAdd(s_hist + c, 1u);
+        else atomicAdd(counts + c, 1ull);
+    }
+    if (priv) {
+        __syncthreads();
+        for (u32 i = threadIdx.x; i < n_cols; i += blockDim.x) {
+            const u32 v = s_hist[i];
+            if (v) atomicAdd(counts + i, u64(v));
+        }
+    }
+}
+
 // chunk-local CSR offsets -> global offsets (pipelined host API)
 __global__ void add_base_kernel(u64 *p, u64 n, u64 base) {
     u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;

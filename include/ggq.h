@@ -113,6 +113,15 @@ void ggq_rows_result_free(ggq_rows_result *r);
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
                       uint64_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
 
+/* counts[j] = number of t with column j set in row rows[t] (duplicates counted) — the histogram
+ * StaticBinRelAnnotator::count_labels builds with one get_row per index (annotation/annotate_static.cpp:149-162),
+ * i.e. what get_labels(indices, ratio) / get_top_labels threshold (annotate_static.cpp:71-94, annotate.cpp:57-83).
+ * The row sets never leave the device: descent + shared-memory histogram, num_columns counters come back.
+ * counts: num_columns entries.  Column-sharded matrices count their owned columns (others stay 0: sum over ranks). */
+int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts);
+int ggq_count_labels_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
+                            const uint64_t **d_counts);
+
 /* slice_rows: concatenation of get_row(R[t]) each followed by UINT64_MAX (SURVEY.md "Three facts" 1). */
 int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len);
 void ggq_buffer_free(void *p);

@@ -85,6 +85,15 @@ class GpuMatrixBase : public BinaryMatrix {
         return out;
     }
 
+    // Histogram of the set columns over a multiset of rows: the counter StaticBinRelAnnotator::count_labels fills
+    // with one get_row per index (annotate_static.cpp:149-162), computed on the device without materialising rows.
+    std::vector<uint64_t> count_columns(const std::vector<Row> &rows) const {
+        std::vector<uint64_t> counts(num_columns());
+        uint64_t dummy = 0;
+        check(ggq_count_labels(handle(), rows.data(), rows.size(), counts.empty() ? &dummy : counts.data()));
+        return counts;
+    }
+
     std::vector<bool> has_column(const std::vector<Row> &rows, Column column) const {
         std::vector<uint8_t> tmp(rows.size());
         check(ggq_has_column(handle(), rows.data(), rows.size(), column, tmp.data()));

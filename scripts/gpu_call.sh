@@ -2,4 +2,7 @@
 mkdir -p gpurun_out
 ( time timeout 900 python -m pytest tests -m gpu -x -q ) > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+timeout 600 python scripts/bench_bv.py --kinds stat --densities 0.01,0.5 > gpurun_out/bench_bv_stat.log 2>&1
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
+echo "bench exit $?" >> gpurun_out/bench_n1.err
 echo done

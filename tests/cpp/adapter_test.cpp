@@ -59,6 +59,14 @@ static void compare(const BinaryMatrix &ref, const ggq::GpuMatrixBase &gpu, cons
         REQUIRE(sliced[sp++] == ~uint64_t(0));
     }
     REQUIRE(sp == sliced.size());
+    {   // the counter of StaticBinRelAnnotator::count_labels (annotate_static.cpp:149-162), duplicates counted
+        std::vector<uint64_t> idx(rows);
+        for (uint64_t i = 0; i < n; i += 3) idx.push_back(i);
+        std::vector<uint64_t> expect(m, 0);
+        for (auto i : idx)
+            for (auto j : ref.get_row(i)) expect[j]++;
+        REQUIRE(gpu.count_columns(idx) == expect);
+    }
     for (uint64_t j = 0; j < m; ++j) {
         REQUIRE(gpu.get_column(j) == ref.get_column(j));
         auto hc = gpu.has_column(rows, j);

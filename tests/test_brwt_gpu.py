@@ -35,6 +35,11 @@ def check_matrix(ggq, rm, dense=None, rows=None, all_cells=True):
         off, cols = gm.get_rows_csr(rows)
         assert np.array_equal(off, eoff)
         assert np.array_equal(cols, ecols)
+        # count_labels: histogram over a multiset of rows (annotate_static.cpp:149-162), duplicates counted
+        half = rows[:rows.size // 2]
+        exp_cnt = np.bincount(ecols.astype(np.int64), minlength=m) + \
+            np.bincount(ecols[:int(eoff[half.size])].astype(np.int64), minlength=m)
+        assert np.array_equal(gm.count_labels(np.concatenate([rows, half])), exp_cnt.astype(np.uint64)[:m])
         # slice_rows = rows separated by UINT64_MAX
         sl = gm.slice_rows(rows)
         exp = []

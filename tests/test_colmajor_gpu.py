@@ -22,6 +22,8 @@ def check(ggq, ref, dense):
         off, cols = gm.get_rows_csr(rows)
         eoff, ecols, _ = rm.get_rows(rows)
         assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
+        dup = np.concatenate([rows, rows[::3]])
+        assert np.array_equal(gm.count_labels(dup), (dense.sum(0) + dense[::3].sum(0)).astype(np.uint64))
         for c in range(m):
             assert np.array_equal(gm.get_column(c), rm.get_column(c)), c
             assert np.array_equal(gm.get_column(c), np.nonzero(dense[:, c])[0].astype(np.uint64))
