@@ -1,8 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-( time timeout 900 python -m pytest tests -m gpu -x -q ) > gpurun_out/pytest_gpu.log 2>&1
-echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
-timeout 600 python scripts/bench_bv.py --kinds stat --densities 0.01,0.5 > gpurun_out/bench_bv_stat.log 2>&1
-timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
-echo "bench exit $?" >> gpurun_out/bench_n1.err
+BCMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
+timeout 400 $BCMD > gpurun_out/plain_launch.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_v2.csv $BCMD > gpurun_out/ncu_launch.log 2>&1
+FCMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e --rows 1e9"
+timeout 400 $FCMD > gpurun_out/plain_full.log 2>&1 &&
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:brwt_rows_kernel -s 3 -c 1 -f -o gpurun_out/prof_rows_v2b $FCMD > gpurun_out/ncu_full.log 2>&1
 echo done
