@@ -36,6 +36,27 @@ SEED = 42
 L2_BYTES = 126e6
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """NCCL (and friends) write banners such as 'NCCL version ...' to fd 1; the driver wants exactly ONE JSON
+    line there.  Route fd 1 to stderr for the whole run and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -159,7 +180,7 @@ def run_reference(args):
             "dtype": "u64", "data": "synthetic"}
     if built is None:
         line["unavailable"] = "oracle/_ref/libggref.so (the unmodified reference) is not built on this box"
-        print(json.dumps(line))
+        emit(line)
         return
     R, rm, n, threads = built
     rng = np.random.default_rng(SEED)
@@ -184,7 +205,7 @@ def run_reference(args):
                  "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
                  "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(args, n_gpus, sub_rows=None):
@@ -363,7 +384,7 @@ def run_ours(args):
                 "sample": "%d random rows in %.1f s on a %d x %d d=%g sub-shape (same generator; the reference "
                           "builder cannot make the full shape); unmodified BRWT::get_row under omp parallel for" %
                           (cnt, secs, sub_n, args.cols, args.density)}
-    print(json.dumps(line))
+    emit(line)
     ws.close()
     gm.close()
     if dist is not None:
@@ -460,13 +481,14 @@ def run_c5(args):
                 "gpu_launches": launches, "build_seconds": build_s,
                 "device_image_gb_per_rank_max": float(tmax[4]) / 1e9, "device_image_gb_total": float(tsum[4]) / 1e9,
                 "column_ids_per_row": ids_total / (B * K)}
-        print(json.dumps(line))
+        emit(line)
     ws.close(); gm.close(); comm.close()
     dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse_args()
+    quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     elif a.workload == "c5":
