@@ -12,8 +12,9 @@ GPU holds the whole structure, no collective on the query path 
   python bench.py --impl reference ...                   # the reference's own BRWT::get_row on host cores
 
 `value`  : device-resident rows/s (row ids and CSR in HBM), CUDA events on the query stream, max over ranks.
-`e2e`    : same metric through the host-buffer C-ABI call ggq_get_rows_into (pinned host row ids in,
-           host CSR out; H2D and D2H inside the timed region).
+`e2e`    : same metric through the host-buffer C-ABI call ggq_get_rows_into_u32 (pinned host row ids in, host
+           CSR offsets + u32 column ids out; H2D and D2H inside the timed region); `e2e_u64`: the same through
+           ggq_get_rows_into (u64 column ids, twice the PCIe bytes).
 `roofline`: brwt_rows_kernel (the descent), algorithmic bytes per SURVEY.md §8(d) / its event-timed duration.
 """
 import argparse
@@ -295,30 +296,40 @@ def run_ours(args):
     value = world * B / (ms_step / 1e3)
 
     # ---- end to end through the host-buffer C ABI ------------------------------------------
-    e2e = None
+    e2e = e2e_u64 = None
     if not args.no_e2e:
         cap = int(ids / K * 1.05) + 1024
         h_rows = [b.cpu().pin_memory() for b in batches[:min(n_pool, 3)]]
         h_off = torch.empty(B + 1, dtype=torch.int64).pin_memory()
-        h_cols = torch.empty(cap, dtype=torch.int64).pin_memory()
         np_rows = [r.numpy().view(np.uint64) for r in h_rows]
-        np_off, np_cols = h_off.numpy().view(np.uint64), h_cols.numpy().view(np.uint64)
+        np_off = h_off.numpy().view(np.uint64)
         Ke, We = max(3, min(K, 5)), 2
-        for i in range(We):
-            gm.get_rows_into(np_rows[i % len(np_rows)], np_off, np_cols)
-        barrier()
-        tw = time.perf_counter()
-        d2h = 0
-        for i in range(Ke):
-            total = gm.get_rows_into(np_rows[(We + i) % len(np_rows)], np_off, np_cols)
-            d2h += (B + 1) * 8 + total * 8
-        torch.cuda.synchronize()
-        te = torch.tensor([time.perf_counter() - tw], device="cuda", dtype=torch.float64)
-        if dist is not None:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * B * Ke / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": B * 8,
-               "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
-               "api": "ggq_get_rows_into (host row ids in, host CSR offsets + u64 column ids out)"}
+
+        def host_api(np_cols, id_bytes, api):
+            for i in range(We):
+                gm.get_rows_into(np_rows[i % len(np_rows)], np_off, np_cols)
+            barrier()
+            tw = time.perf_counter()
+            d2h = 0
+            for i in range(Ke):
+                total = gm.get_rows_into(np_rows[(We + i) % len(np_rows)], np_off, np_cols)
+                d2h += (B + 1) * 8 + total * id_bytes
+            torch.cuda.synchronize()
+            te = torch.tensor([time.perf_counter() - tw], device="cuda", dtype=torch.float64)
+            if dist is not None:
+                dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            return {"value": world * B * Ke / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": B * 8,
+                    "d2h_bytes_per_step": d2h // Ke, "steps": Ke, "api": api}
+
+        # headline: compact ids (u32; the engine holds < 2^31 columns) — half the PCIe bytes of the u64 form
+        h_cols32 = torch.empty(cap, dtype=torch.int32).pin_memory()
+        e2e = host_api(h_cols32.numpy().view(np.uint32), 4,
+                       "ggq_get_rows_into_u32 (host row ids in, host CSR offsets + u32 column ids out)")
+        del h_cols32
+        h_cols = torch.empty(cap, dtype=torch.int64).pin_memory()
+        e2e_u64 = host_api(h_cols.numpy().view(np.uint64), 8,
+                           "ggq_get_rows_into (host row ids in, host CSR offsets + u64 column ids out)")
+        del h_cols
 
     # ---- the call `annograph classify` really makes: count_labels (annotate_static.cpp:149-162), fused on device ----
     cl = None
@@ -372,6 +383,7 @@ def run_ours(args):
             "column_ids_per_row": ids / (B * K)}
     if e2e is not None:
         line["e2e"] = e2e
+        line["e2e_u64"] = e2e_u64
     if cl is not None:
         line["count_labels_e2e"] = cl
     if world == 1 and not args.no_cpu_baseline:

@@ -79,6 +79,7 @@ def lib():
         "ggq_rows_count": (C.c_uint64, [vp]),
         "ggq_rows_result_free": (None, [vp]),
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_get_rows_into_u32": (C.c_int, [vp, u64p, C.c_uint64, u64p, C.c_void_p, C.c_uint64, u64p]),
         "ggq_count_labels": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
         "ggq_count_labels_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.POINTER(vp)]),
         "ggq_slice_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(u64p), u64p]),
@@ -312,11 +313,18 @@ class GpuMatrix:
         return off, cols
 
     def get_rows_into(self, rows, offsets, cols):
-        """Caller-provided (e.g. pinned) output arrays; returns the number of column ids."""
+        """Caller-provided (e.g. pinned) output arrays; returns the number of column ids.  `cols` may be uint64
+        (ggq_get_rows_into) or uint32 (ggq_get_rows_into_u32, half the device->host bytes)."""
         n_cols = C.c_uint64()
-        _check(lib().ggq_get_rows_into(self._h, rows.ctypes.data_as(u64p), rows.size,
-                                       offsets.ctypes.data_as(u64p), cols.ctypes.data_as(u64p),
-                                       cols.size, C.byref(n_cols)))
+        if cols.dtype == np.uint32:
+            _check(lib().ggq_get_rows_into_u32(self._h, rows.ctypes.data_as(u64p), rows.size,
+                                               offsets.ctypes.data_as(u64p), cols.ctypes.data, cols.size,
+                                               C.byref(n_cols)))
+        else:
+            assert cols.dtype == np.uint64
+            _check(lib().ggq_get_rows_into(self._h, rows.ctypes.data_as(u64p), rows.size,
+                                           offsets.ctypes.data_as(u64p), cols.ctypes.data_as(u64p),
+                                           cols.size, C.byref(n_cols)))
         return n_cols.value
 
     def get_rows(self, rows):

@@ -165,6 +165,12 @@ void Matrix::refresh_img() {
     img.multi_leaf = tree.multi_column_leaves;
 }
 
+// The instantiation of K1 for a tree: stack spill to global memory, leaves holding several columns.
+static const void *rows_kernel_fn(bool spill, bool multi_leaf) {
+    if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true> : (const void *)brwt_rows_kernel<true, false>;
+    return multi_leaf ? (const void *)brwt_rows_kernel<false, true> : (const void *)brwt_rows_kernel<false, false>;
+}
+
 // Descent kernel configuration: rows per warp batch, stack capacity, grid, query ordering.
 void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     // descent kernel configuration
@@ -185,19 +191,15 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
         cap_s = (std::max<u32>(worst, 32) + 1) & ~1u;
         cap_spill = 0;
         if (cap_s > 512) { cap_spill = cap_s - 512; cap_s = 512; }   // deep/wide trees: overflow to global memory
-        rows_smem = size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(rb) * bm_words * 4);
+        rows_smem = rows_smem_bytes(cap_s, rb, bm_words);
         if (rows_smem <= size_t(max_smem) || rb == 1) break;
         rb >>= 1;
     }
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
     int per_sm = 0;
-    if (cap_spill) {
-        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
-        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<true>, kRowsWarps * 32, rows_smem));
-    } else {
-        CUDA_CHECK(cudaFuncSetAttribute(brwt_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, brwt_rows_kernel<false>, kRowsWarps * 32, rows_smem));
-    }
+    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0);
+    CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
+    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
     rows_grid = u32(sm_count * per_sm);
     // query ordering (see K1): sort on the top `sort_bits` bits of the row id
@@ -398,8 +400,12 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         u64 batches = (n + m->rb - 1) / m->rb;
         u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
         CUDA_CHECK(cudaEventRecord(ws->ev0, st));
-        if (m->cap_spill) brwt_rows_kernel<true><<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
-        else brwt_rows_kernel<false><<<grid, kRowsWarps * 32, m->rows_smem, st>>>(m->img, a);
+        {
+            Img img = m->img;
+            void *kargs[] = {&img, &a};
+            CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0), dim3(grid), dim3(kRowsWarps * 32),
+                                        kargs, m->rows_smem, st));
+        }
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaEventRecord(ws->ev1, st));
         size_t cb = ws->cub_bytes;
@@ -815,8 +821,9 @@ void ggq_rows_result_free(ggq_rows_result *r) {
 // travels to the host, chunk k+1 is sorted and descended — the PCIe copy, not the kernel, bounds this call.
 static const u64 kPipelineChunk = u64(1) << 20;
 
-int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint64_t *cols,
-                      uint64_t cols_capacity, uint64_t *n_cols) {
+static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, void *cols_v,
+                         uint64_t cols_capacity, uint64_t *n_cols, int col_bytes) {
+    unsigned char *cols = static_cast<unsigned char *>(cols_v);
     GGQ_TRY
     if (!m || !offsets || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
@@ -834,7 +841,7 @@ int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uin
             ws->reserve_rows(nc);
             if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + r0, nc * 8, cudaMemcpyHostToDevice, ws->stream));
             u64 total = 0;
-            rows_device(m, ws, ws->d_rows.p, nc, 8, &total);
+            rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             launches += ws->launches; probes += ws->last_probes; touches += ws->last_touches;
             if (base) {
                 add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
@@ -844,7 +851,7 @@ int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uin
             CUDA_CHECK(cudaMemcpyAsync(offsets + r0, ws->d_offsets.p, (nc + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
             if (base + total > cols_capacity || (total && !cols)) fits = false;
             if (fits && total)
-                CUDA_CHECK(cudaMemcpyAsync(cols + base, ws->d_out.p, total * 8, cudaMemcpyDeviceToHost, ws->stream));
+                CUDA_CHECK(cudaMemcpyAsync(cols + base * col_bytes, ws->d_out.p, total * col_bytes, cudaMemcpyDeviceToHost, ws->stream));
             base += total;
             if (r0 + kPipelineChunk >= n) break;
         }
@@ -863,6 +870,16 @@ int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uin
         if (ws) m->release(ws);
     return rc;
     GGQ_CATCH
+}
+
+int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint64_t *cols,
+                      uint64_t cols_capacity, uint64_t *n_cols) {
+    return get_rows_into(m, rows, n, offsets, cols, cols_capacity, n_cols, 8);
+}
+
+int ggq_get_rows_into_u32(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint32_t *cols,
+                          uint64_t cols_capacity, uint64_t *n_cols) {
+    return get_rows_into(m, rows, n, offsets, cols, cols_capacity, n_cols, 4);
 }
 
 // device part of count_labels: counts (u64 x num_columns) in ws->d_counts

@@ -1,18 +1,17 @@
 // Hand-written sm_100a kernels of the query engine.  HBM-bound integer work: no tensor cores.
 //
 //   pack_plain_kernel / chunk_sum_kernel / lane_scan_kernel / header_kernel   build the slot arena
-//   brwt_rows_kernel      K1  batched BRWT::get_row  (BRWT.cpp:26-53)
+//   brwt_rows_kernel      K1  batched BRWT::get_row  (BRWT.cpp:26-53)  -> ggq_rows.cuh
 //   gather_rows_kernel        temp chunks -> ordered CSR
 //   brwt_get_kernel       K2  BRWT::get              (BRWT.cpp:9-24)
 //   lane_enumerate_kernel K3a leaf call_ones         (BRWT.cpp:65-71)
 //   lane_select_kernel    K3b rows[i] = select1(rows[i]+1) at one ancestor (BRWT.cpp:81-83)
 #pragma once
 #include "ggq_device.cuh"
+#include "ggq_rows.cuh"
 
 namespace ggq {
 
-constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
-constexpr int kItemsPerIter = 16;      // work items a warp probes per iteration (2 lanes each, 2 children per lane)
 
 // ------------------------------------------------------------------------------------------
 // Arena construction
@@ -156,214 +155,6 @@ header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, Chun
             my_sel[(ones + (1ull << kSelectShift) - 1) >> kSelectShift] = u32(b);
         }
     }
-}
-
-// ------------------------------------------------------------------------------------------
-// K1: batched get_row.  The engine first orders the batch by row id (radix sort of (row, query index)
-// pairs): rank1 is monotone, so sorted rows walk EVERY node vector front to back — TLB- and DRAM-page-local
-// instead of 33 random pages per row — and results are written back under the caller's query index.
-// One warp owns a batch of `rb` consecutive (sorted) rows and a private LIFO stack of work items
-// (t, group, r) = "probe the sibling group `group` at index r for query t".  Per iteration the warp pops up
-// to 16 items; 2 lanes serve one item, each reading with ONE 256-bit load the 32-byte sector that holds the
-// slots of two children (one coalesced 64-byte block per item).  A set bit of a leaf child marks the column's
-// DFS rank in the row's bitmap (shared memory); a set bit of an internal child pushes the child's first group
-// with r' = rank1(r) - 1.  When the stack drains, the bitmaps are enumerated in rank order, which IS the
-// reference's output order (DFS over child_nodes_, BRWT.cpp:45-50).
-// ------------------------------------------------------------------------------------------
-struct RowsArgs {
-    const u64 *rows;          // query row ids in PROCESSING order (sorted by the engine, or the caller's order)
-    const u32 *perm;          // processing position -> caller's query index (null: identity)
-    u64 n;                    // number of queries
-    u32 *tmp_cols;            // unordered chunk arena
-    u64 tmp_cap;
-    u64 *cursor;              // [0] chunk cursor, [1] batch ticket, [2] probe counter, [3] (node,row) touches
-    u64 *row_tmp_off;         // per query (caller's index): start in tmp_cols
-    u32 *row_cnt;             // per query (caller's index): number of columns
-    u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
-    u32 cap_s, cap_spill;     // shared / global stack capacity per warp
-    u32 bm_words;             // bitmap words per row
-    u32 rb;                   // rows per warp batch
-    int *err;
-};
-
-// Stack access.  SPILL = false: the shared-memory stack is provably large enough (simulate_stack), no checks.
-template <bool SPILL>
-__device__ __forceinline__ u64 stk_get(const u64 *s_stack, const u64 *spill, u32 cap_s, u32 i) {
-    if (!SPILL) return s_stack[i];
-    return i < cap_s ? s_stack[i] : spill[i - cap_s];
-}
-template <bool SPILL>
-__device__ __forceinline__ void stk_set(u64 *s_stack, u64 *spill, u32 cap_s, u32 cap_total, u32 i, u64 v, int *err) {
-    if (!SPILL) { s_stack[i] = v; return; }
-    if (i < cap_s) s_stack[i] = v;
-    else if (i < cap_total) spill[i - cap_s] = v;
-    else *err = 1;
-}
-
-// One child of a probed group: bit test; a set leaf bit marks the row's bitmap, a set internal bit yields the
-// work item of the child's first group with r' = rank1(r) - 1 (BRWT.cpp:43-50).
-__device__ __forceinline__ bool visit_child(const Img &img, const uint4 &s, u32 bit, u64 blk, u32 li, u32 info,
-                                            bool multi_sb, u32 t, u32 *s_bm_row, u64 *child_item) {
-    if (!slot_test(s, bit)) return false;
-    if (info & kLeafFlag) {
-        if (info == kRemoteLane) return false;   // held by another shard (column sharding)
-        u32 rank = info & ~kLeafFlag;
-        if (!img.multi_leaf) {
-            atomicOr(s_bm_row + (rank >> 5), 1u << (rank & 31));
-        } else {
-            u32 ncol = __ldg(img.lane_aux + li);
-            for (u32 k = 0; k < ncol; ++k, ++rank) atomicOr(s_bm_row + (rank >> 5), 1u << (rank & 31));
-        }
-        return false;
-    }
-    u64 ones = u64(s.x) + slot_rank_before(s, bit);
-    if (multi_sb) ones += img.sb_base[img.lane_sb_off[li] + (blk >> kSuperShift)];   // entry 0 of a lane is 0
-    *child_item = (ones << kItemRShift) | (u64(t) << kItemGroupBits) | info;
-    return true;
-}
-
-template <bool SPILL>
-__global__ void __launch_bounds__(kRowsWarps * 32)
-brwt_rows_kernel(Img img, RowsArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u32 lt_mask = (1u << lane) - 1u;
-    u64 *s_stack = reinterpret_cast<u64 *>(smem_raw) + size_t(warp) * a.cap_s;
-    u32 *s_bm = reinterpret_cast<u32 *>(smem_raw + size_t(kRowsWarps) * a.cap_s * 8) + size_t(warp) * a.rb * a.bm_words;
-    u64 *spill = SPILL ? a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill : nullptr;
-    const u32 cap_total = a.cap_s + a.cap_spill;
-    const u32 bm_total = a.rb * a.bm_words;
-    const u32 idx = lane >> 1, half = lane & 1;   // 2 lanes serve one item; lane `half` owns children 2*half, 2*half+1
-    u32 probes = 0;    // lane 0
-    u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
-
-    for (;;) {
-        u64 batch = 0;
-        if (lane == 0) batch = atomicAdd(a.cursor + 1, 1ull);
-        batch = __shfl_sync(0xffffffffu, batch, 0);
-        const u64 row0 = batch * a.rb;
-        if (row0 >= a.n) break;
-        const u32 nr = u32(min(u64(a.rb), a.n - row0));
-
-        for (u32 i = lane; i < bm_total; i += 32) s_bm[i] = 0;
-        // seed the stack with the root probes of the valid rows
-        u64 r = 0;
-        bool valid = false;
-        if (lane < nr) { r = a.rows[row0 + lane]; valid = r < img.n_rows; }
-        const u32 vmask = __ballot_sync(0xffffffffu, valid);
-        if (valid) s_stack[__popc(vmask & lt_mask)] = (r << kItemRShift) | (u64(lane) << kItemGroupBits);
-        u32 top = __popc(vmask);
-        __syncwarp();
-
-        while (top > 0) {
-            const u32 c = min(top, u32(kItemsPerIter));
-            const bool active = idx < c;
-            u64 item = 0;
-            if (active) item = stk_get<SPILL>(s_stack, spill, a.cap_s, top - 1 - idx);
-            __syncwarp();
-            const u32 g = u32(item) & (kMaxGroups - 1);
-            const u32 t = u32(item >> kItemGroupBits) & (kMaxRowsPerWarp - 1);
-            const u64 rr = item >> kItemRShift;
-            bool push_cont = false, push0 = false, push1 = false;
-            u64 item0 = 0, item1 = 0;
-            if (active) {
-                const uint4 rec = __ldg(img.group_rec + 2 * g + half);
-                const u32 sl = (rec.y >> (kGhStrideShift - 32)) & 3u;
-                const u32 cnt = (rec.y >> (kGhCntShift - 32)) & 7u;
-                push_cont = half == 0 && ((rec.y >> (kGhMoreShift - 32)) & 1u);
-                const bool multi_sb = (rec.y >> (kGhSuperShift - 32)) & 1u;
-                if (half == 0) touches += cnt;
-                if (2 * half < cnt) {
-                    u64 blk; u32 bit;
-                    div96(rr, blk, bit);
-                    const u64 base = (u64(rec.y & 0xffu) << 32) | rec.x;
-                    const u64 si = base + (blk << sl) + 2 * half;   // slot of child 2*half
-                    uint4 s0, s1;
-                    ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
-                    if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
-                    u32 *bm_row = s_bm + t * a.bm_words;
-                    push0 = visit_child(img, s0, bit, blk, g * 4 + 2 * half, rec.z, multi_sb, t, bm_row, &item0);
-                    if (2 * half + 1 < cnt)
-                        push1 = visit_child(img, s1, bit, blk, g * 4 + 2 * half + 1, rec.w, multi_sb, t, bm_row, &item1);
-                }
-            }
-            const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
-            const u32 m0 = __ballot_sync(0xffffffffu, push0);
-            const u32 m1 = __ballot_sync(0xffffffffu, push1);
-            u32 pos = top - c;
-            if (push_cont)
-                stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
-            pos += __popc(cont_mask);
-            if (push0) stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(m0 & lt_mask), item0, a.err);
-            pos += __popc(m0);
-            if (push1) stk_set<SPILL>(s_stack, spill, a.cap_s, cap_total, pos + __popc(m1 & lt_mask), item1, a.err);
-            top = pos + __popc(m1);
-            if (SPILL && top > cap_total) top = cap_total;  // overflow already flagged in *err
-            probes += c;
-            __syncwarp();
-        }
-
-        // ---- emit: per-row counts, one chunk allocation per batch, then the column ids in rank order
-        u32 my_cnt = 0;   // lane t holds the count of row t
-        u32 total = 0;
-        for (u32 t = 0; t < nr; ++t) {
-            u32 c = 0;
-            for (u32 w = lane; w < a.bm_words; w += 32) c += __popc(s_bm[t * a.bm_words + w]);
-            c = __reduce_add_sync(0xffffffffu, c);
-            if (lane == t) my_cnt = c;
-            total += c;
-        }
-        u64 base = 0;
-        if (lane == 0 && total) base = atomicAdd(a.cursor, u64(total));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        // exclusive prefix of my_cnt over lanes
-        u32 pre = my_cnt;
-        for (int o = 1; o < 32; o <<= 1) {
-            u32 v = __shfl_up_sync(0xffffffffu, pre, o);
-            if (lane >= o) pre += v;
-        }
-        pre -= my_cnt;
-        if (lane < nr) {
-            const u64 q = a.perm ? u64(a.perm[row0 + lane]) : row0 + lane;
-            a.row_tmp_off[q] = base + pre;
-            a.row_cnt[q] = my_cnt;
-        }
-        const bool fits = base + total <= a.tmp_cap;
-        if (fits && total) {
-            for (u32 t = 0; t < nr; ++t) {
-                u64 pos = base + __shfl_sync(0xffffffffu, pre, t);
-                if (__shfl_sync(0xffffffffu, my_cnt, t) == 0) continue;
-                for (u32 w0 = 0; w0 < a.bm_words; w0 += 32) {
-                    u32 w = w0 + lane;
-                    u32 bits = w < a.bm_words ? s_bm[t * a.bm_words + w] : 0u;
-                    if (!__any_sync(0xffffffffu, bits != 0)) continue;
-                    const u32 c = __popc(bits);
-                    if (!__any_sync(0xffffffffu, c > 1)) {   // common case: at most one id per word
-                        const u32 nz = __ballot_sync(0xffffffffu, c != 0);
-                        if (c) a.tmp_cols[pos + __popc(nz & lt_mask)] = __ldg(img.leaf_col + w * 32 + __ffs(bits) - 1);
-                        pos += __popc(nz);
-                        continue;
-                    }
-                    u32 inc = c;
-                    for (int o = 1; o < 32; o <<= 1) {
-                        u32 v = __shfl_up_sync(0xffffffffu, inc, o);
-                        if (lane >= o) inc += v;
-                    }
-                    u64 p = pos + inc - c;
-                    while (bits) {
-                        u32 b = __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        a.tmp_cols[p++] = __ldg(img.leaf_col + w * 32 + b);
-                    }
-                    pos += __shfl_sync(0xffffffffu, inc, 31);
-                }
-            }
-        }
-        __syncwarp();
-    }
-    if (lane == 0 && probes) atomicAdd(a.cursor + 2, u64(probes));
-    touches = __reduce_add_sync(0xffffffffu, touches);
-    if (lane == 0 && touches) atomicAdd(a.cursor + 3, u64(touches));
 }
 
 // CSR assembly in the caller's query order: 8 lanes copy one row from its chunk in the arena.

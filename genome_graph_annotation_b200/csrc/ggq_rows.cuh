@@ -1,0 +1,314 @@
+// K1 (v3): batched BRWT::get_row (annotation/hierarchical_annotation/BRWT.cpp:26-53) for sm_100a.
+//
+// The engine first orders the batch by row id (radix sort of (row, query index) pairs): rank1 is monotone, so
+// sorted rows walk EVERY node vector front to back — TLB- and DRAM-page-local instead of 33 random pages per
+// row — and results are written back under the caller's query index.
+//
+// One warp owns a tile of `rb` consecutive (sorted) rows and a private LIFO stack of work items
+// (t, group, r) = "probe the sibling group `group` at index r for row t of the tile".  Per iteration the warp
+// pops up to 16 items; 2 lanes serve one item, each reading with ONE 256-bit load the 32-byte sector that
+// holds the slots of two children (one coalesced 64-byte block per item).  A set bit of a leaf child marks the
+// column's DFS rank in the row's bitmap (shared memory) and bumps the row's counter; a set bit of an internal
+// child pushes the child's first group with r' = rank1(r) - 1.  When the stack drains, the bitmaps of the tile
+// are scanned once in (row, word) order — which IS the reference's output order (DFS over child_nodes_,
+// BRWT.cpp:45-50) — non-zero words go through a 64-entry warp queue and are expanded 32 at a time.
+//
+// v3 vs v2 (profiles/r01: the kernel is instruction-issue bound, 27 warp instructions per probe): the two
+// children of a lane are handled without divergent branches (rank computed unconditionally, leaf marks
+// predicated), all shared-memory traffic uses precomputed 32-bit shared addresses, per-row counts come from
+// shared-memory counters bumped during the descent (no counting pass), the bitmaps are cleared while they are
+// read (no zeroing pass), and the emit works on non-zero words only instead of on every (row, 32-word chunk).
+#pragma once
+#include "ggq_device.cuh"
+
+namespace ggq {
+
+constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
+constexpr int kItemsPerIter = 16;      // work items a warp probes per iteration (2 lanes each, 2 children per lane)
+constexpr int kEmitQueue = 64;         // entries of the per-warp queue of non-zero bitmap words
+constexpr int kRowCounters = 16;       // per-warp row counters (>= kMaxRowsPerWarp)
+
+struct RowsArgs {
+    const u64 *rows;          // query row ids in PROCESSING order (sorted by the engine, or the caller's order)
+    const u32 *perm;          // processing position -> caller's query index (null: identity)
+    u64 n;                    // number of queries
+    u32 *tmp_cols;            // unordered chunk arena
+    u64 tmp_cap;
+    u64 *cursor;              // [0] chunk cursor, [1] tile ticket, [2] probe counter, [3] (node,row) touches
+    u64 *row_tmp_off;         // per query (caller's index): start in tmp_cols
+    u32 *row_cnt;             // per query (caller's index): number of columns
+    u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
+    u32 cap_s, cap_spill;     // shared / global stack capacity per warp
+    u32 bm_words;             // bitmap words per row
+    u32 rb;                   // rows per warp tile
+    int *err;
+};
+
+// Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][queues: warps x 64 u64][per warp: rb*bm_words
+// bitmap words + 16 row counters (u32)]
+inline size_t rows_smem_bytes(u32 cap_s, u32 rb, u32 bm_words) {
+    return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(kEmitQueue) * 8 + (size_t(rb) * bm_words + kRowCounters) * 4);
+}
+
+// Shared memory through 32-bit shared-window addresses (computed once per kernel).
+__device__ __forceinline__ u64 lds64(u32 a) {
+    u64 v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts64(u32 a, u64 v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(a), "l"(v) : "memory"); }
+__device__ __forceinline__ u32 lds32(u32 a) {
+    u32 v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(u32 a, u32 v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void reds_or(u32 a, u32 v) { asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void reds_add(u32 a, u32 v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+template <bool SPILL>
+__device__ __forceinline__ u64 stk_get(u32 stk, const u64 *spill, u32 cap_s, u32 i) {
+    if (!SPILL) return lds64(stk + i * 8);
+    return i < cap_s ? lds64(stk + i * 8) : spill[i - cap_s];
+}
+template <bool SPILL>
+__device__ __forceinline__ void stk_set(u32 stk, u64 *spill, u32 cap_s, u32 cap_total, u32 i, u64 v, int *err) {
+    if (!SPILL) { sts64(stk + i * 8, v); return; }
+    if (i < cap_s) sts64(stk + i * 8, v);
+    else if (i < cap_total) spill[i - cap_s] = v;
+    else *err = 1;
+}
+
+// ones strictly before position `bit` of the slot, given the word holding it (wsel = bit / 32, below = mask of
+// the lower positions inside that word), plus the slot's rank header
+__device__ __forceinline__ u32 slot_ones_before(const uint4 &s, u32 w, u32 wsel, u32 below) {
+    u32 c = s.x + __popc(w & below);
+    if (wsel >= 1) c += __popc(s.y);
+    if (wsel >= 2) c += __popc(s.z);
+    return c;
+}
+
+// Set bit of a leaf child: mark the DFS ranks of its columns in the row's bitmap, bump the row's counter.
+template <bool MULTI_LEAF>
+__device__ __forceinline__ void mark_leaf(const Img &img, u32 info, u32 li, u32 bm_row, u32 cnt_addr) {
+    u32 rank = info & ~kLeafFlag;
+    if (!MULTI_LEAF) {
+        reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
+        reds_add(cnt_addr, 1u);
+    } else {
+        const u32 ncol = __ldg(img.lane_aux + li);
+        for (u32 k = 0; k < ncol; ++k, ++rank) reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
+        reds_add(cnt_addr, ncol);
+    }
+}
+
+// Expand `cnt` (<= 32) queued non-zero bitmap words (entry = word index within the row << 32 | bits), in queue
+// order, to column ids at tmp_cols[pos...] (only if `store`); returns the number of ids.
+__device__ __forceinline__ u32 emit_flush(const Img &img, u32 que, u32 cnt, u32 lane, u32 lt_mask, u32 *tmp_cols, u64 pos,
+                                          bool store) {
+    u64 e = 0;
+    if (lane < cnt) e = lds64(que + lane * 8);
+    u32 bits = u32(e);
+    const u32 w = u32(e >> 32);
+    const u32 c = __popc(bits);
+    if (!__any_sync(0xffffffffu, c > 1)) {   // common case: one id per word
+        const u32 nz = __ballot_sync(0xffffffffu, c != 0);
+        if (c && store) tmp_cols[pos + __popc(nz & lt_mask)] = __ldg(img.leaf_col + w * 32 + __ffs(bits) - 1);
+        return __popc(nz);
+    }
+    u32 inc = c;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    u64 p = pos + inc - c;
+    while (bits && store) {
+        const u32 b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        tmp_cols[p++] = __ldg(img.leaf_col + w * 32 + b);
+    }
+    return __shfl_sync(0xffffffffu, inc, 31);
+}
+
+template <bool SPILL, bool MULTI_LEAF>
+__global__ void __launch_bounds__(kRowsWarps * 32)
+brwt_rows_kernel(Img img, RowsArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32 lt_mask = (1u << lane) - 1u;
+    const u32 bm_total = a.rb * a.bm_words;
+    const u32 smem0 = u32(__cvta_generic_to_shared(smem_raw));
+    u32 stk = smem0 + warp * a.cap_s * 8;
+    u32 que = smem0 + kRowsWarps * a.cap_s * 8 + warp * (kEmitQueue * 8);
+    u32 bm = smem0 + kRowsWarps * (a.cap_s * 8 + kEmitQueue * 8) + warp * ((bm_total + kRowCounters) * 4);
+    u32 cnt0 = bm + bm_total * 4;
+    // keep the per-warp bases in registers: ptxas otherwise rematerialises them (S2R + IMAD chains) inside the
+    // descent loop, which is instruction-issue bound; a shuffle is opaque to it
+    stk = __shfl_sync(0xffffffffu, stk, lane);
+    que = __shfl_sync(0xffffffffu, que, lane);
+    bm = __shfl_sync(0xffffffffu, bm, lane);
+    cnt0 = __shfl_sync(0xffffffffu, cnt0, lane);
+    const u32 bm_row_bytes = a.bm_words * 4;
+    u64 *spill = SPILL ? a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill : nullptr;
+    const u32 cap_total = a.cap_s + a.cap_spill;
+    u32 idx = lane >> 1, half = lane & 1;   // 2 lanes serve one item; lane `half` owns children 2*half, 2*half+1
+    const bool short_rows = img.n_rows < (1ull << 37);   // r / 96 by one 32-bit mulhi
+    u32 probes = 0;    // lane 0
+    u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
+
+    // bitmaps and counters start clean; every tile leaves them clean
+    for (u32 i = lane; i < bm_total + kRowCounters; i += 32) sts32(bm + i * 4, 0);
+    __syncwarp();
+
+    for (;;) {
+        u64 tile = 0;
+        if (lane == 0) tile = atomicAdd(a.cursor + 1, 1ull);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        const u64 row0 = tile * a.rb;
+        if (row0 >= a.n) break;
+        const u32 nr = u32(min(u64(a.rb), a.n - row0));
+
+        // seed the stack with the root probes of the valid rows
+        u64 r = 0;
+        bool valid = false;
+        if (lane < nr) { r = a.rows[row0 + lane]; valid = r < img.n_rows; }
+        const u32 vmask = __ballot_sync(0xffffffffu, valid);
+        if (valid) sts64(stk + __popc(vmask & lt_mask) * 8, (r << kItemRShift) | (u64(lane) << kItemGroupBits));
+        u32 top = __popc(vmask);
+        __syncwarp();
+
+        while (top > 0) {
+            const u32 c = min(top, u32(kItemsPerIter));
+            const bool active = idx < c;
+            u64 item = 0;
+            if (active) item = stk_get<SPILL>(stk, spill, a.cap_s, top - 1 - idx);
+            __syncwarp();
+            bool push_cont = false, push0 = false, push1 = false;
+            u64 item0 = 0, item1 = 0;
+            if (active) {
+                const u32 ilo = u32(item);
+                const u32 g = ilo & (kMaxGroups - 1);
+                const u32 tq = ilo & ((kMaxRowsPerWarp - 1) << kItemGroupBits);   // t, in place
+                const uint4 rec = __ldg(img.group_rec + 2 * g + half);
+                const u32 sl = (rec.y >> (kGhStrideShift - 32)) & 3u;
+                const u32 cnt = (rec.y >> (kGhCntShift - 32)) & 7u;
+                push_cont = half == 0 && ((rec.y >> (kGhMoreShift - 32)) & 1u);
+                if (half == 0) touches += cnt;
+                if (2 * half < cnt) {
+                    u64 blk; u32 bit;
+                    if (short_rows) {
+                        const u32 q = __umulhi(u32(item >> (kItemRShift + 5)), 0xAAAAAAABu) >> 1;
+                        blk = q;
+                        bit = u32(item >> kItemRShift) - q * kSlotBits;
+                    } else {
+                        const u64 rr = item >> kItemRShift;
+                        blk = rr / kSlotBits;
+                        bit = u32(rr - blk * kSlotBits);
+                    }
+                    const u64 si = ((u64(rec.y & 0xffu) << 32) | rec.x) + (blk << sl) + 2 * half;   // slot of child 2*half
+                    uint4 s0, s1;
+                    ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
+                    if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
+                    const u32 wsel = bit >> 5, sh = bit & 31, below = (1u << sh) - 1u;
+                    const u32 w0 = wsel == 0 ? s0.y : (wsel == 1 ? s0.z : s0.w);
+                    const u32 w1 = wsel == 0 ? s1.y : (wsel == 1 ? s1.z : s1.w);
+                    const bool set0 = (w0 >> sh) & 1u;
+                    const bool set1 = (2 * half + 1 < cnt) && ((w1 >> sh) & 1u);
+                    const bool leaf0 = int(rec.z) < 0, leaf1 = int(rec.w) < 0;
+                    const u32 t = tq >> kItemGroupBits;
+                    const u32 bm_row = bm + t * bm_row_bytes;
+                    if (set0 && leaf0 && rec.z != kRemoteLane) mark_leaf<MULTI_LEAF>(img, rec.z, g * 4 + 2 * half, bm_row, cnt0 + t * 4);
+                    if (set1 && leaf1 && rec.w != kRemoteLane) mark_leaf<MULTI_LEAF>(img, rec.w, g * 4 + 2 * half + 1, bm_row, cnt0 + t * 4);
+                    push0 = set0 && !leaf0;
+                    push1 = set1 && !leaf1;
+                    // r' = rank1(r) - 1 = ones strictly before r (BRWT.cpp:43-50)
+                    u64 ones0 = slot_ones_before(s0, w0, wsel, below);
+                    u64 ones1 = slot_ones_before(s1, w1, wsel, below);
+                    if ((rec.y >> (kGhSuperShift - 32)) & 1u) {     // some lane of the group spans several superblocks
+                        const u64 sb = blk >> kSuperShift;
+                        if (push0) ones0 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half] + sb];   // entry 0 of a lane is 0
+                        if (push1) ones1 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half + 1] + sb];
+                    }
+                    item0 = (ones0 << kItemRShift) | tq | rec.z;
+                    item1 = (ones1 << kItemRShift) | tq | rec.w;
+                }
+            }
+            const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
+            const u32 m0 = __ballot_sync(0xffffffffu, push0);
+            const u32 m1 = __ballot_sync(0xffffffffu, push1);
+            u32 pos = top - c;
+            if (push_cont)
+                stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
+            pos += __popc(cont_mask);
+            if (push0) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m0 & lt_mask), item0, a.err);
+            pos += __popc(m0);
+            if (push1) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m1 & lt_mask), item1, a.err);
+            top = pos + __popc(m1);
+            if (SPILL && top > cap_total) top = cap_total;  // overflow already flagged in *err
+            probes += c;
+            __syncwarp();
+        }
+
+        // ---- emit: per-row counts from the counters, one chunk allocation per tile, then the column ids in
+        // (row, rank) order
+        u32 my_cnt = 0;   // lane t holds the count of row t
+        if (lane < kRowCounters) { my_cnt = lds32(cnt0 + lane * 4); sts32(cnt0 + lane * 4, 0); }
+        const u32 total = __reduce_add_sync(0xffffffffu, my_cnt);
+        u64 base = 0;
+        if (lane == 0 && total) base = atomicAdd(a.cursor, u64(total));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        u32 pre = my_cnt;   // exclusive prefix of my_cnt over lanes
+        #pragma unroll
+        for (int o = 1; o < kRowCounters; o <<= 1) {
+            const u32 v = __shfl_up_sync(0xffffffffu, pre, o);
+            if (lane >= o) pre += v;
+        }
+        pre -= my_cnt;
+        if (lane < nr) {
+            const u64 q = a.perm ? u64(a.perm[row0 + lane]) : row0 + lane;
+            a.row_tmp_off[q] = base + pre;
+            a.row_cnt[q] = my_cnt;
+        }
+        if (total) {
+            const bool fits = base + total <= a.tmp_cap;   // else: the engine grows the arena and reruns
+            const u32 rows_mask = __ballot_sync(0xffffffffu, my_cnt != 0);
+            u64 pos = base;
+            u32 q = 0;
+            for (u32 t = 0; t < nr; ++t) {
+                if (!((rows_mask >> t) & 1u)) continue;
+                const u32 bm_row = bm + t * bm_row_bytes;
+                for (u32 w0 = 0; w0 < a.bm_words; w0 += 32) {
+                    const u32 w = w0 + lane;
+                    const u32 bits = w < a.bm_words ? lds32(bm_row + w * 4) : 0u;
+                    const u32 nz = __ballot_sync(0xffffffffu, bits != 0);
+                    if (!nz) continue;
+                    if (bits) {
+                        sts32(bm_row + w * 4, 0);
+                        sts64(que + (q + __popc(nz & lt_mask)) * 8, (u64(w) << 32) | bits);
+                    }
+                    q += __popc(nz);
+                    if (q >= 32) {
+                        __syncwarp();
+                        pos += emit_flush(img, que, 32, lane, lt_mask, a.tmp_cols, pos, fits);
+                        q -= 32;
+                        u64 e = 0;
+                        if (lane < q) e = lds64(que + (32 + lane) * 8);
+                        __syncwarp();
+                        if (lane < q) sts64(que + lane * 8, e);
+                    }
+                }
+            }
+            if (q) {
+                __syncwarp();
+                emit_flush(img, que, q, lane, lt_mask, a.tmp_cols, pos, fits);
+            }
+        }
+        __syncwarp();
+    }
+    if (lane == 0 && probes) atomicAdd(a.cursor + 2, u64(probes));
+    touches = __reduce_add_sync(0xffffffffu, touches);
+    if (lane == 0 && touches) atomicAdd(a.cursor + 3, u64(touches));
+}
+
+}  // namespace ggq

@@ -113,6 +113,11 @@ void ggq_rows_result_free(ggq_rows_result *r);
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
                       uint64_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
 
+/* Compact variant: column ids as u32 (the engine holds < 2^31 columns, so nothing is lost) — halves the
+ * device->host traffic, which is what bounds ggq_get_rows_into on PCIe (DESIGN.md "Measurement"). */
+int ggq_get_rows_into_u32(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
+                          uint32_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
+
 /* counts[j] = number of t with column j set in row rows[t] (duplicates counted) — the histogram
  * StaticBinRelAnnotator::count_labels builds with one get_row per index (annotation/annotate_static.cpp:149-162),
  * i.e. what get_labels(indices, ratio) / get_top_labels threshold (annotate_static.cpp:71-94, annotate.cpp:57-83).

@@ -112,6 +112,11 @@ def test_pipelined_host_api_matches_single_shot(ggq):
             eo, ec = gm.get_rows_csr(rows[lo:hi])
             assert np.array_equal(off[lo:hi + 1] - off[lo], eo)
             assert np.array_equal(cols[int(off[lo]):int(off[hi])], ec)
+        # compact u32 ids: same CSR
+        cols32 = np.empty(cols.size, np.uint32)
+        off32 = np.empty_like(off)
+        assert gm.get_rows_into(rows, off32, cols32) == total
+        assert np.array_equal(off32, off) and np.array_equal(cols32[:total], cols[:total].astype(np.uint32))
         # capacity too small: error, but the total is still reported
         small = np.empty(10, np.uint64)
         with pytest.raises(ggq.GgqError):
