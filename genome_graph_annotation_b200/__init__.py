@@ -79,6 +79,9 @@ def lib():
         "ggq_rows_count": (C.c_uint64, [vp]),
         "ggq_rows_result_free": (None, [vp]),
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_get_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p]),
+        "ggq_get_top_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u64p, u64p, u64p]),
+        "ggq_get_labels_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p, C.c_uint64, u64p]),
         "ggq_get_rows_into_u32": (C.c_int, [vp, u64p, C.c_uint64, u64p, C.c_void_p, C.c_uint64, u64p]),
         "ggq_count_labels": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
         "ggq_count_labels_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.POINTER(vp)]),
@@ -340,6 +343,40 @@ class GpuMatrix:
         out = np.zeros(max(int(self.num_columns), 1), np.uint64)
         _check(lib().ggq_count_labels(self._h, rp, rows.size, out.ctypes.data_as(u64p)))
         return out[:int(self.num_columns)]
+
+    def get_labels(self, rows, presence_ratio=0.0):
+        """Columns present in at least ceil(len(rows) * ratio) of the rows (ratio 0: in any), ascending, with
+        their counts (ggq_get_labels; StaticBinRelAnnotator::get_labels(indices, ratio))."""
+        rows, rp = _u64(rows)
+        m = max(int(self.num_columns), 1)
+        cols, cnt, k = np.zeros(m, np.uint64), np.zeros(m, np.uint64), C.c_uint64()
+        _check(lib().ggq_get_labels(self._h, rp, rows.size, float(presence_ratio), cols.ctypes.data_as(u64p),
+                                    cnt.ctypes.data_as(u64p), C.byref(k)))
+        return cols[:k.value], cnt[:k.value]
+
+    def get_labels_batch(self, rows, query_offsets, presence_ratio=0.0, capacity=None):
+        """get_labels for many queries in one launch (ggq_get_labels_batch): query q owns
+        rows[query_offsets[q]:query_offsets[q+1]].  Returns (label_offsets, cols, counts)."""
+        rows, rp = _u64(rows)
+        qo, qp = _u64(query_offsets)
+        nq = qo.size - 1
+        if capacity is None:
+            capacity = max(nq * int(self.num_columns), 1)
+        loff = np.zeros(nq + 1, np.uint64)
+        cols, cnt, k = np.zeros(capacity, np.uint64), np.zeros(capacity, np.uint64), C.c_uint64()
+        _check(lib().ggq_get_labels_batch(self._h, rp, qp, nq, float(presence_ratio), loff.ctypes.data_as(u64p),
+                                          cols.ctypes.data_as(u64p), cnt.ctypes.data_as(u64p), capacity, C.byref(k)))
+        return loff, cols[:k.value], cnt[:k.value]
+
+    def get_top_labels(self, rows, num_top):
+        """The num_top most frequent columns over the multiset `rows`, decreasing count, ties by ascending
+        column (ggq_get_top_labels; MultiLabelEncoded::get_top_labels)."""
+        rows, rp = _u64(rows)
+        m = max(min(int(self.num_columns), int(num_top)), 1)
+        cols, cnt, k = np.zeros(m, np.uint64), np.zeros(m, np.uint64), C.c_uint64()
+        _check(lib().ggq_get_top_labels(self._h, rp, rows.size, int(num_top), cols.ctypes.data_as(u64p),
+                                        cnt.ctypes.data_as(u64p), C.byref(k)))
+        return cols[:k.value], cnt[:k.value]
 
     def slice_rows(self, rows):
         rows, rp = _u64(rows)

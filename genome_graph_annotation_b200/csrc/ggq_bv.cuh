@@ -4,7 +4,7 @@
 //   RankedBits ("rb", used by stat and by the Elias-Fano high part):
 //       64-byte blocks = { u64 ones_before_block, u64 data[7] }  (448 positions, 12.5 % overhead);
 //       bit test + rank = ONE 64-byte transaction.  select1 / select0: one u32 sample per 2^s ones
-//       (zeros), s chosen per vector so that consecutive samples are <= ~8 blocks apart, then a
+//       (zeros), s chosen per vector so that consecutive samples are ~2 blocks apart, then a
 //       <= 3-step binary search over block headers and an in-block __popcll / __fns scan.
 //   stat : rb over the plain bits            (reference: sdsl rank_support_v5 + select_support_mcl,
 //                                             bit_vector.cpp:281-304, rank_support_v5.hpp:116-134)
@@ -27,7 +27,7 @@ namespace ggq {
 
 constexpr u32 kRbBits = 448;          // positions per 64-byte block
 constexpr u32 kRbWords = 8;           // u64 words per block (header + 7 data)
-constexpr u32 kRbSpanBlocks = 8;      // target distance between consecutive select samples
+constexpr u32 kRbSpanBlocks = 2;      // target distance (blocks) between consecutive select samples
 
 struct RbImg {
     const u64 *blk;     // n_blk * 8 words

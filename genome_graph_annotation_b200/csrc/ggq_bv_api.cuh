@@ -106,6 +106,61 @@ __global__ void __launch_bounds__(256) stat_rank_kernel(RbImg v, const u64 *q, u
     }
 }
 
+// select1: 2 lanes per query.  Sample (block of every 2^s-th one; samples ~2 blocks apart) -> at most a couple of
+// 8-byte header probes -> the block itself as two 32-byte sectors (256-bit loads), the in-block select split
+// between the two lanes.  Out-of-range k (undefined in the reference, assert only) yields n_bits.
+__global__ void __launch_bounds__(256) stat_select_kernel(RbImg v, const u64 *q, u64 n, u64 *out) {
+    const u32 half = threadIdx.x & 1;
+    const u64 stride = (u64(gridDim.x) * blockDim.x) >> 1;
+    for (u64 t0 = (u64(blockIdx.x) * blockDim.x + (threadIdx.x & ~31u)) >> 1; t0 < n; t0 += stride) {
+        const u64 t = t0 + ((threadIdx.x & 31) >> 1);
+        const u64 x = t < n ? q[t] : 0;
+        const bool ok = t < n && x >= 1 && x <= v.n_ones;
+        u64 res = v.n_bits;
+        u64 lo = 0, k0 = 0;
+        if (ok) {
+            k0 = x - 1;
+            const u64 si = k0 >> v.s1;
+            lo = __ldg(v.sel1 + si);
+            u64 hi = __ldg(v.sel1 + si + 1);
+            while (lo < hi) {   // last block in [lo, hi] with count-before <= k0
+                const u64 mid = (lo + hi + 1) >> 1;
+                u64 h;
+                asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u64 %0, [%1];" : "=l"(h) : "l"(v.blk + mid * kRbWords));
+                if (h <= k0) lo = mid; else hi = mid - 1;
+            }
+        }
+        u32 r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0, r5 = 0, r6 = 0, r7 = 0;
+        if (ok)
+            asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                         : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7)
+                         : "l"(v.blk + lo * kRbWords + 4 * half));
+        u64 w[4] = {u64(r1) << 32 | r0, u64(r3) << 32 | r2, u64(r5) << 32 | r4, u64(r7) << 32 | r6};
+        const u64 header = __shfl_sync(0xffffffffu, w[0], threadIdx.x & 30);   // lane 0 of the pair holds it
+        if (half == 0) w[0] = 0;                                              // not data
+        const u32 mine = __popcll(w[0]) + __popcll(w[1]) + __popcll(w[2]) + __popcll(w[3]);
+        const u32 first = __shfl_sync(0xffffffffu, mine, threadIdx.x & 30);   // ones in data words 0..2
+        if (ok) {
+            u32 k = u32(k0 - header);
+            const bool owner = half == 0 ? k < first : k >= first;
+            if (owner) {
+                if (half) k -= first;
+                const u64 base = lo * kRbBits + (half ? 3 * 64 : 0);
+#pragma unroll
+                for (u32 j = 0; j < 4; ++j) {
+                    if (half == 0 && j == 0) continue;
+                    const u32 c = __popcll(w[j]);
+                    if (k < c) { res = base + (half ? j : j - 1) * 64 + select_in_word(w[j], k); break; }
+                    k -= c;
+                }
+                out[t] = res;
+            }
+        } else if (t < n && half == 0) {
+            out[t] = res;
+        }
+    }
+}
+
 // bit i set iff mix64(seed_mul + i) < threshold  (SURVEY.md 8d portable generator)
 __global__ void synth_bits_kernel(u64 *words, u64 n_words, u64 n_bits, u64 threshold, u64 seed_mul) {
     u64 w = u64(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -159,6 +214,9 @@ struct BitVec {
         } else if (KIND == GGQ_BV_STAT && op == OP_RANK1) {
             u32 g2 = u32(std::min<u64>((2 * n + 255) / 256, u64(sms) * 32));
             stat_rank_kernel<<<g2, 256, 0, st>>>(img.stat, q, n, static_cast<u64 *>(out));
+        } else if (KIND == GGQ_BV_STAT && op == OP_SELECT1) {
+            u32 g2 = u32(std::min<u64>((2 * n + 255) / 256, u64(sms) * 32));
+            stat_select_kernel<<<g2, 256, 0, st>>>(img.stat, q, n, static_cast<u64 *>(out));
         } else
         if (op == OP_RANK1) bv_query_kernel<KIND, OP_RANK1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));
         else if (op == OP_SELECT1) bv_query_kernel<KIND, OP_SELECT1, u64><<<grid, 256, 0, st>>>(img, q, n, static_cast<u64 *>(out));

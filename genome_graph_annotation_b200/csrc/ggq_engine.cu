@@ -3,6 +3,7 @@
 // ggq_bv.cuh (bit_vector_{stat,sd,rrr} layouts).  No CPU fallback anywhere: every compute entry
 // point launches CUDA kernels or fails.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -202,6 +203,21 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
     rows_grid = u32(sm_count * per_sm);
+    // root fast path + continuation groups (see RowsArgs)
+    root_child = kNoRootFast;
+    any_more = 0;
+    for (u64 h : tree.group_hot) any_more |= u32((h >> kGhMoreShift) & 1u);
+    if (!tree.group_hot.empty()) {
+        const u64 h0 = tree.group_hot[0];
+        const u32 info0 = tree.lane_info[0];
+        if (((h0 >> kGhCntShift) & 7u) == 1 && !((h0 >> kGhMoreShift) & 1u) && !(info0 & kLeafFlag) &&
+            !env_u32("GGQ_NO_ROOT_FAST", 0)) {
+            root_child = info0;
+            root_sl = u32(h0 >> kGhStrideShift) & 3u;
+            root_multi_sb = u32((h0 >> kGhSuperShift) & 1u);
+            root_base = h0 & kGhBaseMask;
+        }
+    }
     // query ordering (see K1): sort on the top `sort_bits` bits of the row id
     row_bits = 1;
     while (row_bits < 64 && (u64(1) << row_bits) < tree.n_rows) ++row_bits;
@@ -362,21 +378,20 @@ Matrix::~Matrix() {
 // ------------------------------------------------------------------------------------------
 // get_rows on the device: rows already in ws.d_rows or caller memory
 // ------------------------------------------------------------------------------------------
-static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
+// Enqueue (no synchronisation) everything of a row query up to the point where the host must learn the result
+// size: batch ordering, descent, offset scan, control words to pinned memory.
+static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n) {
     ws->reserve_rows(n);
     cudaStream_t st = ws->stream;
+    ws->pending_sort_launches = 0;
     if (n == 0) {
         CUDA_CHECK(cudaMemsetAsync(ws->d_offsets.p, 0, 8, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        *total_out = 0;
-        ws->launches = 0;
         return;
     }
     if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
     // order the batch by row id (top sort_bits bits): monotone walks through every node vector
     const u64 *proc_rows = d_rows;
     const u32 *perm = nullptr;
-    int sort_launches = 0;
     if (m->sort_bits && n >= m->sort_min_n) {
         size_t sb = ws->sort_tmp_bytes;
         int end_bit = int(m->row_bits), begin_bit = int(m->row_bits - m->sort_bits);
@@ -385,44 +400,58 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         CUDA_CHECK(cudaGetLastError());
         proc_rows = ws->d_rows_sorted.p;
         perm = ws->d_perm.p;
-        sort_launches = 1 + (end_bit - begin_bit + 7) / 8;   // cub onesweep: histogram + one kernel per 8-bit digit
+        ws->pending_sort_launches = 1 + (end_bit - begin_bit + 7) / 8;   // cub onesweep: histogram + one kernel per 8-bit digit
+    }
+    CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+    CUDA_CHECK(cudaMemsetAsync(ws->d_err.p, 0, sizeof(int), st));
+    RowsArgs a;
+    a.rows = proc_rows; a.perm = perm; a.n = n;
+    a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
+    a.cursor = ws->d_ctrl.p;
+    a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
+    a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
+    a.bm_words = m->bm_words; a.rb = m->rb; a.err = ws->d_err.p;
+    a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
+    a.root_base = m->root_base; a.any_more = m->any_more;
+    u64 batches = (n + m->rb - 1) / m->rb;
+    u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+    CUDA_CHECK(cudaEventRecord(ws->ev0, st));
+    {
+        Img img = m->img;
+        void *kargs[] = {&img, &a};
+        CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0), dim3(grid), dim3(kRowsWarps * 32),
+                                    kargs, m->rows_smem, st));
+    }
+    CUDA_CHECK(cudaEventRecord(ws->ev1, st));
+    size_t cb = ws->cub_bytes;
+    // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
+    CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
+    cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
+    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 4 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 4, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+}
+
+// Wait for brwt_rows_begin, then assemble the CSR (enqueued, not awaited).  The chunk arena grows and the query
+// reruns if it was too small (steady state never does).
+static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
+    cudaStream_t st = ws->stream;
+    if (n == 0) {
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        *total_out = 0;
+        ws->launches = 0;
+        return;
     }
     for (int attempt = 0; attempt < 2; ++attempt) {
-        CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
-        CUDA_CHECK(cudaMemsetAsync(ws->d_err.p, 0, sizeof(int), st));
-        RowsArgs a;
-        a.rows = proc_rows; a.perm = perm; a.n = n;
-        a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
-        a.cursor = ws->d_ctrl.p;
-        a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
-        a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
-        a.bm_words = m->bm_words; a.rb = m->rb; a.err = ws->d_err.p;
-        u64 batches = (n + m->rb - 1) / m->rb;
-        u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
-        CUDA_CHECK(cudaEventRecord(ws->ev0, st));
-        {
-            Img img = m->img;
-            void *kargs[] = {&img, &a};
-            CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0), dim3(grid), dim3(kRowsWarps * 32),
-                                        kargs, m->rows_smem, st));
-        }
-        CUDA_CHECK(cudaGetLastError());
-        CUDA_CHECK(cudaEventRecord(ws->ev1, st));
-        size_t cb = ws->cub_bytes;
-        // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
-        CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
-        cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
-        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 4 * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 4, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
         if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) throw std::runtime_error("descent stack overflow (engine bug)");
         u64 total = ws->h_ctrl[0];
         ws->last_probes = ws->h_ctrl[2];
         ws->last_touches = ws->h_ctrl[3];
         ws->kernel_timed = true;
-        ws->launches = 3 + sort_launches;  // descent + 2 scan kernels (+ radix sort)
-        if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo (steady state never does)
+        ws->launches = 3 + ws->pending_sort_launches;  // descent + 2 scan kernels (+ radix sort)
+        if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo
             ws->d_tmp.alloc(total + total / 8 + 1024);
+            brwt_rows_begin(m, ws, d_rows, n);
             continue;
         }
         *total_out = total;
@@ -443,6 +472,11 @@ static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         return;
     }
     throw std::runtime_error("chunk arena did not converge");
+}
+
+static void brwt_rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
+    brwt_rows_begin(m, ws, d_rows, n);
+    brwt_rows_finish(m, ws, d_rows, n, col_bytes, total_out);
 }
 
 void rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out) {
@@ -820,6 +854,7 @@ void ggq_rows_result_free(ggq_rows_result *r) {
 // Large batches are cut into chunks that alternate between two workspaces (streams): while chunk k's CSR
 // travels to the host, chunk k+1 is sorted and descended — the PCIe copy, not the kernel, bounds this call.
 static const u64 kPipelineChunk = u64(1) << 20;
+static const u64 kPipelineDepth = 3;   // workspaces (streams) a pipelined host call rotates over
 
 static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, void *cols_v,
                          uint64_t cols_capacity, uint64_t *n_cols, int col_bytes) {
@@ -827,21 +862,35 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     GGQ_TRY
     if (!m || !offsets || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
-    Workspace *w[2] = {m->acquire(), nullptr};
+    // Chunks rotate over kPipelineDepth workspaces (streams).  Chunk k+1 is enqueued (H2D, ordering, descent, scan)
+    // BEFORE the host waits for chunk k's size, so the device never idles on a host round trip, and the device->host
+    // copy of chunk k overlaps the descent of the chunks after it.
+    const u64 n_chunks = n ? (n + kPipelineChunk - 1) / kPipelineChunk : 1;
+    const bool brwt = m->kind == Matrix::BRWT;
+    std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     int rc = GGQ_OK;
     try {
-        if (n > kPipelineChunk) w[1] = m->acquire();
+        for (auto &p : w) p = m->acquire();
         u64 base = 0;
         bool fits = true;
         int launches = 0;
         u64 probes = 0, touches = 0;
-        for (u64 r0 = 0, k = 0; r0 < n || k == 0; r0 += kPipelineChunk, ++k) {
-            Workspace *ws = w[1] ? w[k & 1] : w[0];
-            const u64 nc = std::min<u64>(kPipelineChunk, n - r0);
+        auto chunk_rows = [&](u64 k) { return std::min<u64>(kPipelineChunk, n - k * kPipelineChunk); };
+        auto begin = [&](u64 k) {
+            Workspace *ws = w[k % w.size()];
+            const u64 nc = chunk_rows(k);
             ws->reserve_rows(nc);
-            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + r0, nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kPipelineChunk, nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            if (brwt) brwt_rows_begin(m, ws, ws->d_rows.p, nc);
+        };
+        begin(0);
+        for (u64 k = 0; k < n_chunks; ++k) {
+            if (k + 1 < n_chunks) begin(k + 1);
+            Workspace *ws = w[k % w.size()];
+            const u64 nc = chunk_rows(k), r0 = k * kPipelineChunk;
             u64 total = 0;
-            rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
+            if (brwt) brwt_rows_finish(m, ws, ws->d_rows.p, nc, col_bytes, &total);
+            else rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             launches += ws->launches; probes += ws->last_probes; touches += ws->last_touches;
             if (base) {
                 add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
@@ -853,7 +902,6 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             if (fits && total)
                 CUDA_CHECK(cudaMemcpyAsync(cols + base * col_bytes, ws->d_out.p, total * col_bytes, cudaMemcpyDeviceToHost, ws->stream));
             base += total;
-            if (r0 + kPipelineChunk >= n) break;
         }
         for (Workspace *ws : w)
             if (ws) CUDA_CHECK(cudaStreamSynchronize(ws->stream));
@@ -882,6 +930,16 @@ int ggq_get_rows_into_u32(const ggq_matrix *m, const uint64_t *rows, uint64_t n,
     return get_rows_into(m, rows, n, offsets, cols, cols_capacity, n_cols, 4);
 }
 
+static void launch_col_hist(const ggq_matrix *m, Workspace *ws, const u32 *ids, u64 total, u64 *d_counts) {
+    const u64 nc = std::max<u64>(m->tree.n_cols, 1);
+    const u32 smem_cols = 12288;   // 48 KB of u32 counters
+    const size_t smem = nc <= smem_cols ? nc * 4 : 0;
+    const u32 grid = u32(std::min<u64>(u64(m->sm_count) * 4, (total + 511) / 512));
+    col_hist_kernel<<<grid, 512, smem, ws->stream>>>(ids, total, u32(nc), smem_cols, d_counts);
+    CUDA_CHECK(cudaGetLastError());
+    ws->launches += 1;
+}
+
 // device part of count_labels: counts (u64 x num_columns) in ws->d_counts
 static void count_labels_device(const ggq_matrix *m, Workspace *ws, const u64 *d_rows, u64 n) {
     const u64 nc = std::max<u64>(m->tree.n_cols, 1);
@@ -898,20 +956,68 @@ static void count_labels_device(const ggq_matrix *m, Workspace *ws, const u64 *d
         rows_device(m, ws, d_rows, n, 4, &total);
         ids = reinterpret_cast<const u32 *>(ws->d_out.p);
     }
-    if (total) {
-        const u32 smem_cols = 12288;   // 48 KB of u32 counters
-        const size_t smem = nc <= smem_cols ? nc * 4 : 0;
-        const u32 grid = u32(std::min<u64>(u64(m->sm_count) * 4, (total + 511) / 512));
-        col_hist_kernel<<<grid, 512, smem, ws->stream>>>(ids, total, u32(nc), smem_cols, ws->d_counts.p);
-        CUDA_CHECK(cudaGetLastError());
-        ws->launches += 1;
+    if (total) launch_col_hist(m, ws, ids, total, ws->d_counts.p);
+}
+
+// Large BRWT batches: chunks rotate over kPipelineDepth streams like get_rows_into — the host->device copy of a
+// chunk and its ordering overlap the descent of the previous one; every chunk's histogram kernel adds into the
+// counters of the first workspace.
+static void count_labels_pipelined(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts) {
+    const u64 n_chunks = (n + kPipelineChunk - 1) / kPipelineChunk;
+    const u64 nc = std::max<u64>(m->tree.n_cols, 1);
+    std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
+    cudaEvent_t zeroed = nullptr;
+    try {
+        for (auto &p : w) p = m->acquire();
+        CUDA_CHECK(cudaEventCreateWithFlags(&zeroed, cudaEventDisableTiming));
+        if (w[0]->d_counts.n < nc) w[0]->d_counts.alloc(nc);
+        CUDA_CHECK(cudaMemsetAsync(w[0]->d_counts.p, 0, nc * 8, w[0]->stream));
+        CUDA_CHECK(cudaEventRecord(zeroed, w[0]->stream));
+        for (size_t i = 1; i < w.size(); ++i) CUDA_CHECK(cudaStreamWaitEvent(w[i]->stream, zeroed, 0));
+        auto chunk_rows = [&](u64 k) { return std::min<u64>(kPipelineChunk, n - k * kPipelineChunk); };
+        auto begin = [&](u64 k) {
+            Workspace *ws = w[k % w.size()];
+            const u64 nr = chunk_rows(k);
+            ws->reserve_rows(nr);
+            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kPipelineChunk, nr * 8, cudaMemcpyHostToDevice, ws->stream));
+            brwt_rows_begin(m, ws, ws->d_rows.p, nr);
+        };
+        int launches = 0;
+        begin(0);
+        for (u64 k = 0; k < n_chunks; ++k) {
+            if (k + 1 < n_chunks) begin(k + 1);
+            Workspace *ws = w[k % w.size()];
+            u64 total = 0;
+            ws->hist_mode = true;
+            try { brwt_rows_finish(m, ws, ws->d_rows.p, chunk_rows(k), 4, &total); } catch (...) { ws->hist_mode = false; throw; }
+            ws->hist_mode = false;
+            if (total) launch_col_hist(m, ws, ws->d_tmp.p, total, w[0]->d_counts.p);
+            launches += ws->launches;
+        }
+        for (Workspace *ws : w) CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        w[0]->launches = launches;
+        if (m->tree.n_cols) {
+            CUDA_CHECK(cudaMemcpyAsync(counts, w[0]->d_counts.p, m->tree.n_cols * 8, cudaMemcpyDeviceToHost, w[0]->stream));
+            CUDA_CHECK(cudaStreamSynchronize(w[0]->stream));
+        }
+    } catch (...) {
+        for (Workspace *ws : w)
+            if (ws) { cudaStreamSynchronize(ws->stream); m->release(ws); }
+        if (zeroed) cudaEventDestroy(zeroed);
+        throw;
     }
+    for (Workspace *ws : w) m->release(ws);
+    cudaEventDestroy(zeroed);
 }
 
 int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts) {
     GGQ_TRY
     if (!m || (!rows && n) || !counts) return fail(GGQ_ERR_ARG, "bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
+    if (m->kind == Matrix::BRWT && n > kPipelineChunk) {
+        count_labels_pipelined(m, rows, n, counts);
+        return GGQ_OK;
+    }
     Workspace *ws = m->acquire();
     try {
         ws->reserve_rows(n);
@@ -926,6 +1032,149 @@ int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint
     }
     m->release(ws);
     return GGQ_OK;
+    GGQ_CATCH
+}
+
+// counts -> (column, count) pairs with count != 0 && count >= min_count, ascending columns; top != 0: stable sort by
+// count, descending (ties keep ascending columns).  Returns the number of pairs, left in d_lab_cols/d_lab_cnt
+// (or d_lab_cols2/d_lab_cnt2 after a sort: *sorted).
+static u64 filter_labels_device(const ggq_matrix *m, Workspace *ws, u64 min_count, bool top, bool *sorted) {
+    const u64 nc = std::max<u64>(m->tree.n_cols, 1);
+    if (ws->d_lab_cols.n < nc) {
+        ws->d_lab_cols.alloc(nc); ws->d_lab_cnt.alloc(nc); ws->d_lab_cols2.alloc(nc); ws->d_lab_cnt2.alloc(nc);
+        ws->d_lab_n.alloc(1);
+    }
+    label_filter_kernel<<<1, 1024, 0, ws->stream>>>(ws->d_counts.p, u32(m->tree.n_cols), min_count, ws->d_lab_cols.p,
+                                                    ws->d_lab_cnt.p, ws->d_lab_n.p);
+    CUDA_CHECK(cudaGetLastError());
+    ws->launches += 1;
+    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 8, ws->d_lab_n.p, 8, cudaMemcpyDeviceToHost, ws->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    const u64 kept = ws->h_ctrl[8];
+    *sorted = false;
+    if (top && kept > 1) {
+        size_t need = 0;
+        cub::DeviceRadixSort::SortPairsDescending(nullptr, need, ws->d_lab_cnt.p, ws->d_lab_cnt2.p, ws->d_lab_cols.p,
+                                                  ws->d_lab_cols2.p, kept, 0, 64, ws->stream);
+        if (ws->d_lab_sort.n < need + 16) ws->d_lab_sort.alloc(need + 16);
+        cub::DeviceRadixSort::SortPairsDescending(ws->d_lab_sort.p, need, ws->d_lab_cnt.p, ws->d_lab_cnt2.p, ws->d_lab_cols.p,
+                                                  ws->d_lab_cols2.p, kept, 0, 64, ws->stream);
+        CUDA_CHECK(cudaGetLastError());
+        *sorted = true;
+    }
+    return kept;
+}
+
+static int labels_query(const ggq_matrix *m, const uint64_t *rows, uint64_t n, u64 min_count, bool top, u64 limit,
+                        uint64_t *cols, uint64_t *counts, uint64_t *n_out) {
+    if (!m || (!rows && n) || !n_out) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    Workspace *ws = m->acquire();
+    try {
+        ws->reserve_rows(n);
+        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
+        count_labels_device(m, ws, ws->d_rows.p, n);
+        bool sorted = false;
+        u64 kept = m->tree.n_cols ? filter_labels_device(m, ws, min_count, top, &sorted) : 0;
+        kept = std::min(kept, limit);
+        if (kept && cols)
+            CUDA_CHECK(cudaMemcpyAsync(cols, sorted ? ws->d_lab_cols2.p : ws->d_lab_cols.p, kept * 8, cudaMemcpyDeviceToHost, ws->stream));
+        if (kept && counts)
+            CUDA_CHECK(cudaMemcpyAsync(counts, sorted ? ws->d_lab_cnt2.p : ws->d_lab_cnt.p, kept * 8, cudaMemcpyDeviceToHost, ws->stream));
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        *n_out = kept;
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return GGQ_OK;
+}
+
+int ggq_get_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, double presence_ratio, uint64_t *cols,
+                   uint64_t *counts, uint64_t *n_out) {
+    GGQ_TRY
+    if (!(presence_ratio >= 0.0 && presence_ratio <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
+    // annotate_static.cpp:79-82: size_t min_labels_discovered = ratio == 0 ? 1 : std::ceil(indices.size() * ratio)
+    const u64 min_count = presence_ratio == 0 ? 1 : u64(std::ceil(double(n) * presence_ratio));
+    return labels_query(m, rows, n, min_count, false, ~u64(0), cols, counts, n_out);
+    GGQ_CATCH
+}
+
+int ggq_get_top_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t num_top, uint64_t *cols,
+                       uint64_t *counts, uint64_t *n_out) {
+    GGQ_TRY
+    return labels_query(m, rows, n, 1, true, num_top, cols, counts, n_out);
+    GGQ_CATCH
+}
+
+int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                         double presence_ratio, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                         uint64_t capacity, uint64_t *n_out) {
+    GGQ_TRY
+    if (!m || !query_offsets || !label_offsets || !n_out) return fail(GGQ_ERR_ARG, "bad argument");
+    if (!(presence_ratio >= 0.0 && presence_ratio <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
+    if (query_offsets[0] != 0) return fail(GGQ_ERR_ARG, "query_offsets[0] must be 0");
+    for (u64 q = 0; q < n_queries; ++q)
+        if (query_offsets[q + 1] < query_offsets[q]) return fail(GGQ_ERR_ARG, "query_offsets must be non-decreasing");
+    const u64 n = query_offsets[n_queries];
+    if (!rows && n) return fail(GGQ_ERR_ARG, "bad argument");
+    if (n_queries >= (u64(1) << 31)) return fail(GGQ_ERR_LIMIT, "too many queries in one batch");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    int max_smem = 0;
+    CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+    const u64 nc = m->tree.n_cols;
+    const size_t hist_smem = size_t(std::max<u64>(nc, 1)) * 4;
+    if (hist_smem + 1024 > size_t(max_smem)) return fail(GGQ_ERR_LIMIT, "too many columns for the per-query shared-memory histogram");
+    *n_out = 0;
+    if (n_queries == 0) { label_offsets[0] = 0; return GGQ_OK; }
+    Workspace *ws = m->acquire();
+    int rc = GGQ_OK;
+    try {
+        ws->reserve_rows(n);
+        cudaStream_t st = ws->stream;
+        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+        if (ws->d_qoff.n < n_queries + 2) {
+            ws->d_qoff.alloc(n_queries + 2); ws->d_qlab_off.alloc(n_queries + 2); ws->d_qkept.alloc(n_queries + 2);
+        }
+        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, query_offsets, (n_queries + 1) * 8, cudaMemcpyHostToDevice, st));
+        u64 total = 0;
+        rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
+        if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
+        CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
+        query_labels_kernel<<<u32(n_queries), 256, hist_smem, st>>>(ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p),
+                                                                   ws->d_qoff.p, u32(nc), presence_ratio, ws->d_qstage_cols.p,
+                                                                   ws->d_qstage_cnt.p, ws->d_qkept.p);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemsetAsync(ws->d_qkept.p + n_queries, 0, 4, st));
+        size_t need = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
+        if (ws->d_lab_sort.n < need + 16) ws->d_lab_sort.alloc(need + 16);
+        cub::DeviceScan::ExclusiveSum(ws->d_lab_sort.p, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
+        CUDA_CHECK(cudaMemcpyAsync(label_offsets, ws->d_qlab_off.p, (n_queries + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        const u64 kept = label_offsets[n_queries];
+        *n_out = kept;
+        ws->launches += 3;
+        if (kept > capacity || (kept && !cols)) {
+            rc = fail(GGQ_ERR_ARG, "capacity too small");
+        } else if (kept) {
+            if (ws->d_qout_cols.n < kept) { ws->d_qout_cols.alloc(kept + kept / 8 + 1024); ws->d_qout_cnt.alloc(kept + kept / 8 + 1024); }
+            query_labels_gather_kernel<<<u32((n_queries * 8 + 255) / 256), 256, 0, st>>>(
+                ws->d_offsets.p, ws->d_qoff.p, ws->d_qlab_off.p, ws->d_qstage_cols.p, ws->d_qstage_cnt.p, n_queries,
+                ws->d_qout_cols.p, ws->d_qout_cnt.p);
+            CUDA_CHECK(cudaGetLastError());
+            ws->launches += 1;
+            CUDA_CHECK(cudaMemcpyAsync(cols, ws->d_qout_cols.p, kept * 8, cudaMemcpyDeviceToHost, st));
+            if (counts) CUDA_CHECK(cudaMemcpyAsync(counts, ws->d_qout_cnt.p, kept * 8, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+    } catch (...) {
+        m->release(ws);
+        throw;
+    }
+    m->release(ws);
+    return rc;
     GGQ_CATCH
 }
 

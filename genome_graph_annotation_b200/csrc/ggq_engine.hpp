@@ -72,6 +72,8 @@ struct Matrix {
 
     // descent kernel configuration
     u32 bm_words = 1, rb = 8, cap_s = 64, cap_spill = 0, rows_grid = 148;
+    u32 root_child = 0xFFFFFFFFu, root_sl = 0, root_multi_sb = 0, any_more = 0;   // K1 root fast path (RowsArgs)
+    u64 root_base = 0;
     size_t rows_smem = 0;
     u32 sort_bits = 0, row_bits = 0;   // query ordering: sort on the top sort_bits of the row_bits-bit row id
     u64 sort_min_n = 4096;             // batches smaller than this are processed in the caller's order
@@ -110,10 +112,15 @@ struct Workspace {
     size_t h_stage_bytes = 0;
     u64 last_probes = 0, last_touches = 0;
     int launches = 0;
+    int pending_sort_launches = 0;   // between brwt_rows_begin and brwt_rows_finish
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
     bool kernel_timed = false;
     bool hist_mode = false;          // count_labels: skip CSR assembly, the ids stay unordered in d_tmp
     DeviceBuf<u64> d_counts;
+    DeviceBuf<u64> d_lab_cols, d_lab_cnt, d_lab_cols2, d_lab_cnt2, d_lab_n;   // get_labels / get_top_labels
+    DeviceBuf<unsigned char> d_lab_sort;
+    DeviceBuf<u64> d_qoff, d_qlab_off, d_qout_cols, d_qout_cnt;   // ggq_get_labels_batch
+    DeviceBuf<u32> d_qstage_cols, d_qstage_cnt, d_qkept;
     // column-sharded queries: gathered partial CSRs of all shards, merged result, exchange timing
     DeviceBuf<u64> g_off, g_tot, m_off;
     DeviceBuf<u32> g_cols;

@@ -200,6 +200,104 @@ col_hist_kernel(const u32 *ids, u64 n_ids, u32 n_cols, u32 smem_cols, u64 *count
     }
 }
 
+// get_labels(indices, ratio) / get_top_labels thresholds (annotate_static.cpp:86-91, annotate.cpp:63-66): keep the
+// columns with counts[j] != 0 && counts[j] >= min_count, ascending, as (column, count) pairs.  One CTA: the
+// counter array has num_columns entries (thousands), the histogram behind it had billions of increments.
+__global__ void __launch_bounds__(1024)
+label_filter_kernel(const u64 *counts, u32 n_cols, u64 min_count, u64 *out_cols, u64 *out_counts, u64 *n_out) {
+    __shared__ u32 warp_cnt[32];
+    __shared__ u32 base_s;
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) base_s = 0;
+    __syncthreads();
+    for (u32 j0 = 0; j0 < n_cols; j0 += 1024) {
+        const u32 j = j0 + threadIdx.x;
+        const u64 c = j < n_cols ? counts[j] : 0;
+        const bool keep = c != 0 && c >= min_count;
+        const u32 bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        u32 before = 0, total = 0;
+        for (u32 w = 0; w < 32; ++w) {
+            const u32 v = warp_cnt[w];
+            if (w < warp) before += v;
+            total += v;
+        }
+        const u32 base = base_s;
+        if (keep) {
+            const u32 o = base + before + __popc(bal & ((1u << lane) - 1u));
+            out_cols[o] = j;
+            out_counts[o] = c;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) base_s = base + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_out = base_s;
+}
+
+// Cross-query batching (the reference runs one execute_query task per sequence, main.cpp:462-504): one CTA per
+// query builds the histogram of the query's column ids in shared memory (its rows are a contiguous CSR range),
+// applies the get_labels threshold (annotate_static.cpp:79-91) and writes the kept (column, count) pairs,
+// ascending, to a staging area at the query's CSR start (kept <= ids of the query, so the ranges never overlap).
+__global__ void __launch_bounds__(256)
+query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_offsets, u32 n_cols, double ratio,
+                    u32 *stage_cols, u32 *stage_counts, u32 *kept) {
+    extern __shared__ u32 s_hist[];
+    __shared__ u32 warp_cnt[8];
+    __shared__ u32 base_s;
+    const u32 q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u64 r0 = query_offsets[q], r1 = query_offsets[q + 1];
+    const u64 i0 = csr_offsets[r0], i1 = csr_offsets[r1];
+    for (u32 j = threadIdx.x; j < n_cols; j += 256) s_hist[j] = 0;
+    if (threadIdx.x == 0) base_s = 0;
+    __syncthreads();
+    for (u64 i = i0 + threadIdx.x; i < i1; i += 256) atomicAdd(s_hist + ids[i], 1u);
+    __syncthreads();
+    // size_t min_labels_discovered = ratio == 0 ? 1 : std::ceil(indices.size() * ratio)
+    const u64 min_count = ratio == 0 ? 1 : u64(ceil(double(r1 - r0) * ratio));
+    for (u32 j0 = 0; j0 < n_cols; j0 += 256) {
+        const u32 j = j0 + threadIdx.x;
+        const u32 c = j < n_cols ? s_hist[j] : 0;
+        const bool keep = c != 0 && c >= min_count;
+        const u32 bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        u32 before = 0, total = 0;
+        #pragma unroll
+        for (u32 w = 0; w < 8; ++w) {
+            const u32 v = warp_cnt[w];
+            if (w < warp) before += v;
+            total += v;
+        }
+        const u32 base = base_s;
+        if (keep) {
+            const u64 o = i0 + base + before + __popc(bal & ((1u << lane) - 1u));
+            stage_cols[o] = j;
+            stage_counts[o] = c;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) base_s = base + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) kept[q] = base_s;
+}
+
+// staging -> dense per-query lists (8 lanes copy one query)
+__global__ void query_labels_gather_kernel(const u64 *csr_offsets, const u64 *query_offsets, const u64 *label_offsets,
+                                           const u32 *stage_cols, const u32 *stage_counts, u64 n_queries,
+                                           u64 *out_cols, u64 *out_counts) {
+    const u64 q = (u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 3;
+    const u32 sub = threadIdx.x & 7;
+    if (q >= n_queries) return;
+    const u64 src = csr_offsets[query_offsets[q]];
+    const u64 dst = label_offsets[q], len = label_offsets[q + 1] - dst;
+    for (u64 i = sub; i < len; i += 8) {
+        out_cols[dst + i] = stage_cols[src + i];
+        out_counts[dst + i] = stage_counts[src + i];
+    }
+}
+
 // chunk-local CSR offsets -> global offsets (pipelined host API)
 __global__ void add_base_kernel(u64 *p, u64 n, u64 base) {
     u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;

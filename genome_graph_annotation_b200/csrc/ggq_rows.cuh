@@ -11,7 +11,7 @@
 // column's DFS rank in the row's bitmap (shared memory) and bumps the row's counter; a set bit of an internal
 // child pushes the child's first group with r' = rank1(r) - 1.  When the stack drains, the bitmaps of the tile
 // are scanned once in (row, word) order — which IS the reference's output order (DFS over child_nodes_,
-// BRWT.cpp:45-50) — non-zero words go through a 64-entry warp queue and are expanded 32 at a time.
+// BRWT.cpp:45-50) — non-zero words go through a 32-entry warp queue and are expanded a queue at a time.
 //
 // v3 vs v2 (profiles/r01: the kernel is instruction-issue bound, 27 warp instructions per probe): the two
 // children of a lane are handled without divergent branches (rank computed unconditionally, leaf marks
@@ -24,8 +24,11 @@
 namespace ggq {
 
 constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
-constexpr int kItemsPerIter = 16;      // work items a warp probes per iteration (2 lanes each, 2 children per lane)
-constexpr int kEmitQueue = 64;         // entries of the per-warp queue of non-zero bitmap words
+// Work items a warp probes per iteration (2 lanes each, 2 children per lane).  A variant with two items per lane pair
+// and iteration (two independent slot loads in flight per lane, 64 registers -> 4 CTAs/SM instead of 6) was measured
+// slower on B200: 12.3 vs 11.8 ms on the C4 shape at 1e9 rows.
+constexpr int kItemsPerIter = 16;
+constexpr int kEmitQueue = 32;         // entries of the per-warp queue of non-zero bitmap words
 constexpr int kRowCounters = 16;       // per-warp row counters (>= kMaxRowsPerWarp)
 
 struct RowsArgs {
@@ -41,10 +44,18 @@ struct RowsArgs {
     u32 cap_s, cap_spill;     // shared / global stack capacity per warp
     u32 bm_words;             // bitmap words per row
     u32 rb;                   // rows per warp tile
+    // root fast path: the root is a group of one vector; when it is internal the seeding step probes it directly
+    // (one 16-byte slot per row, all lanes busy) instead of spending a whole stack iteration on rb items
+    u32 root_child;           // first group of the root's children, or kNoRootFast
+    u32 root_sl;              // stride_log2 of group 0
+    u32 root_multi_sb;        // root vector spans several superblocks
+    u64 root_base;            // slot base of group 0
+    u32 any_more;             // some node has more than 4 children (continuation groups exist)
     int *err;
 };
+constexpr u32 kNoRootFast = 0xFFFFFFFFu;
 
-// Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][queues: warps x 64 u64][per warp: rb*bm_words
+// Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][queues: warps x 32 u64][per warp: rb*bm_words
 // bitmap words + 16 row counters (u32)]
 inline size_t rows_smem_bytes(u32 cap_s, u32 rb, u32 bm_words) {
     return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(kEmitQueue) * 8 + (size_t(rb) * bm_words + kRowCounters) * 4);
@@ -174,8 +185,30 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         bool valid = false;
         if (lane < nr) { r = a.rows[row0 + lane]; valid = r < img.n_rows; }
         const u32 vmask = __ballot_sync(0xffffffffu, valid);
-        if (valid) sts64(stk + __popc(vmask & lt_mask) * 8, (r << kItemRShift) | (u64(lane) << kItemGroupBits));
-        u32 top = __popc(vmask);
+        u32 top;
+        if (a.root_child != kNoRootFast) {
+            bool push = false;
+            u64 it = 0;
+            if (valid) {
+                u64 blk; u32 bit;
+                div96(r, blk, bit);
+                const uint4 s = ld_slot(img.slots + a.root_base + (blk << a.root_sl));
+                if (slot_test(s, bit)) {
+                    u64 ones = u64(s.x) + slot_rank_before(s, bit);
+                    if (a.root_multi_sb) ones += img.sb_base[img.lane_sb_off[0] + (blk >> kSuperShift)];
+                    it = (ones << kItemRShift) | (u64(lane) << kItemGroupBits) | a.root_child;
+                    push = true;
+                }
+                touches += 1;
+            }
+            const u32 pm = __ballot_sync(0xffffffffu, push);
+            if (push) sts64(stk + __popc(pm & lt_mask) * 8, it);
+            top = __popc(pm);
+            probes += __popc(vmask);
+        } else {
+            if (valid) sts64(stk + __popc(vmask & lt_mask) * 8, (r << kItemRShift) | (u64(lane) << kItemGroupBits));
+            top = __popc(vmask);
+        }
         __syncwarp();
 
         while (top > 0) {
@@ -183,7 +216,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             const bool active = idx < c;
             u64 item = 0;
             if (active) item = stk_get<SPILL>(stk, spill, a.cap_s, top - 1 - idx);
-            __syncwarp();
+            __syncwarp();   // every pop happens before any push below
             bool push_cont = false, push0 = false, push1 = false;
             u64 item0 = 0, item1 = 0;
             if (active) {
@@ -234,13 +267,15 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                     item1 = (ones1 << kItemRShift) | tq | rec.w;
                 }
             }
-            const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
             const u32 m0 = __ballot_sync(0xffffffffu, push0);
             const u32 m1 = __ballot_sync(0xffffffffu, push1);
             u32 pos = top - c;
-            if (push_cont)
-                stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
-            pos += __popc(cont_mask);
+            if (a.any_more) {   // uniform: trees of arity <= 4 have no continuation groups
+                const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
+                if (push_cont)
+                    stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
+                pos += __popc(cont_mask);
+            }
             if (push0) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m0 & lt_mask), item0, a.err);
             pos += __popc(m0);
             if (push1) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m1 & lt_mask), item1, a.err);
@@ -283,20 +318,18 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                     const u32 bits = w < a.bm_words ? lds32(bm_row + w * 4) : 0u;
                     const u32 nz = __ballot_sync(0xffffffffu, bits != 0);
                     if (!nz) continue;
+                    const u32 add = __popc(nz);
+                    if (q + add > kEmitQueue) {   // no room: expand what is queued (reads before the writes below)
+                        __syncwarp();
+                        pos += emit_flush(img, que, q, lane, lt_mask, a.tmp_cols, pos, fits);
+                        q = 0;
+                        __syncwarp();
+                    }
                     if (bits) {
                         sts32(bm_row + w * 4, 0);
                         sts64(que + (q + __popc(nz & lt_mask)) * 8, (u64(w) << 32) | bits);
                     }
-                    q += __popc(nz);
-                    if (q >= 32) {
-                        __syncwarp();
-                        pos += emit_flush(img, que, 32, lane, lt_mask, a.tmp_cols, pos, fits);
-                        q -= 32;
-                        u64 e = 0;
-                        if (lane < q) e = lds64(que + (32 + lane) * 8);
-                        __syncwarp();
-                        if (lane < q) sts64(que + lane * 8, e);
-                    }
+                    q += add;
                 }
             }
             if (q) {

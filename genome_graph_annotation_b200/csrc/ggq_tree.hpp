@@ -333,24 +333,30 @@ inline void assign_geometry(FlatTree *t) {
 inline uint32_t simulate_stack(const FlatTree &t, uint32_t rows_per_warp, uint32_t items_per_iter) {
     std::vector<uint32_t> st(rows_per_warp, 0);  // group ids; all rows start at the root group
     size_t max_top = st.size();
-    std::vector<uint32_t> conts, kids0, kids1;
+    std::vector<uint32_t> pushed, conts, kids0, kids1;
     while (!st.empty()) {
         size_t c = std::min<size_t>(st.size(), items_per_iter);
-        conts.clear(); kids0.clear(); kids1.clear();
-        for (size_t i = 0; i < c; ++i) {
-            uint32_t g = st[st.size() - 1 - i];
-            uint64_t hot = t.group_hot[g];
-            uint32_t cnt = uint32_t(hot >> kGhCntShift) & 7;
-            if ((hot >> kGhMoreShift) & 1) conts.push_back(g + 1);
-            for (uint32_t k = 0; k < cnt; ++k) {   // lane `half` pushes child 2*half first, then 2*half+1
-                uint32_t info = t.lane_info[g * 4 + k];
-                if (!(info & kLeafFlag)) ((k & 1) ? kids1 : kids0).push_back(info);
+        pushed.clear();
+        // the kernel handles the popped items in rounds of 16 (one item per lane pair and round) and pushes, per
+        // round: continuation groups, then the first, then the second child of every lane
+        for (size_t r0 = 0; r0 < c; r0 += 16) {
+            conts.clear(); kids0.clear(); kids1.clear();
+            for (size_t i = r0; i < std::min(c, r0 + 16); ++i) {
+                uint32_t g = st[st.size() - 1 - i];
+                uint64_t hot = t.group_hot[g];
+                uint32_t cnt = uint32_t(hot >> kGhCntShift) & 7;
+                if ((hot >> kGhMoreShift) & 1) conts.push_back(g + 1);
+                for (uint32_t k = 0; k < cnt; ++k) {   // lane `half` pushes child 2*half first, then 2*half+1
+                    uint32_t info = t.lane_info[g * 4 + k];
+                    if (!(info & kLeafFlag)) ((k & 1) ? kids1 : kids0).push_back(info);
+                }
             }
+            pushed.insert(pushed.end(), conts.begin(), conts.end());
+            pushed.insert(pushed.end(), kids0.begin(), kids0.end());
+            pushed.insert(pushed.end(), kids1.begin(), kids1.end());
         }
         st.resize(st.size() - c);
-        st.insert(st.end(), conts.begin(), conts.end());
-        st.insert(st.end(), kids0.begin(), kids0.end());
-        st.insert(st.end(), kids1.begin(), kids1.end());
+        st.insert(st.end(), pushed.begin(), pushed.end());
         max_top = std::max(max_top, st.size());
     }
     return uint32_t(max_top);

@@ -107,9 +107,10 @@ void ggq_rows_result_free(ggq_rows_result *r);
 
 /* Same query, caller-provided host output (cols_capacity entries).  *n_cols receives the number of
  * column ids; if it exceeds cols_capacity GGQ_ERR_ARG is returned (offsets are complete, the contents of
- * cols are unspecified).  Batches above 2^20 rows are pipelined in chunks over two streams so that the
- * device->host copy of one chunk overlaps the descent of the next; page-locked (pinned) caller buffers are
- * needed for that overlap, pageable ones work but serialise. */
+ * cols are unspecified).  Batches above 2^20 rows are pipelined in chunks over three streams: a chunk is enqueued
+ * before the host waits for the size of the previous one, and the device->host copy of a chunk overlaps the
+ * descent of the next ones; page-locked (pinned) caller buffers are needed for that overlap, pageable ones work
+ * but serialise. */
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets,
                       uint64_t *cols, uint64_t cols_capacity, uint64_t *n_cols);
 
@@ -126,6 +127,32 @@ int ggq_get_rows_into_u32(const ggq_matrix *m, const uint64_t *rows, uint64_t n,
 int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts);
 int ggq_count_labels_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
                             const uint64_t **d_counts);
+
+/* StaticBinRelAnnotator::get_labels(indices, presence_ratio) (annotation/annotate_static.cpp:71-94): the columns with
+ * counts[j] != 0 && counts[j] >= (ratio == 0 ? 1 : ceil(n * ratio)), ascending, with their counts.  Histogram and
+ * threshold run on the device; only the kept pairs come back.  cols / counts: num_columns entries (either may be
+ * NULL); *n_out receives the number of kept columns.  presence_ratio outside [0, 1] (assert in the reference):
+ * GGQ_ERR_ARG. */
+int ggq_get_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, double presence_ratio, uint64_t *cols,
+                   uint64_t *counts, uint64_t *n_out);
+/* MultiLabelEncoded::get_top_labels(indices, num_top) (common/annotate.cpp:57-83): the non-zero (column, count) pairs
+ * in decreasing order of count, truncated to num_top.  The reference's std::sort leaves the order of equal counts
+ * unspecified; here ties are in ascending column order (stable device radix sort).  cols / counts: min(num_top,
+ * num_columns) entries. */
+int ggq_get_top_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t num_top, uint64_t *cols,
+                       uint64_t *counts, uint64_t *n_out);
+
+/* Cross-query batching: `annograph classify` runs one execute_query task per sequence
+ * (main.cpp:462-504), each calling get_labels(indices, ratio) on 10^2..10^3 indices — too few to fill a GPU.  Here the
+ * index lists of n_queries sequences are concatenated (query q owns rows[query_offsets[q] .. query_offsets[q+1]),
+ * query_offsets[0] == 0) and answered by ONE descent launch plus one histogram CTA per query.  For every query the
+ * result is exactly ggq_get_labels(rows of q, presence_ratio): label_offsets has n_queries + 1 entries, query q's
+ * columns (ascending) and counts are cols/counts[label_offsets[q] .. label_offsets[q+1]).  capacity: entries of
+ * cols / counts (counts may be NULL); *n_out = total pairs; GGQ_ERR_ARG if it exceeds capacity (label_offsets is
+ * complete).  Matrices with more columns than fit a shared-memory histogram (~57k): GGQ_ERR_LIMIT. */
+int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                         double presence_ratio, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                         uint64_t capacity, uint64_t *n_out);
 
 /* slice_rows: concatenation of get_row(R[t]) each followed by UINT64_MAX (SURVEY.md "Three facts" 1). */
 int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len);

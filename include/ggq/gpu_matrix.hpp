@@ -16,12 +16,14 @@
 #ifndef GGQ_GPU_MATRIX_HPP_
 #define GGQ_GPU_MATRIX_HPP_
 
+#include <algorithm>
 #include <fstream>
 #include <istream>
 #include <memory>
 #include <ostream>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "binary_matrix.hpp"  // the reference's interface (common/binary_matrix.hpp)
@@ -92,6 +94,28 @@ class GpuMatrixBase : public BinaryMatrix {
         uint64_t dummy = 0;
         check(ggq_count_labels(handle(), rows.data(), rows.size(), counts.empty() ? &dummy : counts.data()));
         return counts;
+    }
+
+    // Columns kept by StaticBinRelAnnotator::get_labels(indices, presence_ratio) (annotate_static.cpp:71-94), ascending;
+    // the caller decodes them with its LabelEncoder.  Histogram + threshold on the device.
+    std::vector<Column> get_columns_with_ratio(const std::vector<Row> &rows, double presence_ratio) const {
+        std::vector<Column> cols(std::max<uint64_t>(num_columns(), 1));
+        uint64_t k = 0;
+        check(ggq_get_labels(handle(), rows.data(), rows.size(), presence_ratio, cols.data(), nullptr, &k));
+        cols.resize(k);
+        return cols;
+    }
+
+    // (column, count) pairs of MultiLabelEncoded::get_top_labels(indices, num_top) (common/annotate.cpp:57-83):
+    // decreasing count; equal counts in ascending column order (unspecified in the reference).
+    std::vector<std::pair<Column, uint64_t>> get_top_columns(const std::vector<Row> &rows, size_t num_top) const {
+        const uint64_t cap = std::max<uint64_t>(std::min<uint64_t>(num_columns(), num_top), 1);
+        std::vector<uint64_t> cols(cap), counts(cap);
+        uint64_t k = 0;
+        check(ggq_get_top_labels(handle(), rows.data(), rows.size(), num_top, cols.data(), counts.data(), &k));
+        std::vector<std::pair<Column, uint64_t>> out(k);
+        for (uint64_t i = 0; i < k; ++i) out[i] = {cols[i], counts[i]};
+        return out;
     }
 
     std::vector<bool> has_column(const std::vector<Row> &rows, Column column) const {

@@ -7,6 +7,8 @@
 // and requires IDENTICAL answers through the BinaryMatrix interface — the same triple check as the
 // reference's test_brwt() helper (tests/test_BRWT.cpp:92-150), but with vector equality (order included),
 // plus serialize() byte equality and the batched extensions.
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <random>
@@ -66,6 +68,20 @@ static void compare(const BinaryMatrix &ref, const ggq::GpuMatrixBase &gpu, cons
         for (auto i : idx)
             for (auto j : ref.get_row(i)) expect[j]++;
         REQUIRE(gpu.count_columns(idx) == expect);
+        // get_labels(indices, ratio) threshold (annotate_static.cpp:79-91) and get_top_labels (annotate.cpp:57-83)
+        for (double ratio : {0.0, 0.1, 0.5, 1.0}) {
+            const size_t need = ratio == 0 ? 1 : size_t(std::ceil(idx.size() * ratio));
+            std::vector<uint64_t> keep;
+            for (uint64_t j = 0; j < m; ++j)
+                if (expect[j] && expect[j] >= need) keep.push_back(j);
+            REQUIRE(gpu.get_columns_with_ratio(idx, ratio) == keep);
+        }
+        std::vector<std::pair<uint64_t, uint64_t>> top;
+        for (uint64_t j = 0; j < m; ++j)
+            if (expect[j]) top.emplace_back(j, expect[j]);
+        std::stable_sort(top.begin(), top.end(), [](const auto &a, const auto &b) { return a.second > b.second; });
+        top.resize(std::min<size_t>(top.size(), 3));
+        REQUIRE(gpu.get_top_columns(idx, 3) == top);
     }
     for (uint64_t j = 0; j < m; ++j) {
         REQUIRE(gpu.get_column(j) == ref.get_column(j));

@@ -40,6 +40,18 @@ def check_matrix(ggq, rm, dense=None, rows=None, all_cells=True):
         exp_cnt = np.bincount(ecols.astype(np.int64), minlength=m) + \
             np.bincount(ecols[:int(eoff[half.size])].astype(np.int64), minlength=m)
         assert np.array_equal(gm.count_labels(np.concatenate([rows, half])), exp_cnt.astype(np.uint64)[:m])
+        # get_labels(indices, ratio) (annotate_static.cpp:71-94) and get_top_labels (annotate.cpp:57-83)
+        both = np.concatenate([rows, half])
+        for ratio in (0.0, 0.01, 0.25, 0.5, 1.0):
+            need = 1 if ratio == 0 else int(np.ceil(both.size * ratio))
+            keep = np.nonzero((exp_cnt[:m] != 0) & (exp_cnt[:m] >= need))[0]
+            lc, lv = gm.get_labels(both, ratio)
+            assert np.array_equal(lc, keep.astype(np.uint64)) and np.array_equal(lv, exp_cnt[keep].astype(np.uint64))
+        for num_top in (0, 1, 3, m, m + 5):
+            nzc = np.nonzero(exp_cnt[:m])[0]
+            order = nzc[np.argsort(-exp_cnt[nzc].astype(np.int64), kind="stable")][:num_top]
+            tc, tv = gm.get_top_labels(both, num_top)
+            assert np.array_equal(tc, order.astype(np.uint64)) and np.array_equal(tv, exp_cnt[order].astype(np.uint64))
         # slice_rows = rows separated by UINT64_MAX
         sl = gm.slice_rows(rows)
         exp = []
@@ -157,3 +169,35 @@ def test_config1_norepl_1e5(ggq, ref):
     eoff, ecols, _ = rm.get_rows(rnd)
     assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
     gm.close()
+
+
+def test_config2_uniform_rows_multi_brwt(ggq, ref):
+    """BASELINE config 2 (SURVEY 8d "C2 concrete input"), reduced to 1e5 x 1000 so the CPU build takes seconds:
+    generate_random_rows(2e4 unique x 5, shuffled) seed 42 (experiments/main.cpp:232-247), Multi-BRWT = greedy
+    partitioner + relax(7); batched get_rows over all rows and over random ids at batch sizes 1 / 1e2 / 1e4 / all,
+    get_column for 10 random columns and a sweep of the others."""
+    n, m = 100_000, 1000
+    cw = ref.gen_uniform_rows(n, m, 0.01, n // 5, seed=42)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=7, threads=8)
+    gm = ggq.GpuMatrix.load_brwt(rm.serialize())
+    try:
+        assert (gm.num_rows, gm.num_columns, gm.num_relations) == (n, m, rm.num_relations)
+        assert gm.num_nodes == rm.num_nodes and gm.total_column_size == rm.total_column_size
+        rows = np.arange(n, dtype=np.uint64)
+        eoff, ecols, _ = rm.get_rows(rows, threads=8)
+        off, cols = gm.get_rows_csr(rows)
+        assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
+        rnd = ref.gen_random_ints(n, 0, n, seed=42)
+        roff, rcols, _ = rm.get_rows(rnd, threads=8)
+        for bs in (1, 100, 10_000, n):
+            lim = min(n, bs * 20)   # 20 batches of each size
+            for lo in range(0, lim, bs):
+                o, c = gm.get_rows_csr(rnd[lo:lo + bs])
+                assert np.array_equal(o, roff[lo:lo + bs + 1] - roff[lo])
+                assert np.array_equal(c, rcols[int(roff[lo]):int(roff[lo + bs])])
+        assert np.array_equal(gm.count_labels(rnd), np.bincount(rcols.astype(np.int64), minlength=m).astype(np.uint64))
+        some = ref.gen_random_ints(10, 0, m, seed=42).tolist() + list(range(0, m, 37))
+        for c in some:
+            assert np.array_equal(gm.get_column(int(c)), rm.get_column(int(c)))
+    finally:
+        gm.close()

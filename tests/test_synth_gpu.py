@@ -112,6 +112,8 @@ def test_pipelined_host_api_matches_single_shot(ggq):
             eo, ec = gm.get_rows_csr(rows[lo:hi])
             assert np.array_equal(off[lo:hi + 1] - off[lo], eo)
             assert np.array_equal(cols[int(off[lo]):int(off[hi])], ec)
+        # count_labels above 2^20 rows runs the same chunk pipeline (histograms of all chunks add up)
+        assert np.array_equal(gm.count_labels(rows), np.bincount(cols[:total].astype(np.int64), minlength=m).astype(np.uint64))
         # compact u32 ids: same CSR
         cols32 = np.empty(cols.size, np.uint32)
         off32 = np.empty_like(off)
@@ -136,3 +138,31 @@ def test_two_matrices_with_different_shapes_coexist(ggq):
     b = wide.get_rows_csr(rows)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
     wide.close(); narrow.close()
+
+
+def test_labels_batch_equals_per_query_get_labels(ggq):
+    """ggq_get_labels_batch (cross-query batching, main.cpp:462-504) == ggq_get_labels per query: same columns,
+    same counts, same threshold (annotate_static.cpp:79-91), empty queries and duplicates included."""
+    n, m, d = 40_000, 150, 0.04
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=11, arity=3)
+    try:
+        rng = np.random.default_rng(5)
+        sizes = np.concatenate([[0, 1, 2], rng.integers(1, 400, 120), [0, 5000]])
+        qoff = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+        rows = rng.integers(0, n, int(qoff[-1])).astype(np.uint64)
+        rows[10:20] = rows[10]   # duplicates are counted
+        for ratio in (0.0, 0.05, 0.3, 1.0):
+            loff, cols, cnt = gm.get_labels_batch(rows, qoff, ratio)
+            assert loff[0] == 0 and loff[-1] == cols.size == cnt.size
+            for q in range(sizes.size):
+                ec, ev = gm.get_labels(rows[int(qoff[q]):int(qoff[q + 1])], ratio)
+                a, b = int(loff[q]), int(loff[q + 1])
+                assert np.array_equal(cols[a:b], ec) and np.array_equal(cnt[a:b], ev), (ratio, q)
+        # capacity too small: error, offsets complete
+        with pytest.raises(ggq.GgqError):
+            gm.get_labels_batch(rows, qoff, 0.0, capacity=3)
+        # no queries
+        loff, cols, cnt = gm.get_labels_batch(np.zeros(0, np.uint64), np.zeros(1, np.uint64), 0.5)
+        assert loff.tolist() == [0] and cols.size == 0
+    finally:
+        gm.close()
