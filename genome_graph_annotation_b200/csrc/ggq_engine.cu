@@ -853,7 +853,19 @@ void ggq_rows_result_free(ggq_rows_result *r) {
 
 // Large batches are cut into chunks that alternate between two workspaces (streams): while chunk k's CSR
 // travels to the host, chunk k+1 is sorted and descended — the PCIe copy, not the kernel, bounds this call.
-static const u64 kPipelineChunk = u64(1) << 20;
+// rows per chunk of the pipelined host calls (GGQ_CHUNK_LOG2 overrides for experiments)
+static u64 pipeline_chunk() {
+    static const u64 v = [] {
+        const char *e = std::getenv("GGQ_CHUNK_LOG2");
+        const u64 l = e && *e ? std::strtoull(e, nullptr, 10) : 20;
+        return u64(1) << std::min<u64>(std::max<u64>(l, 10), 30);
+    }();
+    return v;
+}
+#define kPipelineChunk pipeline_chunk()
+// count_labels returns only num_columns counters, so nothing but the first host->device copy is exposed: larger
+// chunks (measured on C4: 2^20 -> 1.03e9, 2^22 -> 1.12e9 rows/s); get_rows is best at 2^20 (device->host tail)
+static const u64 kCountChunk = u64(1) << 22;
 static const u64 kPipelineDepth = 3;   // workspaces (streams) a pipelined host call rotates over
 
 static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, void *cols_v,
@@ -963,7 +975,7 @@ static void count_labels_device(const ggq_matrix *m, Workspace *ws, const u64 *d
 // chunk and its ordering overlap the descent of the previous one; every chunk's histogram kernel adds into the
 // counters of the first workspace.
 static void count_labels_pipelined(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *counts) {
-    const u64 n_chunks = (n + kPipelineChunk - 1) / kPipelineChunk;
+    const u64 n_chunks = (n + kCountChunk - 1) / kCountChunk;
     const u64 nc = std::max<u64>(m->tree.n_cols, 1);
     std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     cudaEvent_t zeroed = nullptr;
@@ -974,12 +986,12 @@ static void count_labels_pipelined(const ggq_matrix *m, const uint64_t *rows, ui
         CUDA_CHECK(cudaMemsetAsync(w[0]->d_counts.p, 0, nc * 8, w[0]->stream));
         CUDA_CHECK(cudaEventRecord(zeroed, w[0]->stream));
         for (size_t i = 1; i < w.size(); ++i) CUDA_CHECK(cudaStreamWaitEvent(w[i]->stream, zeroed, 0));
-        auto chunk_rows = [&](u64 k) { return std::min<u64>(kPipelineChunk, n - k * kPipelineChunk); };
+        auto chunk_rows = [&](u64 k) { return std::min<u64>(kCountChunk, n - k * kCountChunk); };
         auto begin = [&](u64 k) {
             Workspace *ws = w[k % w.size()];
             const u64 nr = chunk_rows(k);
             ws->reserve_rows(nr);
-            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kPipelineChunk, nr * 8, cudaMemcpyHostToDevice, ws->stream));
+            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kCountChunk, nr * 8, cudaMemcpyHostToDevice, ws->stream));
             brwt_rows_begin(m, ws, ws->d_rows.p, nr);
         };
         int launches = 0;
@@ -1014,7 +1026,7 @@ int ggq_count_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint
     GGQ_TRY
     if (!m || (!rows && n) || !counts) return fail(GGQ_ERR_ARG, "bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
-    if (m->kind == Matrix::BRWT && n > kPipelineChunk) {
+    if (m->kind == Matrix::BRWT && n > kCountChunk) {
         count_labels_pipelined(m, rows, n, counts);
         return GGQ_OK;
     }

@@ -1,10 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_v3b_c4.json 2> gpurun_out/bench_v3b_c4.err
-python -c "
-import json
-d = json.loads(open('gpurun_out/bench_v3b_c4.json').read().strip().splitlines()[-1])
-print(d['value'], d['ms_per_step'], d['roofline']['kernel_ms'], 'e2e', d['e2e']['value'], 'u64', d['e2e_u64']['value'], 'cl', d['count_labels_e2e']['value'])"
-timeout 900 python scripts/bench_bv.py --kinds stat,sd > gpurun_out/bench_bv_v3.log 2>&1
-tail -12 gpurun_out/bench_bv_v3.log | cut -c1-400
+for c in 20 21 22; do
+GGQ_CHUNK_LOG2=$c timeout 600 python bench.py --no-cpu-baseline --rows 1e9 2>/dev/null | python -c "
+import json,sys
+d = json.loads(sys.stdin.read().strip().splitlines()[-1])
+print('chunk', $c, d['value'], d['ms_per_step'], d['roofline']['kernel_ms'], 'e2e', d['e2e']['value'], 'u64', d['e2e_u64']['value'], 'cl', d['count_labels_e2e']['value'])"
+done

@@ -112,8 +112,10 @@ def test_pipelined_host_api_matches_single_shot(ggq):
             eo, ec = gm.get_rows_csr(rows[lo:hi])
             assert np.array_equal(off[lo:hi + 1] - off[lo], eo)
             assert np.array_equal(cols[int(off[lo]):int(off[hi])], ec)
-        # count_labels above 2^20 rows runs the same chunk pipeline (histograms of all chunks add up)
-        assert np.array_equal(gm.count_labels(rows), np.bincount(cols[:total].astype(np.int64), minlength=m).astype(np.uint64))
+        # count_labels above 2^22 rows runs the same chunk pipeline (histograms of all chunks add up)
+        hist = np.bincount(cols[:total].astype(np.int64), minlength=m).astype(np.uint64)
+        assert np.array_equal(gm.count_labels(rows), hist)
+        assert np.array_equal(gm.count_labels(np.tile(rows, 3)), hist * np.uint64(3))
         # compact u32 ids: same CSR
         cols32 = np.empty(cols.size, np.uint32)
         off32 = np.empty_like(off)
