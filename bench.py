@@ -75,6 +75,8 @@ def parse_args():
                          "over all ranks with the NCCL exchange (needs --gpus >= 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-peer", action="store_true",
+                    help="c5: exchange partial rows with NCCL instead of merging from peer memory over NVLink")
     return ap.parse_args()
 
 
@@ -445,6 +447,9 @@ def run_c5(args):
         dist.barrier()
         torch.cuda.synchronize()
 
+    if not args.no_peer:
+        # merge straight from the peers' partial CSRs over NVLink (cudaIpc); capacity: this batch size, ids with slack
+        comm.enable_peer(ws, B, int(B * m * d * 1.3 / world) + (1 << 20))
     for i in range(W):
         ws.get_rows_sharded_device(comm, batches[i % n_pool].data_ptr(), B, 8)
     clocks = ClockSampler(local)
@@ -468,6 +473,7 @@ def run_c5(args):
     tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
     ms_step = float(tmax[0]) / K
+    peer = comm.peer_active
     if rank == 0:
         peak, peak_src = peaks()
         k_ms = float(tmax[1])
@@ -478,17 +484,22 @@ def run_c5(args):
                 "dtype": "u64", "data": "synthetic",
                 "config": {"workload": "C5 RefSeq-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner, "
                                        "column-sharded over %d GPUs; get_rows over %d uniformly random row ids per step "
-                                       "(same batch on every rank), NCCL exchange + merge, full CSR on every rank" %
-                                       (n, m, d, args.arity, world, B),
+                                       "(same batch on every rank), %s, full CSR on every rank" %
+                                       (n, m, d, args.arity, world, B,
+                                        "merge kernels read the shards' partial rows from peer memory over NVLink (cudaIpc)"
+                                        if peer else "NCCL exchange + merge"),
                            "rows": n, "cols": m, "density": d, "arity": args.arity, "batch_rows": B, "seed": SEED,
-                           "parallelism": "column shards x%d (cut frontier dealt in DFS runs), ncclAllGather + grouped ncclBroadcast" % world,
+                           "parallelism": "column shards x%d (cut frontier dealt in DFS runs), %s" %
+                                          (world, "peer-memory merge (P2P loads), 8-byte all-gathers as barriers" if peer
+                                           else "ncclAllGather + grouped ncclBroadcast"),
                            "l2": "inputs larger than L2"},
                 "clocks": clk,
                 "roofline": {"bound": "hbm", "kernel": "brwt_rows_kernel", "achieved": alg / (k_ms / 1e3) / 1e9 / world,
                              "peak": peak, "unit": "GB/s", "frac": alg / (k_ms / 1e3) / 1e9 / world / peak, "traffic": None,
                              "peak_source": peak_src, "kernel_ms_max_over_ranks": k_ms,
                              "note": "per-GPU average: algorithmic bytes of all shards / (ranks x slowest descent)"},
-                "exchange": {"ms_max_over_ranks": float(tmax[2]), "bytes_per_step_per_rank": xch_bytes / K,
+                "exchange": {"mode": "peer (timed: fused transfer + merge)" if peer else "nccl (timed: transfer only)",
+                             "ms_max_over_ranks": float(tmax[2]), "bytes_per_step_per_rank": xch_bytes / K,
                              "gb_per_s_per_rank": xch_bytes / K / (float(tmax[2]) / 1e3) / 1e9 if float(tmax[2]) > 0 else None},
                 "gpu_launches": launches, "build_seconds": build_s,
                 "device_image_gb_per_rank_max": float(tmax[4]) / 1e9, "device_image_gb_total": float(tsum[4]) / 1e9,

@@ -62,6 +62,8 @@ def lib():
         "ggq_comm_unique_id": (C.c_int, [u8p]),
         "ggq_comm_init": (C.c_int, [u8p, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
         "ggq_comm_free": (None, [vp]),
+        "ggq_comm_enable_peer": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
+        "ggq_comm_peer_active": (C.c_int, [vp]),
         "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
         "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
@@ -181,6 +183,15 @@ class Comm:
         h = C.c_void_p()
         _check(lib().ggq_comm_init(buf, rank, n_ranks, device, C.byref(h)))
         self._h = h
+
+    def enable_peer(self, workspace, max_rows, max_ids):
+        """Collective: export `workspace`'s partial-CSR buffers over cudaIpc and map the peers' (ggq_comm_enable_peer);
+        sharded queries on that workspace then merge straight from peer memory over NVLink."""
+        _check(lib().ggq_comm_enable_peer(self._h, workspace._h, int(max_rows), int(max_ids)))
+
+    @property
+    def peer_active(self):
+        return bool(lib().ggq_comm_peer_active(self._h))
 
     def close(self):
         if self._h:

@@ -787,6 +787,48 @@ int ggq_comm_init(const uint8_t id[128], int rank, int n_ranks, int device, ggq_
     GGQ_CATCH
 }
 
+int ggq_comm_enable_peer(ggq_comm *c, ggq_workspace *ws, uint64_t max_rows, uint64_t max_ids) {
+    GGQ_TRY
+    if (!c || !ws || !max_rows) return fail(GGQ_ERR_ARG, "bad argument");
+    if (c->n_ranks > kMaxShards) return fail(GGQ_ERR_LIMIT, "too many shards");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    const int R = c->n_ranks;
+    // pin the partial-CSR buffers at the stated capacity (they must not be reallocated while mapped by peers)
+    ws->reserve_rows(max_rows);
+    const size_t out_bytes = size_t(std::max<u64>(max_ids, 1)) * 4;
+    if (ws->d_out.n < out_bytes) ws->d_out.alloc(out_bytes);
+    if (ws->g_tot.n < size_t(kMaxShards) + 1) ws->g_tot.alloc(kMaxShards + 1);
+    struct Handles { cudaIpcMemHandle_t off, cols; };
+    static_assert(sizeof(Handles) == 128, "cudaIpcMemHandle_t size");
+    Handles mine;
+    CUDA_CHECK(cudaIpcGetMemHandle(&mine.off, ws->d_offsets.p));
+    CUDA_CHECK(cudaIpcGetMemHandle(&mine.cols, ws->d_out.p));
+    DeviceBuf<unsigned char> d_send, d_recv;
+    d_send.alloc(sizeof(Handles));
+    d_recv.alloc(sizeof(Handles) * size_t(R));
+    CUDA_CHECK(cudaMemcpyAsync(d_send.p, &mine, sizeof(Handles), cudaMemcpyHostToDevice, ws->stream));
+    NCCL_CHECK(NcclApi::get().AllGather(d_send.p, d_recv.p, sizeof(Handles), ncclUint8, c->comm, ws->stream));
+    std::vector<Handles> all(static_cast<size_t>(R));
+    CUDA_CHECK(cudaMemcpyAsync(all.data(), d_recv.p, sizeof(Handles) * size_t(R), cudaMemcpyDeviceToHost, ws->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    for (int r = 0; r < R; ++r) {
+        if (r == c->rank) continue;
+        void *po = nullptr, *pc = nullptr;
+        CUDA_CHECK(cudaIpcOpenMemHandle(&po, all[size_t(r)].off, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_off[r] = static_cast<const u64 *>(po);
+        CUDA_CHECK(cudaIpcOpenMemHandle(&pc, all[size_t(r)].cols, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_cols[r] = static_cast<const u32 *>(pc);
+    }
+    c->peer_ws = ws;
+    c->peer_max_rows = max_rows;
+    c->peer_max_ids = max_ids;
+    c->peer = true;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_comm_peer_active(const ggq_comm *c) { return c && c->peer ? 1 : 0; }
+
 void ggq_comm_free(ggq_comm *c) {
     if (!c) return;
     if (c->comm) NcclApi::get().CommDestroy(c->comm);

@@ -52,6 +52,21 @@ __global__ void merge_copy_kernel(ShardPtrs p, const u64 *offsets, u64 n, OutT *
 struct Comm {
     ncclComm_t comm = nullptr;
     int rank = 0, n_ranks = 1, device = 0;
+    // Peer-memory exchange (ggq_comm_enable_peer): the partial-CSR buffers of one workspace per rank are exported
+    // with cudaIpc and mapped by every other rank, so the merge kernels read the shards' segments straight over
+    // NVLink/NVSwitch (P2P loads) — no all-gather, no staging copy.  Valid while batches stay within the capacities
+    // the buffers were pinned at; a larger batch falls back to the NCCL exchange for good (all ranks decide alike).
+    bool peer = false;
+    Workspace *peer_ws = nullptr;        // the local workspace whose buffers were exported
+    u64 peer_max_rows = 0, peer_max_ids = 0;
+    const u64 *peer_off[16] = {};        // [r]: rank r's partial offsets (null for the own rank)
+    const u32 *peer_cols[16] = {};       // [r]: rank r's partial column ids
+    ~Comm() {
+        for (int r = 0; r < 16; ++r) {
+            if (peer_off[r]) cudaIpcCloseMemHandle(const_cast<u64 *>(peer_off[r]));
+            if (peer_cols[r]) cudaIpcCloseMemHandle(const_cast<u32 *>(peer_cols[r]));
+        }
+    }
 };
 
 // NCCL is resolved with dlopen at the first collective call instead of being a link-time dependency: a host
@@ -150,6 +165,31 @@ inline void rows_sharded_device(const Matrix *m, Workspace *ws, Comm *c, const u
     u64 tot[kMaxShards], col_off[kMaxShards + 1];
     col_off[0] = 0;
     for (int r = 0; r < R; ++r) { tot[r] = ws->h_ctrl[r]; col_off[r + 1] = col_off[r] + tot[r]; }
+    if (c->peer && ws == c->peer_ws) {
+        bool within = n <= c->peer_max_rows;
+        for (int r = 0; r < R; ++r) within = within && tot[r] <= c->peer_max_ids;
+        if (within) {
+            // 2'. no transfer step: the all-gather of the totals above is the barrier ("every shard's partial CSR is
+            // complete"); the merge kernels gather the segments from peer memory, tile by tile
+            ShardPtrs p;
+            p.n = R;
+            for (int r = 0; r < R; ++r) {
+                p.off[r] = r == c->rank ? ws->d_offsets.p : c->peer_off[r];
+                p.cols[r] = r == c->rank ? reinterpret_cast<const u32 *>(ws->d_out.p) : c->peer_cols[r];
+            }
+            merge_shards(ws, p, n, col_bytes, total_out);
+            // nobody may overwrite its partial CSR (next query) before every peer has read it
+            NCCL_CHECK(NcclApi::get().AllGather(ws->g_tot.p + kMaxShards, ws->g_tot.p, 1, ncclUint64, c->comm, st));
+            CUDA_CHECK(cudaEventRecord(e1, st));
+            ws->exchange_bytes = 0;
+            for (int r = 0; r < R; ++r)
+                if (r != c->rank) ws->exchange_bytes += (n + 1) * 8 * 2 + tot[r] * 4;   // offsets are read by both merge kernels
+            ws->exchange_timed = true;
+            ws->launches += 5;
+            return;
+        }
+        c->peer = false;   // the exported buffers were (or will be) reallocated: the mappings are stale
+    }
     if (ws->g_off.n < size_t(R) * (n + 1)) ws->g_off.alloc(size_t(R) * (n + 1));
     if (ws->g_cols.n < std::max<u64>(col_off[R], 1)) ws->g_cols.alloc(col_off[R] + col_off[R] / 8 + 1024);
     // 2b. offsets: all-gather; column ids: all-gather-v as grouped broadcasts

@@ -204,6 +204,14 @@ int ggq_merge_shards_device(ggq_workspace *ws, uint64_t n, int n_shards, const u
 int ggq_comm_unique_id(uint8_t id[128]);
 int ggq_comm_init(const uint8_t id[128], int rank, int n_ranks, int device, ggq_comm **out);
 void ggq_comm_free(ggq_comm *c);
+/* Peer-memory exchange — collective, optional, one process per GPU on one NVLink/NVSwitch node.  Pins the partial-CSR
+ * buffers of `ws` at the given capacities (rows per batch, partial column ids per shard and batch), exports them with
+ * cudaIpc and maps every peer's.  ggq_get_rows_sharded_device on that workspace then skips the NCCL all-gather: its
+ * merge kernels read the shards' segments directly from peer memory over NVLink (transfer and merge are one pass),
+ * with two 8-byte all-gathers as barriers.  A batch beyond the capacities falls back to the NCCL exchange for good
+ * (every rank takes the same decision).  ggq_comm_peer_active tells which path the next query takes. */
+int ggq_comm_enable_peer(ggq_comm *c, ggq_workspace *ws, uint64_t max_rows, uint64_t max_ids);
+int ggq_comm_peer_active(const ggq_comm *c);
 /* Collective over the shards of one matrix: every rank passes the SAME batch (device memory) and ends with the
  * complete CSR: local descent, ncclAllGather of partial offsets + grouped ncclBroadcast of partial column ids over
  * NVLink, merge kernel.  Runs on the workspace stream. */

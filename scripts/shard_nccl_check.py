@@ -44,6 +44,23 @@ def main():
             assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), B
         print("rank %d B=%d total=%d exchange %.3f ms %.1f MB" % (rank, B, total, ws.stat("exchange_ms"),
                                                                   ws.stat("exchange_bytes") / 1e6), flush=True)
+    # peer-memory exchange (ggq_comm_enable_peer): merge straight from the peers' buffers over NVLink; then a batch
+    # beyond the pinned capacity, which must fall back to the NCCL exchange on every rank — same answers throughout
+    whole = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local) if rank == 0 else None
+    comm.enable_peer(ws, 400_000, 400_000 * 8)
+    assert comm.peer_active
+    for B, expect_peer in ((1, True), (1000, True), (300_000, True), (300_000, True), (0, True), (500_000, False), (1000, False)):
+        rows = torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen)
+        off, cols, total = ws.get_rows_sharded_device(comm, rows.data_ptr(), B, 8)
+        h_off, h_cols = d2h(off, (B + 1) * 8, np.uint64), d2h(cols, total * 8, np.uint64)
+        assert comm.peer_active == expect_peer, (B, comm.peer_active)
+        if rank == 0:
+            eoff, ecols = whole.get_rows_csr(rows.cpu().numpy().view(np.uint64))
+            assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), ("peer", B)
+        print("rank %d peer=%d B=%d total=%d exchange %.3f ms %.1f MB" % (rank, expect_peer, B, total, ws.stat("exchange_ms"),
+                                                                          ws.stat("exchange_bytes") / 1e6), flush=True)
+    if whole is not None:
+        whole.close()
     dist.barrier()
     ws.close(); sm.close(); comm.close()
     dist.destroy_process_group()
