@@ -91,14 +91,22 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 50 ms DURING the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+    """nvidia-smi clocks + throttle reasons sampled every 50 ms.  The sampler is started before the warm-up steps
+    (nvidia-smi needs up to a second to come up on an 8-GPU box) and only the samples stamped inside the timed
+    region are kept; if the region was too short to catch any, the samples of warm-up + timed region (the same
+    load) are reported and `window` says so."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
         self.index = index
+        self.t0 = self.t1 = None
+
+    def mark_begin(self):
+        import datetime
+        self.t0 = datetime.datetime.now()
 
     def start(self):
         try:
@@ -109,6 +117,8 @@ class ClockSampler:
             self.p = None
 
     def stop(self):
+        import datetime
+        self.t1 = datetime.datetime.now()
         if self.p is not None:
             self.p.terminate()
             try:
@@ -117,29 +127,34 @@ class ClockSampler:
                 self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for line in self.f.read().splitlines():
             parts = [x.strip() for x in line.split(",")]
-            if len(parts) < 7:
+            if len(parts) < 8:
                 continue
             try:
-                sm.append(float(parts[0]))
-                mx.append(float(parts[1]))
+                ts = datetime.datetime.strptime(parts[0], "%Y/%m/%d %H:%M:%S.%f")
+                rows.append((ts, float(parts[1]), float(parts[2]),
+                             [nm for nm, v in zip(names, parts[4:8]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for nm, v in zip(names, parts[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
         self.f.close()
         try:
             os.unlink(self.f.name)
         except OSError:
             pass
-        if not sm:
+        window = "timed"
+        inside = [r for r in rows if self.t0 is None or self.t0 <= r[0] <= self.t1]
+        if not inside:
+            inside, window = rows, "warmup+timed"
+        if not inside:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+        reasons = set()
+        for r in inside:
+            reasons.update(r[3])
+        return {"sm_mhz": float(np.median([r[1] for r in inside])), "sm_max_mhz": float(max(r[2] for r in inside)),
+                "reasons": sorted(reasons), "samples": len(inside), "window": window}
 
 
 # --------------------------------------------------------------------------------------------
@@ -270,11 +285,12 @@ def run_ours(args):
         return ws.get_rows_device(batches[i % n_pool].data_ptr(), B, 8)
 
     # ---- device-resident number ----------------------------------------------------------
+    clocks = ClockSampler(local)
+    clocks.start()
     for i in range(W):
         device_step(i)
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
+    clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kern_ms, touches, probes, ids, launches = [], 0, 0, 0, 0
     with torch.cuda.stream(stream):
@@ -450,11 +466,12 @@ def run_c5(args):
     if not args.no_peer:
         # merge straight from the peers' partial CSRs over NVLink (cudaIpc); capacity: this batch size, ids with slack
         comm.enable_peer(ws, B, int(B * m * d * 1.3 / world) + (1 << 20))
+    clocks = ClockSampler(local)
+    clocks.start()
     for i in range(W):
         ws.get_rows_sharded_device(comm, batches[i % n_pool].data_ptr(), B, 8)
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
+    clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kern_ms, xch_ms, xch_bytes, touches, ids_total, launches = [], [], 0, 0, 0, 0
     with torch.cuda.stream(stream):

@@ -723,7 +723,8 @@ double ggq_workspace_stat(const ggq_workspace *ws, int what) {
         case GGQ_STAT_LAUNCHES: return double(ws->launches);
         case GGQ_STAT_EXCHANGE_MS: {
             float ms = 0.f;
-            if (!ws->exchange_timed || cudaEventElapsedTime(&ms, ws->ev2, ws->ev3) != cudaSuccess) return -1.0;
+            if (!ws->exchange_timed || cudaEventSynchronize(ws->ev3) != cudaSuccess ||
+                cudaEventElapsedTime(&ms, ws->ev2, ws->ev3) != cudaSuccess) return -1.0;
             return ms;
         }
         case GGQ_STAT_EXCHANGE_BYTES: return double(ws->exchange_bytes);
