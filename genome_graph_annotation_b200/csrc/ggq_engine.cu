@@ -905,7 +905,6 @@ static u64 pipeline_chunk() {
     }();
     return v;
 }
-#define kPipelineChunk pipeline_chunk()
 // count_labels returns only num_columns counters, so nothing but the first host->device copy is exposed: larger
 // chunks (measured on C4: 2^20 -> 1.03e9, 2^22 -> 1.12e9 rows/s); get_rows is best at 2^20 (device->host tail)
 static const u64 kCountChunk = u64(1) << 22;
@@ -920,7 +919,7 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     // Chunks rotate over kPipelineDepth workspaces (streams).  Chunk k+1 is enqueued (H2D, ordering, descent, scan)
     // BEFORE the host waits for chunk k's size, so the device never idles on a host round trip, and the device->host
     // copy of chunk k overlaps the descent of the chunks after it.
-    const u64 n_chunks = n ? (n + kPipelineChunk - 1) / kPipelineChunk : 1;
+    const u64 n_chunks = n ? (n + pipeline_chunk() - 1) / pipeline_chunk() : 1;
     const bool brwt = m->kind == Matrix::BRWT;
     std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     int rc = GGQ_OK;
@@ -930,19 +929,19 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
         bool fits = true;
         int launches = 0;
         u64 probes = 0, touches = 0;
-        auto chunk_rows = [&](u64 k) { return std::min<u64>(kPipelineChunk, n - k * kPipelineChunk); };
+        auto chunk_rows = [&](u64 k) { return std::min<u64>(pipeline_chunk(), n - k * pipeline_chunk()); };
         auto begin = [&](u64 k) {
             Workspace *ws = w[k % w.size()];
             const u64 nc = chunk_rows(k);
             ws->reserve_rows(nc);
-            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kPipelineChunk, nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * pipeline_chunk(), nc * 8, cudaMemcpyHostToDevice, ws->stream));
             if (brwt) brwt_rows_begin(m, ws, ws->d_rows.p, nc);
         };
         begin(0);
         for (u64 k = 0; k < n_chunks; ++k) {
             if (k + 1 < n_chunks) begin(k + 1);
             Workspace *ws = w[k % w.size()];
-            const u64 nc = chunk_rows(k), r0 = k * kPipelineChunk;
+            const u64 nc = chunk_rows(k), r0 = k * pipeline_chunk();
             u64 total = 0;
             if (brwt) brwt_rows_finish(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             else rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
