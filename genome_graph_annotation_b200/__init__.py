@@ -81,6 +81,8 @@ def lib():
         "ggq_rows_count": (C.c_uint64, [vp]),
         "ggq_rows_result_free": (None, [vp]),
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_image_save": (C.c_int, [vp, C.c_char_p]),
+        "ggq_image_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
         "ggq_get_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p]),
         "ggq_get_top_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u64p, u64p, u64p]),
         "ggq_get_labels_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p, C.c_uint64, u64p]),
@@ -239,6 +241,16 @@ class GpuMatrix:
         m = cls(h.value, "brwt")
         m.consumed = used.value
         return m
+
+    @classmethod
+    def load_image(cls, path, device=0):
+        """Flattened device image written by save_image (ggq_image_load): uploaded as it is."""
+        h = C.c_void_p()
+        _check(lib().ggq_image_load(os.fsencode(path), device, C.byref(h)))
+        return cls(h.value, "brwt")
+
+    def save_image(self, path):
+        _check(lib().ggq_image_save(self._h, os.fsencode(path)))
 
     @classmethod
     def load_brwt_shard(cls, data, shard, n_shards, device=0):

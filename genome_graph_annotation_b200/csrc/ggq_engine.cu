@@ -25,6 +25,7 @@
 #include "ggq_builder.cuh"
 #include "ggq_bv.cuh"
 #include "ggq_colmajor.cuh"
+#include "ggq_image.hpp"
 #include "ggq_shard.cuh"
 
 namespace ggq {
@@ -226,14 +227,25 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
 }
 
 void Matrix::derive_stats() {
-    n_nodes = tree.nodes.size();
-    total_column_size = 0;
-    num_relations = 0;
-    for (const FlatNode &n : tree.nodes) {
-        total_column_size += n.size;
-        if (n.children.empty())   // column-sharded: owned columns only
-            for (u32 c : n.cols)
-                if (tree.col_owned.empty() || tree.col_owned[c]) num_relations += n.ones;
+    if (!tree.nodes.empty()) {   // (a matrix restored from an image file has no host nodes: stats come from the file)
+        n_nodes = tree.nodes.size();
+        total_column_size = 0;
+        num_relations = 0;
+        for (const FlatNode &n : tree.nodes) {
+            total_column_size += n.size;
+            if (n.children.empty())   // column-sharded: owned columns only
+                for (u32 c : n.cols)
+                    if (tree.col_owned.empty() || tree.col_owned[c]) num_relations += n.ones;
+        }
+        // per lane: length and popcount of its vector (get_column: leaf size, all-ones ancestors BRWT.cpp:77-78)
+        lane_size_h.assign(tree.lane_node.size(), 0);
+        lane_ones_h.assign(tree.lane_node.size(), 0);
+        for (size_t li = 0; li < tree.lane_node.size(); ++li) {
+            const u32 node = tree.lane_node[li];
+            if (node == ~0u || !tree.present(node)) continue;
+            lane_size_h[li] = tree.nodes[node].size;
+            lane_ones_h[li] = tree.nodes[node].ones;
+        }
     }
     configure_rows(0, ~0u);
     device_bytes = slots.bytes() + sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
@@ -764,6 +776,22 @@ int ggq_merge_shards_device(ggq_workspace *ws, uint64_t n, int n_shards, const u
     GGQ_CATCH
 }
 
+int ggq_image_save(const ggq_matrix *m, const char *path) {
+    GGQ_TRY
+    if (!m || !path) return fail(GGQ_ERR_ARG, "bad argument");
+    image_save(m, path);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_image_load(const char *path, int device, ggq_matrix **out) {
+    GGQ_TRY
+    if (!path || !out) return fail(GGQ_ERR_ARG, "bad argument");
+    *out = static_cast<ggq_matrix *>(image_load(path, device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 int ggq_comm_unique_id(uint8_t id[128]) {
     GGQ_TRY
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
@@ -919,7 +947,26 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     // Chunks rotate over kPipelineDepth workspaces (streams).  Chunk k+1 is enqueued (H2D, ordering, descent, scan)
     // BEFORE the host waits for chunk k's size, so the device never idles on a host round trip, and the device->host
     // copy of chunk k overlaps the descent of the chunks after it.
-    const u64 n_chunks = n ? (n + pipeline_chunk() - 1) / pipeline_chunk() : 1;
+    // Chunk plan: full chunks in the middle, quarter and half chunks at both ends — the first device->host copy
+    // starts early and the last one (which nothing overlaps) is short.
+    std::vector<u64> start = {0};
+    {
+        const u64 c = pipeline_chunk();
+        if (n >= 4 * c) {
+            start.push_back(c / 4);
+            start.push_back(c / 4 + c / 2);
+            const u64 tail = c / 2 + c / 4;
+            while (n - start.back() > tail + c) start.push_back(start.back() + c);
+            const u64 rest = n - start.back() - tail;   // in (0, c]
+            if (rest > 0) start.push_back(start.back() + rest);
+            start.push_back(start.back() + c / 2);
+            start.push_back(n);
+        } else {
+            while (n - start.back() > c) start.push_back(start.back() + c);
+            if (n > start.back() || start.size() == 1) start.push_back(n);
+        }
+    }
+    const u64 n_chunks = start.size() - 1;
     const bool brwt = m->kind == Matrix::BRWT;
     std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     int rc = GGQ_OK;
@@ -929,19 +976,19 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
         bool fits = true;
         int launches = 0;
         u64 probes = 0, touches = 0;
-        auto chunk_rows = [&](u64 k) { return std::min<u64>(pipeline_chunk(), n - k * pipeline_chunk()); };
+        auto chunk_rows = [&](u64 k) { return start[k + 1] - start[k]; };
         auto begin = [&](u64 k) {
             Workspace *ws = w[k % w.size()];
             const u64 nc = chunk_rows(k);
             ws->reserve_rows(nc);
-            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * pipeline_chunk(), nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + start[k], nc * 8, cudaMemcpyHostToDevice, ws->stream));
             if (brwt) brwt_rows_begin(m, ws, ws->d_rows.p, nc);
         };
         begin(0);
         for (u64 k = 0; k < n_chunks; ++k) {
             if (k + 1 < n_chunks) begin(k + 1);
             Workspace *ws = w[k % w.size()];
-            const u64 nc = chunk_rows(k), r0 = k * pipeline_chunk();
+            const u64 nc = chunk_rows(k), r0 = start[k];
             u64 total = 0;
             if (brwt) brwt_rows_finish(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             else rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
@@ -1343,7 +1390,7 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
             const FlatTree &t = m->tree;
             u32 p0 = t.col_path_off[col], p1 = t.col_path_off[col + 1];
             u32 leaf_li = t.col_path[p1 - 1];
-            cnt = t.nodes[t.lane_node[leaf_li]].ones;
+            cnt = m->lane_ones_h[leaf_li];
             // an empty ancestor makes the column empty (BRWT.cpp:58-62); an empty leaf too
             d_res.alloc(std::max<u64>(cnt, 1));
             if (cnt) {
@@ -1351,8 +1398,7 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
                 lane_enumerate_kernel<<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res.p);
                 for (u32 p = p1 - 1; p-- > p0;) {
                     u32 li = t.col_path[p];
-                    const FlatNode &a = t.nodes[t.lane_node[li]];
-                    if (a.ones == a.size) continue;  // all ones: identity (BRWT.cpp:77-78)
+                    if (m->lane_ones_h[li] == m->lane_size_h[li]) continue;  // all ones: identity (BRWT.cpp:77-78)
                     lane_select_kernel<<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res.p, cnt);
                 }
                 CUDA_CHECK(cudaGetLastError());

@@ -69,6 +69,7 @@ struct Matrix {
     // stats
     u64 n_nodes = 0, total_column_size = 0, num_relations = 0, device_bytes = 0;
     mutable u64 last_probes = 0;
+    std::vector<u64> lane_size_h, lane_ones_h;   // per lane: bits / set bits of its vector (host copy)
 
     // descent kernel configuration
     u32 bm_words = 1, rb = 8, cap_s = 64, cap_spill = 0, rows_grid = 148;

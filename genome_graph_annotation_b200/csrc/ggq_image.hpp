@@ -1,0 +1,178 @@
+// Flattened device-image file: the GPU-resident layout of a BRWT written next to the
+// .brwt.annodbg it came from, so that a restart uploads the arrays as they are instead of re-parsing the
+// reference stream (RRR decode, BRWT.cpp:87-111), re-flattening it and rebuilding rank headers / select samples.
+//
+//   header   magic "GGQIMG01", endianness tag, matrix shape, the BRWT stats the reference API reports
+//   tables   the host-side geometry (group records, lane tables, leaf order, column paths, shard plan) + FNV-1a
+//   arrays   slots (16-byte slots with inline rank headers), select samples, superblock bases, lane totals
+//   trailer  end tag (a truncated file is rejected)
+//
+// Host words are little-endian (sm_100a hosts are); the tag makes a foreign file fail loudly instead of misreading.
+#pragma once
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace ggq {
+
+static const char kImageMagic[8] = {'G', 'G', 'Q', 'I', 'M', 'G', '0', '1'};
+static const u64 kImageEnd = 0x454e44474751494dull;
+static const u32 kImageEndian = 0x01020304u;
+
+struct ImageHeader {
+    char magic[8];
+    u32 endian, kind;
+    u64 n_rows, n_cols, n_nodes, total_column_size, num_relations;
+    u64 total_slots, total_sb, total_sel;
+    u32 max_depth, multi_leaf, shard, n_shards, cut_depth, reserved;
+};
+
+struct Fnv {
+    u64 h = 0xcbf29ce484222325ull;
+    void add(const void *p, size_t n) {
+        const unsigned char *b = static_cast<const unsigned char *>(p);
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 0x100000001b3ull; }
+    }
+};
+
+struct ImageFile {
+    FILE *f = nullptr;
+    Fnv sum;
+    explicit ImageFile(const char *path, const char *mode) : f(std::fopen(path, mode)) {
+        if (!f) throw ParseError(std::string("cannot open image file ") + path);
+    }
+    ~ImageFile() { if (f) std::fclose(f); }
+    void put(const void *p, size_t n) {
+        if (n && std::fwrite(p, 1, n, f) != n) throw std::runtime_error("image write failed (disk full?)");
+        sum.add(p, n);
+    }
+    void get(void *p, size_t n) {
+        if (n && std::fread(p, 1, n, f) != n) throw ParseError("image file truncated");
+        sum.add(p, n);
+    }
+    template <typename T> void put_vec(const std::vector<T> &v) {
+        const u64 n = v.size();
+        put(&n, 8);
+        put(v.data(), size_t(n) * sizeof(T));
+    }
+    template <typename T> void get_vec(std::vector<T> *v, u64 limit) {
+        u64 n = 0;
+        get(&n, 8);
+        if (n > limit) throw ParseError("image file: implausible table size");
+        v->resize(size_t(n));
+        get(v->data(), size_t(n) * sizeof(T));
+    }
+};
+
+// device array <-> file through a pinned staging buffer (the arrays are tens of GB: no host copy of the whole)
+template <typename T>
+inline void image_put_device(ImageFile &io, const DeviceBuf<T> &d, unsigned char *stage, size_t stage_bytes) {
+    const u64 bytes = d.n * sizeof(T);
+    if (std::fwrite(&bytes, 1, 8, io.f) != 8) throw std::runtime_error("image write failed");
+    const unsigned char *src = reinterpret_cast<const unsigned char *>(d.p);
+    for (u64 o = 0; o < bytes; o += stage_bytes) {
+        const size_t n = size_t(std::min<u64>(stage_bytes, bytes - o));
+        CUDA_CHECK(cudaMemcpy(stage, src + o, n, cudaMemcpyDeviceToHost));
+        if (std::fwrite(stage, 1, n, io.f) != n) throw std::runtime_error("image write failed (disk full?)");
+    }
+}
+
+template <typename T>
+inline void image_get_device(ImageFile &io, DeviceBuf<T> &d, u64 expect_count, unsigned char *stage, size_t stage_bytes) {
+    u64 bytes = 0;
+    if (std::fread(&bytes, 1, 8, io.f) != 8) throw ParseError("image file truncated");
+    if (bytes != expect_count * sizeof(T)) throw ParseError("image file: array size does not match its header");
+    d.alloc(size_t(expect_count));
+    unsigned char *dst = reinterpret_cast<unsigned char *>(d.p);
+    for (u64 o = 0; o < bytes; o += stage_bytes) {
+        const size_t n = size_t(std::min<u64>(stage_bytes, bytes - o));
+        if (std::fread(stage, 1, n, io.f) != n) throw ParseError("image file truncated");
+        CUDA_CHECK(cudaMemcpy(dst + o, stage, n, cudaMemcpyHostToDevice));
+    }
+}
+
+struct PinnedStage {
+    unsigned char *p = nullptr;
+    size_t bytes = size_t(64) << 20;
+    PinnedStage() { CUDA_CHECK(cudaMallocHost(&p, bytes)); }
+    ~PinnedStage() { if (p) cudaFreeHost(p); }
+};
+
+inline void image_save(const Matrix *m, const char *path) {
+    if (m->kind != Matrix::BRWT) throw std::runtime_error("only BRWT images can be saved");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    const FlatTree &t = m->tree;
+    ImageFile io(path, "wb");
+    ImageHeader h;
+    std::memset(&h, 0, sizeof(h));
+    std::memcpy(h.magic, kImageMagic, 8);
+    h.endian = kImageEndian; h.kind = 0;
+    h.n_rows = t.n_rows; h.n_cols = t.n_cols;
+    h.n_nodes = m->n_nodes; h.total_column_size = m->total_column_size; h.num_relations = m->num_relations;
+    h.total_slots = m->slots.n; h.total_sb = m->sb_base.n; h.total_sel = m->sel.n;
+    h.max_depth = t.max_depth; h.multi_leaf = t.multi_column_leaves; h.shard = t.shard; h.n_shards = t.n_shards;
+    h.cut_depth = t.cut_depth;
+    io.put(&h, sizeof(h));
+    io.put_vec(t.group_hot); io.put_vec(t.group_nblocks);
+    io.put_vec(t.lane_info); io.put_vec(t.lane_aux); io.put_vec(t.lane_sb_off); io.put_vec(t.lane_sel_off);
+    io.put_vec(t.leaf_col); io.put_vec(t.col_path_off); io.put_vec(t.col_path);
+    io.put_vec(t.col_owned); io.put_vec(t.col_owner);
+    io.put_vec(m->lane_size_h); io.put_vec(m->lane_ones_h);
+    const u64 check = io.sum.h;
+    if (std::fwrite(&check, 1, 8, io.f) != 8) throw std::runtime_error("image write failed");
+    PinnedStage st;
+    image_put_device(io, m->slots, st.p, st.bytes);
+    image_put_device(io, m->sel, st.p, st.bytes);
+    image_put_device(io, m->sb_base, st.p, st.bytes);
+    image_put_device(io, m->lane_ones, st.p, st.bytes);
+    if (std::fwrite(&kImageEnd, 1, 8, io.f) != 8 || std::fflush(io.f) != 0) throw std::runtime_error("image write failed");
+}
+
+inline Matrix *image_load(const char *path, int device) {
+    ImageFile io(path, "rb");
+    ImageHeader h;
+    io.get(&h, sizeof(h));
+    if (std::memcmp(h.magic, kImageMagic, 8) != 0) throw ParseError("not a ggq image file (or another version)");
+    if (h.endian != kImageEndian || h.kind != 0) throw ParseError("image file of a foreign byte order / kind");
+    if (h.n_rows >= kMaxRows || h.n_cols >= (u64(1) << 31)) throw LimitError("image exceeds engine limits");
+    std::unique_ptr<Matrix> m(new Matrix());
+    m->kind = Matrix::BRWT;
+    m->device = device;
+    CUDA_CHECK(cudaSetDevice(device));
+    FlatTree &t = m->tree;
+    t.n_rows = h.n_rows; t.n_cols = h.n_cols;
+    const u64 lim = u64(1) << 33;
+    io.get_vec(&t.group_hot, kMaxGroups); io.get_vec(&t.group_nblocks, kMaxGroups);
+    io.get_vec(&t.lane_info, u64(kMaxGroups) * 4); io.get_vec(&t.lane_aux, u64(kMaxGroups) * 4);
+    io.get_vec(&t.lane_sb_off, u64(kMaxGroups) * 4); io.get_vec(&t.lane_sel_off, u64(kMaxGroups) * 4);
+    io.get_vec(&t.leaf_col, lim); io.get_vec(&t.col_path_off, lim); io.get_vec(&t.col_path, lim);
+    io.get_vec(&t.col_owned, lim); io.get_vec(&t.col_owner, lim);
+    io.get_vec(&m->lane_size_h, u64(kMaxGroups) * 4); io.get_vec(&m->lane_ones_h, u64(kMaxGroups) * 4);
+    const u64 expect = io.sum.h;
+    u64 check = 0;
+    if (std::fread(&check, 1, 8, io.f) != 8 || check != expect) throw ParseError("image file: table checksum mismatch");
+    const size_t G = t.group_hot.size();
+    if (G == 0 || t.group_nblocks.size() != G || t.lane_info.size() != 4 * G || t.lane_aux.size() != 4 * G ||
+        t.lane_sb_off.size() != 4 * G || t.lane_sel_off.size() != 4 * G || m->lane_size_h.size() != 4 * G ||
+        m->lane_ones_h.size() != 4 * G || t.col_path_off.size() != t.n_cols + 1 ||
+        (!t.col_owned.empty() && t.col_owned.size() != t.n_cols))
+        throw ParseError("image file: inconsistent tables");
+    t.total_slots = h.total_slots; t.total_sb = h.total_sb; t.total_sel = h.total_sel;
+    t.max_depth = h.max_depth; t.multi_column_leaves = h.multi_leaf != 0;
+    t.shard = h.shard; t.n_shards = h.n_shards; t.cut_depth = h.cut_depth;
+    m->upload_tables(t);   // group records and lane tables; allocates lane_ones / sb_base
+    PinnedStage st;
+    image_get_device(io, m->slots, h.total_slots, st.p, st.bytes);
+    image_get_device(io, m->sel, h.total_sel, st.p, st.bytes);
+    image_get_device(io, m->sb_base, h.total_sb, st.p, st.bytes);
+    image_get_device(io, m->lane_ones, u64(G) * 4, st.p, st.bytes);
+    u64 end = 0;
+    if (std::fread(&end, 1, 8, io.f) != 8 || end != kImageEnd) throw ParseError("image file truncated");
+    m->refresh_img();
+    m->n_nodes = h.n_nodes; m->total_column_size = h.total_column_size; m->num_relations = h.num_relations;
+    m->derive_stats();   // no host nodes: keeps the stats above, configures the descent kernel
+    return m.release();
+}
+
+}  // namespace ggq

@@ -64,6 +64,14 @@ int ggq_colmajor_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, i
 int ggq_brwt_synthesize(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed,
                         uint32_t arity, int device, ggq_matrix **out);
 
+/* Flattened device-image file.  ggq_image_save writes the GPU-resident layout of a BRWT (header,
+ * geometry tables with a checksum, slot arena, select samples) to `path`; ggq_image_load uploads it as it is —
+ * no RRR decode, no flattening, no rank-header construction (what BRWT::load + upload cost at every start,
+ * BRWT.cpp:87-111).  The loaded matrix answers every query identically; BinaryMatrix::serialize still needs the
+ * original stream (the adapters keep it).  A truncated, foreign-endian or other-version file: GGQ_ERR_FORMAT. */
+int ggq_image_save(const ggq_matrix *m, const char *path);
+int ggq_image_load(const char *path, int device, ggq_matrix **out);
+
 void ggq_free(ggq_matrix *m);
 
 /* Host-only: parse + flatten a serialized BRWT exactly as ggq_brwt_load does, without touching the

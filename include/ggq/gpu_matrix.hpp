@@ -185,6 +185,29 @@ class GpuBRWT final : public GpuMatrixBase {
     // BRWT stats (BRWT.hpp:44-49)
     uint64_t num_nodes() const { return h_ ? ggq_num_nodes(h_.get()) : 0; }
     uint64_t total_column_size() const { return h_ ? ggq_total_column_size(h_.get()) : 0; }
+
+    // Flattened device image (ggq_image_save / ggq_image_load): written once next to the .brwt.annodbg, it restores
+    // the GPU-resident layout without parsing the stream again.  `stream_path` (optional) names the serialized
+    // matrix the image was made from; it is read back only if serialize() is called.
+    void save_image(const std::string &path) const { check(ggq_image_save(handle(), path.c_str())); }
+    bool load_image(const std::string &path, const std::string &stream_path = std::string()) {
+        ggq_matrix *m = nullptr;
+        if (ggq_image_load(path.c_str(), device_, &m) != GGQ_OK) return false;
+        h_.reset(m, [](ggq_matrix *p) { ggq_free(p); });
+        stream_.clear();
+        stream_path_ = stream_path;
+        return true;
+    }
+    void serialize(std::ostream &out) const override {
+        if (!stream_.empty() || stream_path_.empty()) { GpuMatrixBase::serialize(out); return; }
+        if (!out.good()) throw std::ofstream::failure("Error when dumping the matrix");
+        std::ifstream in(stream_path_, std::ios::binary);
+        if (!in.good()) throw std::ofstream::failure("ggq: cannot read the serialized matrix behind the image");
+        out << in.rdbuf();
+    }
+
+  private:
+    std::string stream_path_;
 };
 
 class GpuColMajor final : public GpuMatrixBase {

@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <fstream>
 #include <random>
 #include <sstream>
 
@@ -111,6 +112,18 @@ static void check_brwt(Columns &&cols, int arity, bool relax) {
     compare(ref, gpu, stream);
     ggq::GpuBRWT copy = gpu;  // copies share the device image (BRWT is copyable, BRWT.hpp:27-31)
     REQUIRE(copy.get_column(0) == ref.get_column(0));
+    // flattened device image next to the serialized matrix: restored without parsing, same answers, and
+    // serialize() still reproduces the reference's stream byte for byte
+    const std::string img = "/tmp/ggq_adapter_test.ggqimg", ser = "/tmp/ggq_adapter_test.brwt";
+    gpu.save_image(img);
+    { std::ofstream f(ser, std::ios::binary); f << stream; }
+    ggq::GpuBRWT restored;
+    REQUIRE(restored.load_image(img, ser));
+    REQUIRE(restored.num_nodes() == ref.num_nodes());
+    compare(ref, restored, stream);
+    REQUIRE(!restored.load_image(ser));   // not an image
+    std::remove(img.c_str());
+    std::remove(ser.c_str());
 }
 
 static void check_colmajor(uint64_t n, uint64_t m, double d, unsigned seed) {

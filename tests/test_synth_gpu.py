@@ -116,6 +116,15 @@ def test_pipelined_host_api_matches_single_shot(ggq):
         hist = np.bincount(cols[:total].astype(np.int64), minlength=m).astype(np.uint64)
         assert np.array_equal(gm.count_labels(rows), hist)
         assert np.array_equal(gm.count_labels(np.tile(rows, 3)), hist * np.uint64(3))
+        # >= 4 chunks: the ramped chunk plan (quarter / half chunks at both ends)
+        rows3 = np.tile(rows, 3)
+        off3 = np.empty(rows3.size + 1, np.uint64)
+        cols3 = np.empty(3 * total + 16, np.uint32)
+        assert gm.get_rows_into(rows3, off3, cols3) == 3 * total
+        for rep in range(3):
+            lo = rep * rows.size
+            assert np.array_equal(off3[lo:lo + rows.size + 1] - off3[lo], off)
+            assert np.array_equal(cols3[int(off3[lo]):int(off3[lo + rows.size])], cols[:total].astype(np.uint32))
         # compact u32 ids: same CSR
         cols32 = np.empty(cols.size, np.uint32)
         off32 = np.empty_like(off)
@@ -166,5 +175,46 @@ def test_labels_batch_equals_per_query_get_labels(ggq):
         # no queries
         loff, cols, cnt = gm.get_labels_batch(np.zeros(0, np.uint64), np.zeros(1, np.uint64), 0.5)
         assert loff.tolist() == [0] and cols.size == 0
+    finally:
+        gm.close()
+
+
+def test_concurrent_const_calls_from_many_threads(ggq):
+    """The reference's callers run const queries concurrently from a thread pool on ONE matrix object
+    (main.cpp:462-491); the engine answers every calling thread on its own stream + scratch (workspace pool).
+    ctypes releases the GIL during the calls, so these really overlap."""
+    import threading
+    n, m, d = 80_000, 200, 0.03
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=21, arity=4)
+    try:
+        rng = np.random.default_rng(9)
+        batches = [rng.integers(0, n, int(sz)).astype(np.uint64) for sz in rng.integers(1, 60_000, 24)]
+        expect = [gm.get_rows_csr(b) for b in batches]
+        expect_cnt = [gm.count_labels(b) for b in batches]
+        expect_lab = [gm.get_labels(b, 0.02) for b in batches]
+        errors = []
+
+        def worker(tid):
+            try:
+                for rep in range(3):
+                    for i in range(tid, len(batches), 4):
+                        off, cols = gm.get_rows_csr(batches[i])
+                        assert np.array_equal(off, expect[i][0]) and np.array_equal(cols, expect[i][1])
+                        assert np.array_equal(gm.count_labels(batches[i]), expect_cnt[i])
+                        lc, lv = gm.get_labels(batches[i], 0.02)
+                        assert np.array_equal(lc, expect_lab[i][0]) and np.array_equal(lv, expect_lab[i][1])
+                        col = int(batches[i][0]) % m
+                        hc = gm.has_column(batches[i][:1000], col)
+                        ex = np.array([col in cols[off[t]:off[t + 1]] for t in range(min(1000, batches[i].size))])
+                        assert np.array_equal(hc.astype(bool), ex)
+            except Exception as e:   # noqa: BLE001
+                errors.append((tid, repr(e)))
+
+        threads = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not errors, errors
     finally:
         gm.close()
