@@ -947,22 +947,25 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     // Chunks rotate over kPipelineDepth workspaces (streams).  Chunk k+1 is enqueued (H2D, ordering, descent, scan)
     // BEFORE the host waits for chunk k's size, so the device never idles on a host round trip, and the device->host
     // copy of chunk k overlaps the descent of the chunks after it.
-    // Chunk plan: full chunks in the middle, quarter and half chunks at both ends — the first device->host copy
-    // starts early and the last one (which nothing overlaps) is short.
+    // Chunk plan: full chunks in the middle (large launches cost less per row), geometric ramps at both
+    // ends — the first device->host copy starts early and the last one (which nothing overlaps) is short.
     std::vector<u64> start = {0};
     {
         const u64 c = pipeline_chunk();
-        if (n >= 4 * c) {
-            start.push_back(c / 4);
-            start.push_back(c / 4 + c / 2);
-            const u64 tail = c / 2 + c / 4;
-            while (n - start.back() > tail + c) start.push_back(start.back() + c);
-            const u64 rest = n - start.back() - tail;   // in (0, c]
-            if (rest > 0) start.push_back(start.back() + rest);
-            start.push_back(start.back() + c / 2);
+        std::vector<u64> ramp;
+        for (u64 r = std::max<u64>(c / 8, u64(1) << 18); r < c; r *= 2) ramp.push_back(r);
+        u64 ramp_sum = 0;
+        for (u64 r : ramp) ramp_sum += r;
+        if (!ramp.empty() && n >= 2 * ramp_sum + c) {
+            for (u64 r : ramp) start.push_back(start.back() + r);
+            while (n - start.back() > ramp_sum + c) start.push_back(start.back() + c);
+            const u64 rest = n - start.back() - ramp_sum;   // in (0, c]
+            start.push_back(start.back() + rest);
+            for (size_t i = ramp.size(); i-- > 1;) start.push_back(start.back() + ramp[i]);
             start.push_back(n);
         } else {
-            while (n - start.back() > c) start.push_back(start.back() + c);
+            const u64 cs = std::min<u64>(c, u64(1) << 20);
+            while (n - start.back() > cs) start.push_back(start.back() + cs);
             if (n > start.back() || start.size() == 1) start.push_back(n);
         }
     }

@@ -43,6 +43,20 @@ def test_no_cpu_fallback(ggq):
         ggq.GpuMatrix.synthesize_brwt(100, 10, 0.1)
 
 
+def test_image_loader_rejects_non_images_without_a_device(ggq, tmp_path):
+    """ggq_image_load validates the header before it touches the device: a missing file, a serialized BRWT stream
+    (not an image) and a short file are GGQ_ERR_FORMAT on any box."""
+    g = np.load(os.path.join(GOLD, "brwt_400x40_greedy_relax7.npz"))
+    not_image = tmp_path / "m.brwt"
+    not_image.write_bytes(g["stream"].tobytes())
+    short = tmp_path / "short.ggqimg"
+    short.write_bytes(b"GGQIMG01" + b"\0" * 10)
+    for path in (str(tmp_path / "missing.ggqimg"), str(not_image), str(short)):
+        with pytest.raises(ggq.GgqError) as e:
+            ggq.GpuMatrix.load_image(path)
+        assert e.value.code == -1, path
+
+
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "brwt_*.npz"))))
 def test_host_flattener_vs_golden(ggq, path):
     g = np.load(path)
