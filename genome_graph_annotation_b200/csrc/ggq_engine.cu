@@ -192,7 +192,10 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
         u32 worst = simulate_stack(tree, rb, kItemsPerIter) + 8;
         cap_s = (std::max<u32>(worst, 32) + 1) & ~1u;
         cap_spill = 0;
-        if (cap_s > 512) { cap_spill = cap_s - 512; cap_s = 512; }   // deep/wide trees: overflow to global memory
+        // deep/wide trees: overflow to global memory (GGQ_STACK_CAP lowers the shared part: the tests use it to run
+        // the SPILL instantiation on ordinary trees)
+        const u32 cap_limit = std::min<u32>(std::max<u32>(env_u32("GGQ_STACK_CAP", 512) & ~1u, 16), 512);
+        if (cap_s > cap_limit) { cap_spill = cap_s - cap_limit; cap_s = cap_limit; }
         rows_smem = rows_smem_bytes(cap_s, rb, bm_words);
         if (rows_smem <= size_t(max_smem) || rb == 1) break;
         rb >>= 1;
@@ -471,7 +474,7 @@ static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         size_t out_bytes = size_t(total) * col_bytes;
         if (ws->d_out.n < out_bytes) ws->d_out.alloc(out_bytes + out_bytes / 8 + 1024);
         if (total) {
-            u32 g = u32((n * 8 + 255) / 256);
+            u32 g = u32(((n + kGatherRows - 1) / kGatherRows * 8 + 255) / 256);
             if (col_bytes == 8)
                 gather_rows_kernel<u64><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
                                                           reinterpret_cast<u64 *>(ws->d_out.p));

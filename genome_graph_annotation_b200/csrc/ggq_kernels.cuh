@@ -157,16 +157,35 @@ header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, Chun
     }
 }
 
-// CSR assembly in the caller's query order: 8 lanes copy one row from its chunk in the arena.
+// CSR assembly in the caller's query order: 8 lanes copy one row from its chunk in the arena.  The chunk of a row sits
+// where its tile happened to allocate it (processing order), so the read is a dependent random gather: every 8-lane
+// group handles kGatherRows rows with all metadata loads, then all source loads, issued back to back.
+constexpr int kGatherRows = 4;
 template <typename OutT>
-__global__ void gather_rows_kernel(const u32 *tmp_cols, const u64 *row_tmp_off, const u64 *offsets,
-                                   u64 n, OutT *out) {
-    const u64 q = (u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 3;
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const u32 *tmp_cols, const u64 *row_tmp_off, const u64 *offsets, u64 n, OutT *out) {
+    const u64 grp = (u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 3;
     const u32 sub = threadIdx.x & 7;
-    if (q >= n) return;
-    const u64 dst0 = offsets[q], len = offsets[q + 1] - dst0;
-    const u64 src0 = row_tmp_off[q];
-    for (u64 i = sub; i < len; i += 8) out[dst0 + i] = OutT(tmp_cols[src0 + i]);
+    const u64 n_grp = (u64(gridDim.x) * blockDim.x) >> 3;
+    u64 dst0[kGatherRows], len[kGatherRows], src0[kGatherRows];
+    #pragma unroll
+    for (int k = 0; k < kGatherRows; ++k) {
+        const u64 q = grp + u64(k) * n_grp;   // neighbouring groups take neighbouring rows: coalesced metadata
+        dst0[k] = len[k] = src0[k] = 0;
+        if (q < n) {
+            dst0[k] = offsets[q];
+            len[k] = offsets[q + 1] - dst0[k];
+            src0[k] = row_tmp_off[q];
+        }
+    }
+    u32 first[kGatherRows];
+    #pragma unroll
+    for (int k = 0; k < kGatherRows; ++k) first[k] = sub < len[k] ? tmp_cols[src0[k] + sub] : 0u;
+    #pragma unroll
+    for (int k = 0; k < kGatherRows; ++k) {
+        if (sub < len[k]) out[dst0[k] + sub] = OutT(first[k]);
+        for (u64 i = sub + 8; i < len[k]; i += 8) out[dst0[k] + i] = OutT(tmp_cols[src0[k] + i]);
+    }
 }
 
 // iota for the (row id, query index) sort

@@ -218,3 +218,25 @@ def test_concurrent_const_calls_from_many_threads(ggq):
         assert not errors, errors
     finally:
         gm.close()
+
+
+def test_stack_spill_instantiation_gives_the_same_rows(ggq, orc, monkeypatch):
+    """Trees whose worst-case descent stack exceeds the shared-memory budget use the SPILL instantiation of the
+    descent kernel (overflow area in global memory).  GGQ_STACK_CAP shrinks the shared part so that an ordinary
+    tree takes that path; dense rows make the stack actually overflow into the global part."""
+    n, m, d = 20_000, 400, 0.35
+    rows = np.random.default_rng(4).integers(0, n, 30_000).astype(np.uint64)
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=5, arity=4)
+    base = gm.get_rows_csr(rows)
+    gm.close()
+    thr = ggq.density_threshold(d)
+    for t in range(0, rows.size, 997):
+        assert np.array_equal(base[1][base[0][t]:base[0][t + 1]], orc.synth_row(m, thr, 5, int(rows[t])))
+    monkeypatch.setenv("GGQ_STACK_CAP", "16")
+    gs = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=5, arity=4)
+    try:
+        off, cols = gs.get_rows_csr(rows)
+        assert np.array_equal(off, base[0]) and np.array_equal(cols, base[1])
+        assert np.array_equal(gs.count_labels(rows), np.bincount(base[1].astype(np.int64), minlength=m).astype(np.uint64))
+    finally:
+        gs.close()
