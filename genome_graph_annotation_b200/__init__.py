@@ -62,6 +62,7 @@ def lib():
         "ggq_comm_unique_id": (C.c_int, [u8p]),
         "ggq_comm_init": (C.c_int, [u8p, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
         "ggq_comm_free": (None, [vp]),
+        "ggq_count_labels_allreduce_device": (C.c_int, [vp, vp, vp, C.c_void_p, C.c_uint64, C.POINTER(vp)]),
         "ggq_comm_enable_peer": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
         "ggq_comm_peer_active": (C.c_int, [vp]),
         "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
@@ -472,6 +473,13 @@ class Workspace:
         """-> device pointer to uint64[num_columns] counts, owned by the workspace."""
         out = C.c_void_p()
         _check(lib().ggq_count_labels_device(self.m._h, self._h, C.c_void_p(d_rows_ptr), n, C.byref(out)))
+        return out.value
+
+    def count_labels_allreduce_device(self, comm, d_rows_ptr, n):
+        """Collective: histogram of the whole batch on every rank (ggq_count_labels_allreduce_device) -> device ptr."""
+        out = C.c_void_p()
+        _check(lib().ggq_count_labels_allreduce_device(self.m._h, self._h, comm._h, C.c_void_p(d_rows_ptr), n,
+                                                       C.byref(out)))
         return out.value
 
     def get_rows_sharded_device(self, comm, d_rows_ptr, n, col_bytes=4):

@@ -1296,6 +1296,23 @@ int ggq_count_labels_device(const ggq_matrix *m, ggq_workspace *ws, const uint64
     GGQ_CATCH
 }
 
+int ggq_count_labels_allreduce_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                      uint64_t n, const uint64_t **d_counts) {
+    GGQ_TRY
+    if (!m || !ws || !comm || (!d_rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    count_labels_device(m, ws, reinterpret_cast<const u64 *>(d_rows), n);
+    const u64 nc = std::max<u64>(m->tree.n_cols, 1);
+    // replicas: every rank counted its own slice of the batch; column shards: every rank counted its own columns
+    // over the whole batch (the others are 0) — in both cases the sum over ranks is the histogram of the batch
+    NCCL_CHECK(NcclApi::get().AllReduce(ws->d_counts.p, ws->d_counts.p, nc, ncclUint64, ncclSum, comm->comm, ws->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    ws->launches += 1;
+    if (d_counts) *d_counts = reinterpret_cast<const uint64_t *>(ws->d_counts.p);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len) {
     GGQ_TRY
     if (!m || !out || !out_len || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");

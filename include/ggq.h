@@ -227,6 +227,13 @@ int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm
                                 uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
                                 uint64_t *n_cols);
 
+/* count_labels across GPUs — collective.  Replicas: every rank passes ITS slice of the index list; column shards:
+ * every rank passes the whole list (a shard counts its own columns, the others stay 0).  Either way one
+ * ncclAllReduce(sum) over num_columns counters leaves the histogram of the whole batch on every rank — 21 KB over
+ * NVLink instead of the row sets. */
+int ggq_count_labels_allreduce_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                      uint64_t n, const uint64_t **d_counts);
+
 /* ------------------------------------------------------------------ cells / columns ---------- */
 
 /* out[t] = BinaryMatrix::get(rows[t], cols[t]) (BRWT.cpp:9-24, column_major.cpp:27-32). */

@@ -59,6 +59,24 @@ def main():
             assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), ("peer", B)
         print("rank %d peer=%d B=%d total=%d exchange %.3f ms %.1f MB" % (rank, expect_peer, B, total, ws.stat("exchange_ms"),
                                                                           ws.stat("exchange_bytes") / 1e6), flush=True)
+    # count_labels across GPUs: column shards count their own columns over the whole batch, replicas count their slice
+    # of the batch; one all-reduce over num_columns counters gives the histogram of the batch on every rank
+    B = 200_000
+    rows = torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen)
+    np_rows = rows.cpu().numpy().view(np.uint64)
+    expect = None
+    if rank == 0:
+        expect = whole.count_labels(np_rows)
+    cnt = d2h(ws.count_labels_allreduce_device(comm, rows.data_ptr(), B), m * 8, np.uint64)
+    replica = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local)
+    rws = replica.workspace()
+    lo, hi = B * rank // world, B * (rank + 1) // world
+    cnt2 = d2h(rws.count_labels_allreduce_device(comm, rows.data_ptr() + lo * 8, hi - lo), m * 8, np.uint64)
+    if rank == 0:
+        assert np.array_equal(cnt, expect), "sharded count_labels + all-reduce"
+        assert np.array_equal(cnt2, expect), "replica count_labels + all-reduce"
+        print("count_labels all-reduce ok (shards and replicas)", flush=True)
+    rws.close(); replica.close()
     if whole is not None:
         whole.close()
     dist.barrier()
