@@ -313,6 +313,45 @@ def run_ours(args):
     ms_step = float(t.item()) / K
     value = world * B / (ms_step / 1e3)
 
+    # ---- full-scale spot check (outside every timed region): rows of the measured matrix against direct
+    # evaluation of M[i][j] = mix64(seed*K + i*m + j) < T in numpy; for the basic partitioner DFS order = ascending
+    spot_rows = 4096
+    sr = batches[0][:spot_rows].cpu().numpy().view(np.uint64)
+    s_off, s_cols = gm.get_rows_csr(sr)
+    thr = np.uint64(g.density_threshold(args.density))
+    base = np.uint64((SEED * g.SEED_MUL) % 2**64)
+    jj = np.arange(args.cols, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        for t in range(spot_rows):
+            exp = np.nonzero(g.mix64(base + sr[t] * np.uint64(args.cols) + jj) < thr)[0].astype(np.uint64)
+            if not np.array_equal(s_cols[int(s_off[t]):int(s_off[t + 1])], exp):
+                raise RuntimeError("bench.py: row %d of the measured matrix differs from direct evaluation" % int(sr[t]))
+    spot = {"rows": spot_rows, "identical": True,
+            "against": "direct numpy evaluation of the implicit matrix (SURVEY.md 8d generator), full-size matrix"}
+
+    # ---- the other calls of the BinaryMatrix interface on the same matrix (host to host, outside the headline):
+    # get_column (BRWT.cpp:55-85) for a few columns, get (BRWT.cpp:9-24) for 2^22 random cells
+    extra = None
+    if not args.no_e2e:
+        pick = [7, args.cols // 3, args.cols - 1]
+        h_col = torch.empty(max(gm.get_column_count(c) for c in pick) + 1, dtype=torch.int64).pin_memory()
+        np_col = h_col.numpy().view(np.uint64)
+        gm.get_column_into(pick[0], np_col)
+        tw = time.perf_counter()
+        p_out = sum(int(gm.get_column_into(c, np_col)) for c in pick)
+        tcol = (time.perf_counter() - tw) / len(pick)
+        del h_col
+        nq = 1 << 22
+        cr = batches[1 % n_pool][:nq].cpu().numpy().view(np.uint64)
+        cc = (cr * np.uint64(2654435761) % np.uint64(args.cols)).astype(np.uint64)
+        gm.get_cells(cr, cc)   # warm-up at full size (scratch buffers grow once)
+        tw = time.perf_counter()
+        cells = gm.get_cells(cr, cc)
+        tcell = time.perf_counter() - tw
+        extra = {"get_column": {"api": "ggq_get_column_into (pinned host buffer)", "ms_per_column": tcol * 1e3, "rows_out_per_column": p_out / len(pick),
+                                "rows_out_per_s": p_out / len(pick) / tcol},
+                 "get": {"cells": nq, "cells_per_s": nq / tcell, "set_fraction": float(np.mean(cells))}}
+
     # ---- end to end through the host-buffer C ABI ------------------------------------------
     e2e = e2e_u64 = None
     if not args.no_e2e:
@@ -399,6 +438,9 @@ def run_ours(args):
             "clocks": clk, "roofline": roof, "gpu_launches": launches,
             "build_seconds": build_s, "device_image_gb": gm.device_bytes / 1e9,
             "column_ids_per_row": ids / (B * K)}
+    line["spot_check"] = spot
+    if extra is not None:
+        line["other_calls_host_to_host"] = extra
     if e2e is not None:
         line["e2e"] = e2e
         line["e2e_u64"] = e2e_u64

@@ -82,6 +82,8 @@ def lib():
         "ggq_rows_count": (C.c_uint64, [vp]),
         "ggq_rows_result_free": (None, [vp]),
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_get_column_count": (C.c_int, [vp, C.c_uint64, u64p]),
+        "ggq_get_column_into": (C.c_int, [vp, C.c_uint64, u64p, C.c_uint64, u64p]),
         "ggq_image_save": (C.c_int, [vp, C.c_char_p]),
         "ggq_image_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
         "ggq_get_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p]),
@@ -428,6 +430,17 @@ class GpuMatrix:
         out = np.empty(rows.size, dtype=np.uint8)
         _check(lib().ggq_has_column(self._h, rp, rows.size, col, out.ctypes.data_as(u8p)))
         return out
+
+    def get_column_count(self, col):
+        n = C.c_uint64()
+        _check(lib().ggq_get_column_count(self._h, col, C.byref(n)))
+        return n.value
+
+    def get_column_into(self, col, out):
+        """Ascending set rows of `col` into the caller's uint64 array (e.g. pinned); returns their number."""
+        n = C.c_uint64()
+        _check(lib().ggq_get_column_into(self._h, col, out.ctypes.data_as(u64p), out.size, C.byref(n)))
+        return n.value
 
     def get_column(self, col):
         out = u64p()

@@ -192,7 +192,7 @@ inline void colmajor_get_column(const Matrix *m, Workspace *ws, u64 col, DeviceB
     const ColMajorImage *cm = m->cm;
     const SdImg &v = cm->cols[col]->img;
     *cnt = cm->col_ones[col];
-    d_res->alloc(std::max<u64>(*cnt, 1));
+    if (d_res->n < std::max<u64>(*cnt, 1)) d_res->alloc(std::max<u64>(*cnt, 1));
     if (!*cnt) return;
     if (!v.inverted)
         sd_enumerate_kernel<<<u32((v.high.n_blk + 127) / 128), 128, 0, ws->stream>>>(v, d_res->p);

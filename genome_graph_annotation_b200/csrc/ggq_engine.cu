@@ -1397,49 +1397,88 @@ int ggq_has_column(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64
     return get_cells(m, rows, nullptr, col, n, out);
 }
 
-int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t *n_rows) {
-    GGQ_TRY
-    if (!m || !rows || !n_rows) return fail(GGQ_ERR_ARG, "bad argument");
+// number of set rows of a column: known on the host (popcount of the column's leaf vector / of the sd vector)
+static u64 column_count(const ggq_matrix *m, uint64_t col) {
+    if (m->kind != Matrix::BRWT) return m->cm->col_ones[col];
+    const FlatTree &t = m->tree;
+    return m->lane_ones_h[t.col_path[t.col_path_off[col + 1] - 1]];
+}
+
+// BinaryMatrix::get_column on the device: ascending row ids in *d_res (enqueued on ws->stream, not awaited)
+static void column_device(const ggq_matrix *m, Workspace *ws, uint64_t col, DeviceBuf<u64> *d_res, u64 *cnt_out) {
+    cudaStream_t st = ws->stream;
+    u64 cnt = 0;
+    if (m->kind == Matrix::BRWT) {
+        const FlatTree &t = m->tree;
+        u32 p0 = t.col_path_off[col], p1 = t.col_path_off[col + 1];
+        u32 leaf_li = t.col_path[p1 - 1];
+        cnt = m->lane_ones_h[leaf_li];
+        // an empty ancestor makes the column empty (BRWT.cpp:58-62); an empty leaf too
+        if (d_res->n < std::max<u64>(cnt, 1)) d_res->alloc(std::max<u64>(cnt, 1));
+        if (cnt) {
+            u64 nb = t.group_nblocks[leaf_li >> 2];
+            lane_enumerate_kernel<<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res->p);
+            for (u32 p = p1 - 1; p-- > p0;) {
+                u32 li = t.col_path[p];
+                if (m->lane_ones_h[li] == m->lane_size_h[li]) continue;  // all ones: identity (BRWT.cpp:77-78)
+                lane_select_kernel<<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res->p, cnt);
+            }
+            CUDA_CHECK(cudaGetLastError());
+        }
+    } else {
+        colmajor_get_column(m, ws, col, d_res, &cnt);
+    }
+    *cnt_out = cnt;
+}
+
+static int column_check(const ggq_matrix *m, uint64_t col) {
     if (col >= ggq_num_columns(m)) return fail(GGQ_ERR_ARG, "column out of range");
     if (m->kind == Matrix::BRWT && !m->tree.col_owned.empty() && !m->tree.col_owned[col])
         return fail(GGQ_ERR_ARG, "column is held by another shard");
+    return GGQ_OK;
+}
+
+int ggq_get_column_count(const ggq_matrix *m, uint64_t col, uint64_t *n_rows) {
+    GGQ_TRY
+    if (!m || !n_rows) return fail(GGQ_ERR_ARG, "bad argument");
+    if (int rc = column_check(m, col)) return rc;
+    *n_rows = column_count(m, col);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_get_column_into(const ggq_matrix *m, uint64_t col, uint64_t *rows, uint64_t capacity, uint64_t *n_rows) {
+    GGQ_TRY
+    if (!m || !n_rows || (!rows && capacity)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (int rc = column_check(m, col)) return rc;
+    *n_rows = column_count(m, col);
+    if (*n_rows > capacity) return fail(GGQ_ERR_ARG, "capacity too small");
     Workspace *ws = m->acquire();
     try {
         CUDA_CHECK(cudaSetDevice(m->device));
-        cudaStream_t st = ws->stream;
         u64 cnt = 0;
-        DeviceBuf<u64> d_res;
-        if (m->kind == Matrix::BRWT) {
-            const FlatTree &t = m->tree;
-            u32 p0 = t.col_path_off[col], p1 = t.col_path_off[col + 1];
-            u32 leaf_li = t.col_path[p1 - 1];
-            cnt = m->lane_ones_h[leaf_li];
-            // an empty ancestor makes the column empty (BRWT.cpp:58-62); an empty leaf too
-            d_res.alloc(std::max<u64>(cnt, 1));
-            if (cnt) {
-                u64 nb = t.group_nblocks[leaf_li >> 2];
-                lane_enumerate_kernel<<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res.p);
-                for (u32 p = p1 - 1; p-- > p0;) {
-                    u32 li = t.col_path[p];
-                    if (m->lane_ones_h[li] == m->lane_size_h[li]) continue;  // all ones: identity (BRWT.cpp:77-78)
-                    lane_select_kernel<<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res.p, cnt);
-                }
-                CUDA_CHECK(cudaGetLastError());
-            }
-        } else {
-            colmajor_get_column(m, ws, col, &d_res, &cnt);
-        }
-        uint64_t *h = static_cast<uint64_t *>(std::malloc(std::max<u64>(cnt, 1) * 8));
-        if (!h) throw std::bad_alloc();
-        if (cnt) CUDA_CHECK(cudaMemcpyAsync(h, d_res.p, cnt * 8, cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        *rows = h;
-        *n_rows = cnt;
+        column_device(m, ws, col, &ws->d_col, &cnt);   // workspace-owned result buffer: no cudaMalloc / cudaFree per call
+        if (cnt) CUDA_CHECK(cudaMemcpyAsync(rows, ws->d_col.p, cnt * 8, cudaMemcpyDeviceToHost, ws->stream));
+        CUDA_CHECK(cudaStreamSynchronize(ws->stream));
     } catch (...) {
         m->release(ws);
         throw;
     }
     m->release(ws);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t *n_rows) {
+    GGQ_TRY
+    if (!m || !rows || !n_rows) return fail(GGQ_ERR_ARG, "bad argument");
+    if (int rc = column_check(m, col)) return rc;
+    const u64 cnt = column_count(m, col);
+    uint64_t *h = static_cast<uint64_t *>(std::malloc(std::max<u64>(cnt, 1) * 8));
+    if (!h) throw std::bad_alloc();
+    const int rc = ggq_get_column_into(m, col, h, cnt, n_rows);
+    if (rc != GGQ_OK) { std::free(h); return rc; }
+    *rows = h;
     return GGQ_OK;
     GGQ_CATCH
 }

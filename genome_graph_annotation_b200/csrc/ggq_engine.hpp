@@ -118,6 +118,7 @@ struct Workspace {
     bool kernel_timed = false;
     bool hist_mode = false;          // count_labels: skip CSR assembly, the ids stay unordered in d_tmp
     DeviceBuf<u64> d_counts;
+    DeviceBuf<u64> d_col;            // get_column result
     DeviceBuf<u64> d_lab_cols, d_lab_cnt, d_lab_cols2, d_lab_cnt2, d_lab_n;   // get_labels / get_top_labels
     DeviceBuf<unsigned char> d_lab_sort;
     DeviceBuf<u64> d_qoff, d_qlab_off, d_qout_cols, d_qout_cnt;   // ggq_get_labels_batch

@@ -51,10 +51,10 @@ class GpuMatrixBase : public BinaryMatrix {
     }
 
     std::vector<Row> get_column(Column column) const override {
-        uint64_t *rows = nullptr, n = 0;
-        check(ggq_get_column(handle(), column, &rows, &n));
-        std::vector<Row> out(rows, rows + n);
-        ggq_buffer_free(rows);
+        uint64_t n = 0;
+        check(ggq_get_column_count(handle(), column, &n));   // host-side lookup
+        std::vector<Row> out(n);
+        check(ggq_get_column_into(handle(), column, out.data(), n, &n));   // straight into the result: one copy
         return out;
     }
 

@@ -26,8 +26,15 @@ def test_matrix_fixture(ggq, path):
     off, cols = gm.get_rows_csr(np.arange(n, dtype=np.uint64))
     assert np.array_equal(off, g["row_offsets"]) and np.array_equal(cols, g["row_cols"])
     coff, crows = g["col_offsets"], g["col_rows"]
+    buf = np.empty(max(n, 1), np.uint64)
     for c in range(m):
         assert np.array_equal(gm.get_column(c), crows[coff[c]:coff[c + 1]])
+        k = gm.get_column_into(c, buf)   # caller-provided buffer; the count is a host-side lookup
+        assert k == gm.get_column_count(c) == coff[c + 1] - coff[c]
+        assert np.array_equal(buf[:k], crows[coff[c]:coff[c + 1]])
+    if m and coff[1] - coff[0] > 0:
+        with pytest.raises(ggq.GgqError):
+            gm.get_column_into(0, np.empty(0, np.uint64))   # capacity too small
     shape = tuple(int(x) for x in g["shape"])
     if n * m:
         dense = np.unpackbits(g["dense"])[: n * m].reshape(shape)
