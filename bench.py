@@ -336,10 +336,13 @@ def run_ours(args):
         pick = [7, args.cols // 3, args.cols - 1]
         h_col = torch.empty(max(gm.get_column_count(c) for c in pick) + 1, dtype=torch.int64).pin_memory()
         np_col = h_col.numpy().view(np.uint64)
-        gm.get_column_into(pick[0], np_col)
-        tw = time.perf_counter()
-        p_out = sum(int(gm.get_column_into(c, np_col)) for c in pick)
-        tcol = (time.perf_counter() - tw) / len(pick)
+        for c in pick:   # warm-up: the result buffer grows to the largest column once
+            gm.get_column_into(c, np_col)
+        tcol = 1e30
+        for rep in range(3):
+            tw = time.perf_counter()
+            p_out = sum(int(gm.get_column_into(c, np_col)) for c in pick)
+            tcol = min(tcol, (time.perf_counter() - tw) / len(pick))
         del h_col
         nq = 1 << 22
         cr = batches[1 % n_pool][:nq].cpu().numpy().view(np.uint64)

@@ -15,6 +15,7 @@ struct Img {
     const uint4 *slots;
     const u64 *group_hot;
     const uint4 *group_rec;   // [g*2 + half] = { hot.lo, hot.hi, lane_info[4g+2*half], lane_info[4g+2*half+1] }
+    const uint4 *group_rec16; // [g] = compact 16-byte record (ggq_rows.cuh: load_rec), null if the tree does not qualify
     const u64 *group_nblocks;
     const u32 *lane_info;
     const u32 *lane_aux;

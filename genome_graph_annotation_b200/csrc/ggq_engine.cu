@@ -133,6 +133,27 @@ void Matrix::upload_tables(const FlatTree &t) {
                                             t.lane_info[4 * g + 2 * h + 1]);
         upload_vec(group_rec, rec);
     }
+    {   // compact 16-byte records: 21-bit children (leaf bit 20), base in units of 4 slots
+        compact_rec = t.leaf_col.size() < (1u << 20) - 1 && t.n_groups() < (1u << 20) && !std::getenv("GGQ_WIDE_REC");
+        std::vector<uint4> rec16(compact_rec ? size_t(t.n_groups()) : 0);
+        for (u32 g = 0; compact_rec && g < t.n_groups(); ++g) {
+            const u64 hot = t.group_hot[g];
+            const u64 base = hot & kGhBaseMask;
+            if ((base & 3) || (base >> 2) > 0xFFFFFFFFull) { compact_rec = false; break; }
+            u32 c[4] = {0, 0, 0, 0};
+            for (u32 k = 0; k < 4; ++k) {
+                const u32 info = t.lane_info[4 * g + k];
+                if (info == kRemoteLane) c[k] = (1u << 21) - 1u;
+                else if (info & kLeafFlag) c[k] = (1u << 20) | (info & ~kLeafFlag);
+                else c[k] = info;
+                if (info != kRemoteLane && (info & ~kLeafFlag) >= (1u << 20) - 1) { compact_rec = false; break; }
+            }
+            const u32 flags = u32(hot >> kGhStrideShift) & 0x7fu;
+            rec16[g] = make_uint4(u32(base >> 2), flags | (c[0] << 7), c[1] | (c[2] << 21), (c[2] >> 11) | (c[3] << 10));
+        }
+        if (compact_rec) upload_vec(group_rec16, rec16);
+        else group_rec16.release();
+    }
     upload_vec(lane_info, t.lane_info);
     upload_vec(lane_aux, t.lane_aux);
     upload_vec(lane_sb_off, t.lane_sb_off);
@@ -150,6 +171,7 @@ void Matrix::refresh_img() {
     img.slots = slots.p;
     img.group_hot = group_hot.p;
     img.group_rec = group_rec.p;
+    img.group_rec16 = compact_rec ? group_rec16.p : nullptr;
     img.group_nblocks = group_nblocks.p;
     img.lane_info = lane_info.p;
     img.lane_aux = lane_aux.p;
@@ -168,9 +190,13 @@ void Matrix::refresh_img() {
 }
 
 // The instantiation of K1 for a tree: stack spill to global memory, leaves holding several columns.
-static const void *rows_kernel_fn(bool spill, bool multi_leaf) {
-    if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true> : (const void *)brwt_rows_kernel<true, false>;
-    return multi_leaf ? (const void *)brwt_rows_kernel<false, true> : (const void *)brwt_rows_kernel<false, false>;
+static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact) {
+    if (compact) {
+        if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, true> : (const void *)brwt_rows_kernel<true, false, true>;
+        return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true> : (const void *)brwt_rows_kernel<false, false, true>;
+    }
+    if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, false> : (const void *)brwt_rows_kernel<true, false, false>;
+    return multi_leaf ? (const void *)brwt_rows_kernel<false, true, false> : (const void *)brwt_rows_kernel<false, false, false>;
 }
 
 // Descent kernel configuration: rows per warp batch, stack capacity, grid, query ordering.
@@ -202,7 +228,7 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     }
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
     int per_sm = 0;
-    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0);
+    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec);
     CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
@@ -434,7 +460,7 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
     {
         Img img = m->img;
         void *kargs[] = {&img, &a};
-        CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0), dim3(grid), dim3(kRowsWarps * 32),
+        CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid), dim3(kRowsWarps * 32),
                                     kargs, m->rows_smem, st));
     }
     CUDA_CHECK(cudaEventRecord(ws->ev1, st));
@@ -825,6 +851,7 @@ int ggq_comm_enable_peer(ggq_comm *c, ggq_workspace *ws, uint64_t max_rows, uint
     if (c->n_ranks > kMaxShards) return fail(GGQ_ERR_LIMIT, "too many shards");
     CUDA_CHECK(cudaSetDevice(c->device));
     const int R = c->n_ranks;
+    c->close_peer();   // a second call re-pins and re-maps (collective, like the first)
     // pin the partial-CSR buffers at the stated capacity (they must not be reallocated while mapped by peers)
     ws->reserve_rows(max_rows);
     const size_t out_bytes = size_t(std::max<u64>(max_ids, 1)) * 4;

@@ -63,6 +63,8 @@ struct Matrix {
     DeviceBuf<uint4> slots;
     DeviceBuf<u64> group_hot, group_nblocks, lane_sel_off, lane_ones, sb_base;
     DeviceBuf<uint4> group_rec;   // per (group, half): hot word + the two children's lane_info (descent kernel)
+    DeviceBuf<uint4> group_rec16; // per group: compact record (trees with < 2^20 - 1 columns), else empty
+    bool compact_rec = false;
     DeviceBuf<u32> lane_info, lane_aux, lane_sb_off, sel, leaf_col, col_path_off, col_path;
     Img img{};
 

@@ -101,8 +101,7 @@ __device__ __forceinline__ u32 slot_ones_before(const uint4 &s, u32 w, u32 wsel,
 
 // Set bit of a leaf child: mark the DFS ranks of its columns in the row's bitmap, bump the row's counter.
 template <bool MULTI_LEAF>
-__device__ __forceinline__ void mark_leaf(const Img &img, u32 info, u32 li, u32 bm_row, u32 cnt_addr) {
-    u32 rank = info & ~kLeafFlag;
+__device__ __forceinline__ void mark_leaf(const Img &img, u32 rank, u32 li, u32 bm_row, u32 cnt_addr) {
     if (!MULTI_LEAF) {
         reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
         reds_add(cnt_addr, 1u);
@@ -142,9 +141,38 @@ __device__ __forceinline__ u32 emit_flush(const Img &img, u32 que, u32 cnt, u32 
     return __shfl_sync(0xffffffffu, inc, 31);
 }
 
-template <bool SPILL, bool MULTI_LEAF>
+// Group record seen by one lane: where the group's blocks are, its shape flags (stride_log2 | cnt << 2 | more << 5 |
+// multi-superblock << 6) and the lane's two children.  A child is `leaf bit | index`: for an internal child the
+// index of its first group, for a leaf the DFS rank of its first column; all ones = held by another shard.
+//   wide    (32 bytes per group, two 16-byte halves): 32-bit children, leaf bit 31      (Img::group_rec)
+//   compact (16 bytes per group): 21-bit children, leaf bit 20 — trees with < 2^20 - 1 columns.  Half the table:
+//            44 -> 22 KB for the C4 tree, which is what lets it stay in the ~28 KB of L1 left beside 6 CTAs' shared memory
+template <bool COMPACT> struct RecFmt;
+template <> struct RecFmt<false> { static constexpr u32 kLeaf = kLeafFlag, kRemote = kRemoteLane; };
+template <> struct RecFmt<true> { static constexpr u32 kLeaf = 1u << 20, kRemote = (1u << 21) - 1u; };
+
+template <bool COMPACT>
+__device__ __forceinline__ void load_rec(const Img &img, u32 g, u32 half, u64 &base, u32 &flags, u32 &child0, u32 &child1) {
+    if (!COMPACT) {
+        const uint4 rec = __ldg(img.group_rec + 2 * g + half);
+        base = (u64(rec.y & 0xffu) << 32) | rec.x;
+        flags = (rec.y >> (kGhStrideShift - 32)) & 0x7fu;
+        child0 = rec.z;
+        child1 = rec.w;
+    } else {
+        const uint4 rec = __ldg(img.group_rec16 + g);   // x: base / 4; y: flags | c0 << 7; z: c1 | c2 << 21; w: c2 >> 11 | c3 << 10
+        base = u64(rec.x) << 2;
+        flags = rec.y & 0x7fu;
+        const u32 m = (1u << 21) - 1u;
+        child0 = half ? ((rec.z >> 21) | (rec.w << 11)) & m : (rec.y >> 7) & m;
+        child1 = half ? (rec.w >> 10) & m : rec.z & m;
+    }
+}
+
+template <bool SPILL, bool MULTI_LEAF, bool COMPACT>
 __global__ void __launch_bounds__(kRowsWarps * 32)
 brwt_rows_kernel(Img img, RowsArgs a) {
+    typedef RecFmt<COMPACT> Fmt;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 lt_mask = (1u << lane) - 1u;
@@ -223,10 +251,12 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                 const u32 ilo = u32(item);
                 const u32 g = ilo & (kMaxGroups - 1);
                 const u32 tq = ilo & ((kMaxRowsPerWarp - 1) << kItemGroupBits);   // t, in place
-                const uint4 rec = __ldg(img.group_rec + 2 * g + half);
-                const u32 sl = (rec.y >> (kGhStrideShift - 32)) & 3u;
-                const u32 cnt = (rec.y >> (kGhCntShift - 32)) & 7u;
-                push_cont = half == 0 && ((rec.y >> (kGhMoreShift - 32)) & 1u);
+                u64 gbase;
+                u32 flags, child0, child1;
+                load_rec<COMPACT>(img, g, half, gbase, flags, child0, child1);
+                const u32 sl = flags & 3u;
+                const u32 cnt = (flags >> 2) & 7u;
+                push_cont = half == 0 && ((flags >> 5) & 1u);
                 if (half == 0) touches += cnt;
                 if (2 * half < cnt) {
                     u64 blk; u32 bit;
@@ -239,7 +269,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                         blk = rr / kSlotBits;
                         bit = u32(rr - blk * kSlotBits);
                     }
-                    const u64 si = ((u64(rec.y & 0xffu) << 32) | rec.x) + (blk << sl) + 2 * half;   // slot of child 2*half
+                    const u64 si = gbase + (blk << sl) + 2 * half;   // slot of child 2*half
                     uint4 s0, s1;
                     ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
                     if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
@@ -248,23 +278,23 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                     const u32 w1 = wsel == 0 ? s1.y : (wsel == 1 ? s1.z : s1.w);
                     const bool set0 = (w0 >> sh) & 1u;
                     const bool set1 = (2 * half + 1 < cnt) && ((w1 >> sh) & 1u);
-                    const bool leaf0 = int(rec.z) < 0, leaf1 = int(rec.w) < 0;
+                    const bool leaf0 = child0 & Fmt::kLeaf, leaf1 = child1 & Fmt::kLeaf;
                     const u32 t = tq >> kItemGroupBits;
                     const u32 bm_row = bm + t * bm_row_bytes;
-                    if (set0 && leaf0 && rec.z != kRemoteLane) mark_leaf<MULTI_LEAF>(img, rec.z, g * 4 + 2 * half, bm_row, cnt0 + t * 4);
-                    if (set1 && leaf1 && rec.w != kRemoteLane) mark_leaf<MULTI_LEAF>(img, rec.w, g * 4 + 2 * half + 1, bm_row, cnt0 + t * 4);
+                    if (set0 && leaf0 && child0 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child0 & (Fmt::kLeaf - 1u), g * 4 + 2 * half, bm_row, cnt0 + t * 4);
+                    if (set1 && leaf1 && child1 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child1 & (Fmt::kLeaf - 1u), g * 4 + 2 * half + 1, bm_row, cnt0 + t * 4);
                     push0 = set0 && !leaf0;
                     push1 = set1 && !leaf1;
                     // r' = rank1(r) - 1 = ones strictly before r (BRWT.cpp:43-50)
                     u64 ones0 = slot_ones_before(s0, w0, wsel, below);
                     u64 ones1 = slot_ones_before(s1, w1, wsel, below);
-                    if ((rec.y >> (kGhSuperShift - 32)) & 1u) {     // some lane of the group spans several superblocks
+                    if ((flags >> 6) & 1u) {     // some lane of the group spans several superblocks
                         const u64 sb = blk >> kSuperShift;
                         if (push0) ones0 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half] + sb];   // entry 0 of a lane is 0
                         if (push1) ones1 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half + 1] + sb];
                     }
-                    item0 = (ones0 << kItemRShift) | tq | rec.z;
-                    item1 = (ones1 << kItemRShift) | tq | rec.w;
+                    item0 = (ones0 << kItemRShift) | tq | child0;   // (only pushed for internal children: plain group index)
+                    item1 = (ones1 << kItemRShift) | tq | child1;
                 }
             }
             const u32 m0 = __ballot_sync(0xffffffffu, push0);

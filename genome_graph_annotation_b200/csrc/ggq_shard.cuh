@@ -61,12 +61,17 @@ struct Comm {
     u64 peer_max_rows = 0, peer_max_ids = 0;
     const u64 *peer_off[16] = {};        // [r]: rank r's partial offsets (null for the own rank)
     const u32 *peer_cols[16] = {};       // [r]: rank r's partial column ids
-    ~Comm() {
+    void close_peer() {
         for (int r = 0; r < 16; ++r) {
             if (peer_off[r]) cudaIpcCloseMemHandle(const_cast<u64 *>(peer_off[r]));
             if (peer_cols[r]) cudaIpcCloseMemHandle(const_cast<u32 *>(peer_cols[r]));
+            peer_off[r] = nullptr;
+            peer_cols[r] = nullptr;
         }
+        peer = false;
+        peer_ws = nullptr;
     }
+    ~Comm() { close_peer(); }
 };
 
 // NCCL is resolved with dlopen at the first collective call instead of being a link-time dependency: a host

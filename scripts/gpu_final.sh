@@ -2,6 +2,7 @@
 # final build of the round: GPU tests, the default bench line, the reference arm, the ncu launch list of the same
 # command, one full capture of the descent kernel (1e9-row footprint: the 3.7e9-row capture would replay 80 GB ~40x)
 mkdir -p gpurun_out
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke_final.log 2>&1; tail -1 gpurun_out/smoke_final.log
 timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_final.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_final.log
 tail -3 gpurun_out/pytest_final.log
 timeout 900 python bench.py > gpurun_out/bench_final_c4.json 2> gpurun_out/bench_final_c4.err
