@@ -24,8 +24,29 @@ def check(ggq, ref, dense):
         assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
         dup = np.concatenate([rows, rows[::3]])
         assert np.array_equal(gm.count_labels(dup), (dense.sum(0) + dense[::3].sum(0)).astype(np.uint64))
+        # the annotator's thresholds on top of the histogram (annotate_static.cpp:71-94, annotate.cpp:57-83), also
+        # batched across queries — same code path as for BRWT, fed by the column-major row kernel
+        cnt = (dense.sum(0) + dense[::3].sum(0)).astype(np.uint64) if m else np.zeros(0, np.uint64)
+        for ratio in (0.0, 0.3):
+            need = 1 if ratio == 0 else int(np.ceil(dup.size * ratio))
+            keep = np.nonzero((cnt != 0) & (cnt >= need))[0]
+            lc, lv = gm.get_labels(dup, ratio)
+            assert np.array_equal(lc, keep.astype(np.uint64)) and np.array_equal(lv, cnt[keep])
+        if n and m:
+            qoff = np.array([0, n // 2, n // 2, dup.size], dtype=np.uint64)
+            loff, bc, bv = gm.get_labels_batch(dup, qoff, 0.25)
+            for q in range(3):
+                ec, ev = gm.get_labels(dup[int(qoff[q]):int(qoff[q + 1])], 0.25)
+                assert np.array_equal(bc[int(loff[q]):int(loff[q + 1])], ec) and np.array_equal(bv[int(loff[q]):int(loff[q + 1])], ev)
+            tc, tv = gm.get_top_labels(dup, 2)
+            nz = np.nonzero(cnt)[0]
+            order = nz[np.argsort(-cnt[nz].astype(np.int64), kind="stable")][:2]
+            assert np.array_equal(tc, order.astype(np.uint64)) and np.array_equal(tv, cnt[order])
+        buf = np.empty(max(n, 1), np.uint64)
         for c in range(m):
             assert np.array_equal(gm.get_column(c), rm.get_column(c)), c
+            k = gm.get_column_into(c, buf)
+            assert k == gm.get_column_count(c) and np.array_equal(buf[:k], rm.get_column(c))
             assert np.array_equal(gm.get_column(c), np.nonzero(dense[:, c])[0].astype(np.uint64))
         if n * m:
             rr, cc = np.meshgrid(rows, np.arange(m, dtype=np.uint64), indexing="ij")
