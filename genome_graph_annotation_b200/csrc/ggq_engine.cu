@@ -419,6 +419,25 @@ Matrix::~Matrix() {
 // ------------------------------------------------------------------------------------------
 // get_rows on the device: rows already in ws.d_rows or caller memory
 // ------------------------------------------------------------------------------------------
+// K1 launch on the workspace stream (d_ctrl must have been cleared)
+static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_rows, const u32 *perm, u64 n) {
+    RowsArgs a;
+    a.rows = proc_rows; a.perm = perm; a.n = n;
+    a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
+    a.cursor = ws->d_ctrl.p;
+    a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
+    a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
+    a.bm_words = m->bm_words; a.rb = m->rb; a.err = reinterpret_cast<int *>(ws->d_ctrl.p + 4);
+    a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
+    a.root_base = m->root_base; a.any_more = m->any_more;
+    u64 batches = (n + m->rb - 1) / m->rb;
+    u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+    Img img = m->img;
+    void *kargs[] = {&img, &a};
+    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid),
+                                dim3(kRowsWarps * 32), kargs, m->rows_smem, ws->stream));
+}
+
 // Enqueue (no synchronisation) everything of a row query up to the point where the host must learn the result
 // size: batch ordering, descent, offset scan, control words to pinned memory.
 static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n) {
@@ -443,33 +462,15 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
         perm = ws->d_perm.p;
         ws->pending_sort_launches = 1 + (end_bit - begin_bit + 7) / 8;   // cub onesweep: histogram + one kernel per 8-bit digit
     }
-    CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
-    CUDA_CHECK(cudaMemsetAsync(ws->d_err.p, 0, sizeof(int), st));
-    RowsArgs a;
-    a.rows = proc_rows; a.perm = perm; a.n = n;
-    a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
-    a.cursor = ws->d_ctrl.p;
-    a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
-    a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
-    a.bm_words = m->bm_words; a.rb = m->rb; a.err = ws->d_err.p;
-    a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
-    a.root_base = m->root_base; a.any_more = m->any_more;
-    u64 batches = (n + m->rb - 1) / m->rb;
-    u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+    CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));   // incl. the overflow flag in ctrl[4]
     CUDA_CHECK(cudaEventRecord(ws->ev0, st));
-    {
-        Img img = m->img;
-        void *kargs[] = {&img, &a};
-        CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid), dim3(kRowsWarps * 32),
-                                    kargs, m->rows_smem, st));
-    }
+    launch_rows_kernel(m, ws, proc_rows, perm, n);
     CUDA_CHECK(cudaEventRecord(ws->ev1, st));
     size_t cb = ws->cub_bytes;
     // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
     CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
     cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
-    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 4 * sizeof(u64), cudaMemcpyDeviceToHost, st));
-    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 4, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 5 * sizeof(u64), cudaMemcpyDeviceToHost, st));
 }
 
 // Wait for brwt_rows_begin, then assemble the CSR (enqueued, not awaited).  The chunk arena grows and the query
@@ -923,6 +924,35 @@ int ggq_get_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ggq_rows
     Workspace *ws = m->acquire();
     try {
         u64 total = 0;
+        // small batches (a scalar get_row is a batch of one): memset + descent + one finishing CTA that writes the CSR
+        // straight into the pinned staging buffer, one synchronisation (small_finish_kernel)
+        if (m->kind == Matrix::BRWT && n >= 1 && n <= u64(kSmallRows) && n < m->sort_min_n) {
+            CUDA_CHECK(cudaSetDevice(m->device));
+            const u64 cap_ids = u64(1) << 16;
+            ws->reserve_rows(n);
+            ws->stage_reserve((2 + n + 1 + cap_ids) * 8);
+            if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
+            cudaStream_t st = ws->stream;
+            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
+            u64 *host = reinterpret_cast<u64 *>(ws->h_stage);
+            small_finish_kernel<<<1, 256, 0, st>>>(ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p,
+                                                  u32(n), host, cap_ids);
+            CUDA_CHECK(cudaGetLastError());
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (host[1] & 1) throw std::runtime_error("descent stack overflow (engine bug)");
+            if (!(host[1] & 2)) {
+                ws->launches = 2; ws->kernel_timed = false; ws->last_probes = 0; ws->last_touches = 0;
+                ggq_rows_result *r = new ggq_rows_result();
+                r->m = m; r->ws = ws; r->n = n; r->total = host[0];
+                r->offsets = host + 2;
+                r->cols = host + 2 + n + 1;
+                *out = r;
+                return GGQ_OK;
+            }
+            // rows too long for the staging buffer (or the chunk arena had to grow): the general path below
+        }
         rows_host(m, ws, rows, n, &total);
         size_t off_bytes = (n + 1) * 8, col_bytes = total * 8;
         ws->stage_reserve(off_bytes + col_bytes + 8);

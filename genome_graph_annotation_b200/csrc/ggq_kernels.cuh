@@ -188,6 +188,70 @@ gather_rows_kernel(const u32 *tmp_cols, const u64 *row_tmp_off, const u64 *offse
     }
 }
 
+// Small batches (a scalar get_row is a batch of one): one CTA turns the descent's per-row counts and chunks into the
+// final CSR and writes it STRAIGHT INTO PINNED HOST MEMORY (zero-copy stores over PCIe), so that a call costs one
+// memset, two kernels and one synchronisation instead of ~14 stream operations and two round trips.
+//   host[0] = total ids, host[1] = status (bit 0: descent stack overflow, bit 1: does not fit -> normal path),
+//   host[2 .. 2+n] = offsets, then the u64 column ids.
+constexpr int kSmallRows = 1024;
+__global__ void __launch_bounds__(256)
+small_finish_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_cols, u64 tmp_cap, const u64 *ctrl,
+                    u32 n, u64 *host, u64 host_cap_ids) {
+    __shared__ u64 s_off[kSmallRows + 1];
+    __shared__ u64 s_src[kSmallRows];
+    __shared__ u32 s_warp[8];
+    __shared__ u64 s_carry;
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (u32 q0 = 0; q0 < n; q0 += 256) {   // block-wide exclusive scan of the counts, 256 rows at a time
+        const u32 q = q0 + threadIdx.x;
+        const u32 c = q < n ? row_cnt[q] : 0;
+        u32 inc = c;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        u32 before = 0, all = 0;
+        #pragma unroll
+        for (u32 w = 0; w < 8; ++w) {
+            const u32 v = s_warp[w];
+            if (w < warp) before += v;
+            all += v;
+        }
+        const u64 carry = s_carry;
+        if (q < n) {
+            s_off[q] = carry + before + inc - c;
+            s_src[q] = row_tmp_off[q];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry = carry + all;
+        __syncthreads();
+    }
+    const u64 total = s_carry;
+    if (threadIdx.x == 0) s_off[n] = total;
+    __syncthreads();
+    const bool fits = total <= host_cap_ids && ctrl[0] <= tmp_cap;   // (ctrl[0]: ids the descent wanted to store)
+    if (threadIdx.x == 0) {
+        host[0] = total;
+        host[1] = (ctrl[4] ? 1u : 0u) | (fits ? 0u : 2u);
+    }
+    if (!fits) return;
+    for (u32 q = threadIdx.x; q <= n; q += 256) host[2 + q] = s_off[q];
+    u64 *cols = host + 2 + n + 1;
+    for (u64 p = threadIdx.x; p < total; p += 256) {
+        u32 lo = 0, hi = n;   // last row with s_off[row] <= p
+        while (hi - lo > 1) {
+            const u32 mid = (lo + hi) >> 1;
+            if (s_off[mid] <= p) lo = mid; else hi = mid;
+        }
+        cols[p] = tmp_cols[s_src[lo] + (p - s_off[lo])];
+    }
+}
+
 // iota for the (row id, query index) sort
 __global__ void iota_kernel(u32 *p, u64 n) {
     u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
