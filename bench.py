@@ -351,7 +351,22 @@ def run_ours(args):
         tw = time.perf_counter()
         cells = gm.get_cells(cr, cc)
         tcell = time.perf_counter() - tw
-        extra = {"get_column": {"api": "ggq_get_column_into (pinned host buffer)", "ms_per_column": tcol * 1e3, "rows_out_per_column": p_out / len(pick),
+        # one query sequence at a time, the way annograph classify calls without cross-query batching:
+        # 300 consecutive-ish row ids (a read's k-mers) -> get_labels(ratio 0.25), and a scalar get_row
+        q300 = np.ascontiguousarray(cr[:300])
+        for _ in range(20):
+            gm.get_labels(q300, 0.25); gm.get_row(int(cr[0]))
+        tw = time.perf_counter()
+        for i in range(200):
+            gm.get_labels(cr[i * 300:(i + 1) * 300], 0.25)
+        t_lab = (time.perf_counter() - tw) / 200
+        tw = time.perf_counter()
+        for i in range(200):
+            gm.get_row(int(cr[i]))
+        t_row = (time.perf_counter() - tw) / 200
+        extra = {"small_calls": {"get_labels_300_indices_us": t_lab * 1e6, "get_row_us": t_row * 1e6,
+                                 "note": "python ctypes call overhead included"},
+                 "get_column": {"api": "ggq_get_column_into (pinned host buffer)", "ms_per_column": tcol * 1e3, "rows_out_per_column": p_out / len(pick),
                                 "rows_out_per_s": p_out / len(pick) / tcol},
                  "get": {"cells": nq, "cells_per_s": nq / tcell, "set_fraction": float(np.mean(cells))}}
 

@@ -1235,6 +1235,37 @@ static int labels_query(const ggq_matrix *m, const uint64_t *rows, uint64_t n, u
     CUDA_CHECK(cudaSetDevice(m->device));
     Workspace *ws = m->acquire();
     try {
+        // one query sequence (<= 1024 indices), threshold only: descent, histogram, filter back to back on the stream,
+        // results written into pinned host memory by the filter kernel, ONE synchronisation
+        const u64 nc_s = m->tree.n_cols;
+        if (m->kind == Matrix::BRWT && !top && n >= 1 && n <= u64(kSmallRows) && n < m->sort_min_n && nc_s >= 1 &&
+            nc_s <= (u64(1) << 16)) {
+            ws->reserve_rows(n);
+            ws->stage_reserve((2 + 2 * nc_s) * 8);
+            if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
+            if (ws->d_counts.n < nc_s) ws->d_counts.alloc(nc_s);
+            cudaStream_t st = ws->stream;
+            u64 *host = reinterpret_cast<u64 *>(ws->h_stage);
+            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+            CUDA_CHECK(cudaMemsetAsync(ws->d_counts.p, 0, nc_s * 8, st));
+            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
+            col_hist_small_kernel<<<8, 512, 0, st>>>(ws->d_tmp.p, ws->d_ctrl.p, ws->d_tmp.n, ws->d_counts.p);
+            label_filter_small_kernel<<<1, 1024, 0, st>>>(ws->d_counts.p, u32(nc_s), min_count, ws->d_ctrl.p, ws->d_tmp.n, host);
+            CUDA_CHECK(cudaGetLastError());
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (host[1] & 1) throw std::runtime_error("descent stack overflow (engine bug)");
+            if (!(host[1] & 2)) {
+                const u64 kept = host[0];
+                if (kept && cols) std::memcpy(cols, host + 2, kept * 8);
+                if (kept && counts) std::memcpy(counts, host + 2 + nc_s, kept * 8);
+                *n_out = kept;
+                ws->launches = 3; ws->kernel_timed = false;
+                m->release(ws);
+                return GGQ_OK;
+            }
+            // the chunk arena has to grow: the general path does that
+        }
         ws->reserve_rows(n);
         if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
         count_labels_device(m, ws, ws->d_rows.p, n);
