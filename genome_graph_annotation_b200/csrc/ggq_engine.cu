@@ -233,6 +233,17 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
     rows_grid = u32(sm_count * per_sm);
+    rows_grid_p = rows_grid;
+    rows_smem_p = rows_smem;
+    if (per_sm >= 3 && !env_u32("GGQ_NO_PIPE_ROOM", 0)) {
+        size_t s = rows_smem;
+        int occ = per_sm;
+        while (occ >= per_sm && s + 512 <= size_t(max_smem)) {
+            s += 512;
+            CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kRowsWarps * 32, s));
+        }
+        if (occ == per_sm - 1) { rows_smem_p = s; rows_grid_p = u32(sm_count * occ); }
+    }
     // root fast path + continuation groups (see RowsArgs)
     root_child = kNoRootFast;
     any_more = 0;
@@ -349,6 +360,7 @@ Workspace::Workspace(const Matrix *m_) : m(m_) {
     CUDA_CHECK(cudaEventCreate(&ev1));
     CUDA_CHECK(cudaEventCreate(&ev2));
     CUDA_CHECK(cudaEventCreate(&ev3));
+    CUDA_CHECK(cudaEventCreateWithFlags(&ev_ctrl, cudaEventDisableTiming));
     if (m->kind == Matrix::BRWT && m->cap_spill)
         d_spill.alloc(size_t(m->rows_grid) * kRowsWarps * m->cap_spill);
 }
@@ -359,6 +371,7 @@ Workspace::~Workspace() {
     if (ev1) cudaEventDestroy(ev1);
     if (ev2) cudaEventDestroy(ev2);
     if (ev3) cudaEventDestroy(ev3);
+    if (ev_ctrl) cudaEventDestroy(ev_ctrl);
     if (stream) cudaStreamDestroy(stream);
     if (h_ctrl) cudaFreeHost(h_ctrl);
     if (h_stage) cudaFreeHost(h_stage);
@@ -382,6 +395,7 @@ void Workspace::reserve_rows(u64 n) {
         d_sort_tmp.alloc(sneed + 16);
         sort_tmp_bytes = sneed;
     }
+    d_blk.alloc((c + kScanBlock - 1) / kScanBlock + 1);
     size_t need = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, need, d_row_cnt.p, d_offsets.p, c, stream);
     d_cub.alloc(need + 16);
@@ -408,6 +422,7 @@ Workspace *Matrix::acquire() const {
     return new Workspace(this);
 }
 void Matrix::release(Workspace *w) const {
+    w->pipelined = false;
     std::lock_guard<std::mutex> lk(pool_mu);
     pool.push_back(w);
 }
@@ -420,6 +435,34 @@ Matrix::~Matrix() {
 // get_rows on the device: rows already in ws.d_rows or caller memory
 // ------------------------------------------------------------------------------------------
 // K1 launch on the workspace stream (d_ctrl must have been cleared)
+// GGQ_TRACE=1: device timeline of the pipelined host API (events on the chunk streams, printed to stderr at the end
+// of the call).  Debug aid for the chunk plan; off by default, no cost when off.
+struct Trace {
+    struct Mark { cudaEvent_t ev; const char *what; u64 chunk; };
+    std::vector<Mark> marks;
+    void mark(cudaStream_t st, const char *what, u64 chunk) {
+        cudaEvent_t e;
+        CUDA_CHECK(cudaEventCreate(&e));
+        CUDA_CHECK(cudaEventRecord(e, st));
+        marks.push_back({e, what, chunk});
+    }
+    void dump() {
+        if (marks.empty()) return;
+        CUDA_CHECK(cudaDeviceSynchronize());
+        for (const Mark &k : marks) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, marks[0].ev, k.ev);
+            std::fprintf(stderr, "[ggq trace] chunk %3llu %-10s %9.3f ms\n", (unsigned long long)k.chunk, k.what, ms);
+            if (&k != &marks[0]) cudaEventDestroy(k.ev);
+        }
+        cudaEventDestroy(marks[0].ev);
+        marks.clear();
+    }
+};
+static thread_local Trace *g_trace = nullptr;
+static thread_local u64 g_trace_chunk = 0;
+#define GGQ_MARK(st, what) do { if (g_trace) g_trace->mark(st, what, g_trace_chunk); } while (0)
+
 static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_rows, const u32 *perm, u64 n) {
     RowsArgs a;
     a.rows = proc_rows; a.perm = perm; a.n = n;
@@ -431,11 +474,12 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
     a.root_base = m->root_base; a.any_more = m->any_more;
     u64 batches = (n + m->rb - 1) / m->rb;
-    u32 grid = u32(std::min<u64>(m->rows_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+    const u32 full_grid = ws->pipelined ? m->rows_grid_p : m->rows_grid;
+    u32 grid = u32(std::min<u64>(full_grid, (batches + kRowsWarps - 1) / kRowsWarps));
     Img img = m->img;
     void *kargs[] = {&img, &a};
     CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid),
-                                dim3(kRowsWarps * 32), kargs, m->rows_smem, ws->stream));
+                                dim3(kRowsWarps * 32), kargs, ws->pipelined ? m->rows_smem_p : m->rows_smem, ws->stream));
 }
 
 // Enqueue (no synchronisation) everything of a row query up to the point where the host must learn the result
@@ -452,7 +496,20 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
     // order the batch by row id (top sort_bits bits): monotone walks through every node vector
     const u64 *proc_rows = d_rows;
     const u32 *perm = nullptr;
-    if (m->sort_bits && n >= m->sort_min_n) {
+    if (m->sort_bits && n >= m->sort_min_n && ws->pipelined && m->sort_bits <= 16 && n < (u64(1) << 32)) {
+        // counting sort in three small kernels that fit beside the previous chunk's descent (order_*_kernel)
+        const u32 n_buckets = 1u << m->sort_bits, shift = m->row_bits - m->sort_bits;
+        if (ws->d_order.n < n_buckets) ws->d_order.alloc(n_buckets);
+        const u32 g = u32(std::min<u64>((n + 1023) / 1024, u64(m->sm_count) * 8));
+        CUDA_CHECK(cudaMemsetAsync(ws->d_order.p, 0, size_t(n_buckets) * 4, st));
+        order_hist_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, ws->d_order.p);
+        order_scan_kernel<<<1, 256, 0, st>>>(ws->d_order.p, n_buckets);
+        order_scatter_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, ws->d_order.p, ws->d_rows_sorted.p, ws->d_perm.p);
+        CUDA_CHECK(cudaGetLastError());
+        proc_rows = ws->d_rows_sorted.p;
+        perm = ws->d_perm.p;
+        ws->pending_sort_launches = 3;
+    } else if (m->sort_bits && n >= m->sort_min_n) {
         size_t sb = ws->sort_tmp_bytes;
         int end_bit = int(m->row_bits), begin_bit = int(m->row_bits - m->sort_bits);
         cub::DeviceRadixSort::SortPairs(ws->d_sort_tmp.p, sb, d_rows, ws->d_rows_sorted.p, ws->d_iota.p, ws->d_perm.p, n,
@@ -463,14 +520,30 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
         ws->pending_sort_launches = 1 + (end_bit - begin_bit + 7) / 8;   // cub onesweep: histogram + one kernel per 8-bit digit
     }
     CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));   // incl. the overflow flag in ctrl[4]
+    GGQ_MARK(st, "sorted");
     CUDA_CHECK(cudaEventRecord(ws->ev0, st));
     launch_rows_kernel(m, ws, proc_rows, perm, n);
     CUDA_CHECK(cudaEventRecord(ws->ev1, st));
-    size_t cb = ws->cub_bytes;
-    // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
-    CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
-    cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
-    CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 5 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    GGQ_MARK(st, "descent");
+    if (ws->pipelined) {
+        // the host learns the chunk's size as soon as the descent is done; offsets by the small scan kernels
+        publish_ctrl_kernel<<<1, 32, 0, st>>>(ws->d_ctrl.p, ws->h_ctrl);
+        CUDA_CHECK(cudaEventRecord(ws->ev_ctrl, st));
+        if (ws->hist_mode) { GGQ_MARK(st, "scan+ctrl"); return; }   // count_labels: no CSR, no offsets
+        const u32 nb = u32((n + 1 + kScanBlock - 1) / kScanBlock);
+        if (ws->d_blk.n < nb) throw std::runtime_error("scan scratch not reserved");
+        cnt_block_sum_kernel<<<nb, 256, 0, st>>>(ws->d_row_cnt.p, n, ws->d_blk.p);
+        block_sum_scan_kernel<<<1, 256, 0, st>>>(ws->d_blk.p, nb);
+        cnt_block_scan_kernel<<<nb, 256, 0, st>>>(ws->d_row_cnt.p, n, ws->d_blk.p, ws->d_offsets.p);
+        CUDA_CHECK(cudaGetLastError());
+    } else {
+        size_t cb = ws->cub_bytes;
+        // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
+        CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
+        cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 5 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+    }
+    GGQ_MARK(st, "scan+ctrl");
 }
 
 // Wait for brwt_rows_begin, then assemble the CSR (enqueued, not awaited).  The chunk arena grows and the query
@@ -484,13 +557,15 @@ static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         return;
     }
     for (int attempt = 0; attempt < 2; ++attempt) {
-        CUDA_CHECK(cudaStreamSynchronize(st));
+        if (ws->pipelined) CUDA_CHECK(cudaEventSynchronize(ws->ev_ctrl));
+        else CUDA_CHECK(cudaStreamSynchronize(st));
         if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) throw std::runtime_error("descent stack overflow (engine bug)");
         u64 total = ws->h_ctrl[0];
         ws->last_probes = ws->h_ctrl[2];
         ws->last_touches = ws->h_ctrl[3];
         ws->kernel_timed = true;
-        ws->launches = 3 + ws->pending_sort_launches;  // descent + 2 scan kernels (+ radix sort)
+        // descent + ordering + (2 cub scan kernels | pipelined: ctrl publish + 3 scan kernels, none for a histogram)
+        ws->launches = 1 + ws->pending_sort_launches + (ws->pipelined ? (ws->hist_mode ? 1 : 4) : 2);
         if (total > ws->d_tmp.n) {  // chunk arena too small: grow and redo
             ws->d_tmp.alloc(total + total / 8 + 1024);
             brwt_rows_begin(m, ws, d_rows, n);
@@ -986,17 +1061,14 @@ void ggq_rows_result_free(ggq_rows_result *r) {
 // travels to the host, chunk k+1 is sorted and descended — the PCIe copy, not the kernel, bounds this call.
 // rows per chunk of the pipelined host calls (GGQ_CHUNK_LOG2 overrides for experiments)
 static u64 pipeline_chunk() {
-    static const u64 v = [] {
-        const char *e = std::getenv("GGQ_CHUNK_LOG2");
-        const u64 l = e && *e ? std::strtoull(e, nullptr, 10) : 20;
-        return u64(1) << std::min<u64>(std::max<u64>(l, 10), 30);
-    }();
-    return v;
+    const char *e = std::getenv("GGQ_CHUNK_LOG2");
+    const u64 l = e && *e ? std::strtoull(e, nullptr, 10) : 20;
+    return u64(1) << std::min<u64>(std::max<u64>(l, 10), 30);
 }
 // count_labels returns only num_columns counters, so nothing but the first host->device copy is exposed: larger
 // chunks (measured on C4: 2^20 -> 1.03e9, 2^22 -> 1.12e9 rows/s); get_rows is best at 2^20 (device->host tail)
 static const u64 kCountChunk = u64(1) << 22;
-static const u64 kPipelineDepth = 3;   // workspaces (streams) a pipelined host call rotates over
+static const u64 kPipelineDepth = 4;   // workspaces (streams) a pipelined host call rotates over
 
 static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, void *cols_v,
                          uint64_t cols_capacity, uint64_t *n_cols, int col_bytes) {
@@ -1033,8 +1105,10 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     const bool brwt = m->kind == Matrix::BRWT;
     std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     int rc = GGQ_OK;
+    if (std::getenv("GGQ_TRACE") && n_chunks > 1 && !g_trace) g_trace = new Trace();
     try {
-        for (auto &p : w) p = m->acquire();
+        const bool room = n_chunks > 1 && !std::getenv("GGQ_NO_PIPE_ROOM");
+        for (auto &p : w) { p = m->acquire(); p->pipelined = room; }
         u64 base = 0;
         bool fits = true;
         int launches = 0;
@@ -1044,7 +1118,10 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             Workspace *ws = w[k % w.size()];
             const u64 nc = chunk_rows(k);
             ws->reserve_rows(nc);
+            g_trace_chunk = k;
+            GGQ_MARK(ws->stream, "begin");
             if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + start[k], nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            GGQ_MARK(ws->stream, "h2d");
             if (brwt) brwt_rows_begin(m, ws, ws->d_rows.p, nc);
         };
         begin(0);
@@ -1053,8 +1130,10 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             Workspace *ws = w[k % w.size()];
             const u64 nc = chunk_rows(k), r0 = start[k];
             u64 total = 0;
+            g_trace_chunk = k;
             if (brwt) brwt_rows_finish(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             else rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
+            GGQ_MARK(ws->stream, "gather");
             launches += ws->launches; probes += ws->last_probes; touches += ws->last_touches;
             if (base) {
                 add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
@@ -1065,10 +1144,12 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             if (base + total > cols_capacity || (total && !cols)) fits = false;
             if (fits && total)
                 CUDA_CHECK(cudaMemcpyAsync(cols + base * col_bytes, ws->d_out.p, total * col_bytes, cudaMemcpyDeviceToHost, ws->stream));
+            GGQ_MARK(ws->stream, "d2h");
             base += total;
         }
         for (Workspace *ws : w)
             if (ws) CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        if (g_trace) { g_trace->dump(); delete g_trace; g_trace = nullptr; }
         w[0]->launches = launches; w[0]->last_probes = probes; w[0]->last_touches = touches;
         m->last_probes = probes;
         if (n_cols) *n_cols = base;
@@ -1076,6 +1157,7 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     } catch (...) {
         for (Workspace *ws : w)
             if (ws) { cudaStreamSynchronize(ws->stream); m->release(ws); }
+        delete g_trace; g_trace = nullptr;
         throw;
     }
     for (Workspace *ws : w)
@@ -1132,7 +1214,8 @@ static void count_labels_pipelined(const ggq_matrix *m, const uint64_t *rows, ui
     std::vector<Workspace *> w(size_t(std::min<u64>(n_chunks, kPipelineDepth)), nullptr);
     cudaEvent_t zeroed = nullptr;
     try {
-        for (auto &p : w) p = m->acquire();
+        const bool room = !std::getenv("GGQ_NO_PIPE_ROOM");
+        for (auto &p : w) { p = m->acquire(); p->pipelined = room; }
         CUDA_CHECK(cudaEventCreateWithFlags(&zeroed, cudaEventDisableTiming));
         if (w[0]->d_counts.n < nc) w[0]->d_counts.alloc(nc);
         CUDA_CHECK(cudaMemsetAsync(w[0]->d_counts.p, 0, nc * 8, w[0]->stream));
@@ -1144,7 +1227,9 @@ static void count_labels_pipelined(const ggq_matrix *m, const uint64_t *rows, ui
             const u64 nr = chunk_rows(k);
             ws->reserve_rows(nr);
             CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + k * kCountChunk, nr * 8, cudaMemcpyHostToDevice, ws->stream));
-            brwt_rows_begin(m, ws, ws->d_rows.p, nr);
+            ws->hist_mode = true;
+            try { brwt_rows_begin(m, ws, ws->d_rows.p, nr); } catch (...) { ws->hist_mode = false; throw; }
+            ws->hist_mode = false;
         };
         int launches = 0;
         begin(0);

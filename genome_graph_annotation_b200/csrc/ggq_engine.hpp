@@ -1,5 +1,6 @@
 // Host-side objects behind the opaque C handles.
 #pragma once
+#include <atomic>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -70,7 +71,7 @@ struct Matrix {
 
     // stats
     u64 n_nodes = 0, total_column_size = 0, num_relations = 0, device_bytes = 0;
-    mutable u64 last_probes = 0;
+    mutable std::atomic<u64> last_probes{0};   // const calls from many threads store it (relaxed)
     std::vector<u64> lane_size_h, lane_ones_h;   // per lane: bits / set bits of its vector (host copy)
 
     // descent kernel configuration
@@ -78,6 +79,10 @@ struct Matrix {
     u32 root_child = 0xFFFFFFFFu, root_sl = 0, root_multi_sb = 0, any_more = 0;   // K1 root fast path (RowsArgs)
     u64 root_base = 0;
     size_t rows_smem = 0;
+    // pipelined host calls: one CTA per SM fewer (shared-memory request padded so that no more fit), which leaves
+    // room for the small kernels of the neighbouring chunks (ordering, scan, CSR gather) beside a running descent
+    u32 rows_grid_p = 148;
+    size_t rows_smem_p = 0;
     u32 sort_bits = 0, row_bits = 0;   // query ordering: sort on the top sort_bits of the row_bits-bit row id
     u64 sort_min_n = 4096;             // batches smaller than this are processed in the caller's order
 
@@ -118,6 +123,9 @@ struct Workspace {
     int pending_sort_launches = 0;   // between brwt_rows_begin and brwt_rows_finish
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
     bool kernel_timed = false;
+    bool pipelined = false;          // chunk of a pipelined host call: counting-sort ordering, descent leaves a CTA slot free
+    DeviceBuf<u32> d_order;          // bucket counters of the counting sort
+    DeviceBuf<u64> d_blk;            // block sums of the chunk's offset scan
     bool hist_mode = false;          // count_labels: skip CSR assembly, the ids stay unordered in d_tmp
     DeviceBuf<u64> d_counts;
     DeviceBuf<u64> d_col;            // get_column result
@@ -130,6 +138,7 @@ struct Workspace {
     DeviceBuf<u32> g_cols;
     DeviceBuf<unsigned char> m_out;
     cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+    cudaEvent_t ev_ctrl = nullptr;   // pipelined chunks: control words published (before the offset scan)
     bool exchange_timed = false;
     u64 exchange_bytes = 0;
 

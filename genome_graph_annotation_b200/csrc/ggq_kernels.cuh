@@ -381,6 +381,159 @@ __global__ void query_labels_gather_kernel(const u64 *csr_offsets, const u64 *qu
     }
 }
 
+// Batch ordering of the pipelined host API: a counting sort on the top bits of the row id (<= 2^16 buckets) in three
+// small kernels (no shared memory, few registers).  cub's onesweep passes need 49 KB of shared memory and 30 K
+// registers per CTA and cannot run beside the descent of the previous chunk; these can (the pipelined descent leaves
+// one CTA slot per SM free), which takes the ordering off the critical path of ggq_get_rows_into.  The order inside
+// a bucket is arrival order of the atomics: irrelevant to the result (perm maps every row back to its position),
+// and as good for locality as the stable order.
+__global__ void __launch_bounds__(256)
+order_hist_kernel(const u64 *rows, u64 n, u32 shift, u32 last_bucket, u32 *cnt) {
+    const u64 stride = u64(gridDim.x) * blockDim.x;
+    for (u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const u64 b = rows[i] >> shift;
+        atomicAdd(cnt + (b < last_bucket ? u32(b) : last_bucket), 1u);
+    }
+}
+
+// counts -> exclusive offsets, in place; one CTA of 256 threads (fits the free slot beside a running descent),
+// n_buckets <= 2^16
+__global__ void __launch_bounds__(256)
+order_scan_kernel(u32 *cnt, u32 n_buckets) {
+    __shared__ u32 warp_sum[8];
+    const u32 per = (n_buckets + 255) / 256;
+    const u32 b0 = threadIdx.x * per;
+    u32 sum = 0;
+    for (u32 j = 0; j < per; ++j)
+        if (b0 + j < n_buckets) sum += cnt[b0 + j];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u32 inc = sum;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_sum[warp] = inc;
+    __syncthreads();
+    u32 run = inc - sum;
+    for (u32 w = 0; w < warp; ++w) run += warp_sum[w];
+    for (u32 j = 0; j < per; ++j)
+        if (b0 + j < n_buckets) {
+            const u32 c = cnt[b0 + j];
+            cnt[b0 + j] = run;
+            run += c;
+        }
+}
+
+__global__ void __launch_bounds__(256)
+order_scatter_kernel(const u64 *rows, u64 n, u32 shift, u32 last_bucket, u32 *cursor, u64 *rows_sorted, u32 *perm) {
+    const u64 stride = u64(gridDim.x) * blockDim.x;
+    for (u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const u64 r = rows[i];
+        const u64 b = r >> shift;
+        const u32 pos = atomicAdd(cursor + (b < last_bucket ? u32(b) : last_bucket), 1u);
+        rows_sorted[pos] = r;
+        perm[pos] = u32(i);
+    }
+}
+
+// Offsets of the pipelined chunks: exclusive sum of the per-row counts (u32) to u64 offsets[0..n_rows] in three small
+// kernels (block sums, scan of the block sums, block-local scan).  cub::DeviceScan's kernel does not fit beside a
+// running descent either; a chunk whose scan has to wait for the NEXT chunk's descent delays the host by a whole
+// descent (GGQ_TRACE timeline).
+constexpr u32 kScanItems = 16, kScanBlock = 256 * kScanItems;
+
+__device__ __forceinline__ u64 warp_inclusive_u64(u64 v, u32 lane) {
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u64 x = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += x;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+cnt_block_sum_kernel(const u32 *cnt, u64 n_rows, u64 *block_sum) {
+    __shared__ u64 wsum[8];
+    const u64 base = u64(blockIdx.x) * kScanBlock;
+    u64 s = 0;
+    #pragma unroll 4
+    for (u32 j = 0; j < kScanItems; ++j) {
+        const u64 i = base + j * 256 + threadIdx.x;
+        if (i < n_rows) s += cnt[i];
+    }
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    s = warp_inclusive_u64(s, lane);
+    if (lane == 31) wsum[warp] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u64 t = 0;
+        for (u32 w = 0; w < 8; ++w) t += wsum[w];
+        block_sum[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+block_sum_scan_kernel(u64 *block_sum, u32 n_blocks) {
+    __shared__ u64 wsum[8];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u64 carry = 0;
+    for (u32 b0 = 0; b0 < n_blocks; b0 += 256) {
+        const u32 i = b0 + threadIdx.x;
+        const u64 v = i < n_blocks ? block_sum[i] : 0;
+        const u64 inc = warp_inclusive_u64(v, lane);
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        u64 pre = carry, tot = 0;
+        for (u32 w = 0; w < 8; ++w) {
+            if (w < warp) pre += wsum[w];
+            tot += wsum[w];
+        }
+        if (i < n_blocks) block_sum[i] = pre + inc - v;
+        carry += tot;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+cnt_block_scan_kernel(const u32 *cnt, u64 n_rows, const u64 *block_off, u64 *offsets) {
+    __shared__ u64 wsum[8];
+    const u64 i0 = u64(blockIdx.x) * kScanBlock + u64(threadIdx.x) * kScanItems;
+    u32 c[kScanItems];
+    if (i0 + kScanItems <= n_rows) {
+        const uint4 *p = reinterpret_cast<const uint4 *>(cnt + i0);
+        #pragma unroll
+        for (u32 j = 0; j < kScanItems / 4; ++j) {
+            const uint4 v = p[j];
+            c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
+        }
+    } else {
+        #pragma unroll
+        for (u32 j = 0; j < kScanItems; ++j) c[j] = i0 + j < n_rows ? cnt[i0 + j] : 0u;
+    }
+    u64 sum = 0;
+    #pragma unroll
+    for (u32 j = 0; j < kScanItems; ++j) sum += c[j];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u64 inc = warp_inclusive_u64(sum, lane);
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    u64 run = block_off[blockIdx.x] + inc - sum;
+    for (u32 w = 0; w < warp; ++w) run += wsum[w];
+    #pragma unroll
+    for (u32 j = 0; j < kScanItems; ++j) {
+        if (i0 + j <= n_rows) offsets[i0 + j] = run;   // n_rows + 1 offsets
+        run += c[j];
+    }
+}
+
+// control words -> pinned host memory by a store from the device: a cudaMemcpyAsync of 40 bytes would queue behind
+// the previous chunk's 40 MB device->host copy on the copy engine and delay the host's "chunk k is done"
+__global__ void publish_ctrl_kernel(const u64 *ctrl, u64 *host) {
+    if (threadIdx.x < 5) host[threadIdx.x] = ctrl[threadIdx.x];
+    __threadfence_system();
+}
+
 // Small-batch form of the label queries (one query sequence = 10^2..10^3 indices): the histogram kernel learns the
 // number of ids from the descent's control words on the device, and the filter writes the kept pairs and a status
 // word straight into pinned host memory — no host round trip between descent, histogram and threshold.
