@@ -395,7 +395,7 @@ void Workspace::reserve_rows(u64 n) {
         d_sort_tmp.alloc(sneed + 16);
         sort_tmp_bytes = sneed;
     }
-    d_blk.alloc((c + kScanBlock - 1) / kScanBlock + 1);
+    d_blk.alloc(std::max<u64>((c + kScanBlock - 1) / kScanBlock + 1, 64));
     size_t need = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, need, d_row_cnt.p, d_offsets.p, c, stream);
     d_cub.alloc(need + 16);
@@ -499,16 +499,21 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
     if (m->sort_bits && n >= m->sort_min_n && ws->pipelined && m->sort_bits <= 16 && n < (u64(1) << 32)) {
         // counting sort in three small kernels that fit beside the previous chunk's descent (order_*_kernel)
         const u32 n_buckets = 1u << m->sort_bits, shift = m->row_bits - m->sort_bits;
-        if (ws->d_order.n < n_buckets) ws->d_order.alloc(n_buckets);
+        if (ws->d_order.n < 2 * size_t(n_buckets) + 16) ws->d_order.alloc(2 * size_t(n_buckets) + 16);
+        u32 *cnt = ws->d_order.p, *cursor = ws->d_order.p + n_buckets;   // counts | exclusive offsets (n_buckets + 1)
         const u32 g = u32(std::min<u64>((n + 1023) / 1024, u64(m->sm_count) * 8));
-        CUDA_CHECK(cudaMemsetAsync(ws->d_order.p, 0, size_t(n_buckets) * 4, st));
-        order_hist_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, ws->d_order.p);
-        order_scan_kernel<<<1, 256, 0, st>>>(ws->d_order.p, n_buckets);
-        order_scatter_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, ws->d_order.p, ws->d_rows_sorted.p, ws->d_perm.p);
+        const u32 nbk = (n_buckets + 1 + kScanBlock - 1) / kScanBlock;
+        if (ws->d_blk.n < nbk) ws->d_blk.alloc(nbk + 16);
+        CUDA_CHECK(cudaMemsetAsync(cnt, 0, size_t(n_buckets) * 4, st));
+        order_hist_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, cnt);
+        cnt_block_sum_kernel<<<nbk, 256, 0, st>>>(cnt, n_buckets, ws->d_blk.p);
+        block_sum_scan_kernel<<<1, 256, 0, st>>>(ws->d_blk.p, nbk);
+        cnt_block_scan_kernel<u32><<<nbk, 256, 0, st>>>(cnt, n_buckets, ws->d_blk.p, cursor);
+        order_scatter_kernel<<<g, 256, 0, st>>>(d_rows, n, shift, n_buckets - 1, cursor, ws->d_rows_sorted.p, ws->d_perm.p);
         CUDA_CHECK(cudaGetLastError());
         proc_rows = ws->d_rows_sorted.p;
         perm = ws->d_perm.p;
-        ws->pending_sort_launches = 3;
+        ws->pending_sort_launches = 5;
     } else if (m->sort_bits && n >= m->sort_min_n) {
         size_t sb = ws->sort_tmp_bytes;
         int end_bit = int(m->row_bits), begin_bit = int(m->row_bits - m->sort_bits);
@@ -534,7 +539,7 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
         if (ws->d_blk.n < nb) throw std::runtime_error("scan scratch not reserved");
         cnt_block_sum_kernel<<<nb, 256, 0, st>>>(ws->d_row_cnt.p, n, ws->d_blk.p);
         block_sum_scan_kernel<<<1, 256, 0, st>>>(ws->d_blk.p, nb);
-        cnt_block_scan_kernel<<<nb, 256, 0, st>>>(ws->d_row_cnt.p, n, ws->d_blk.p, ws->d_offsets.p);
+        cnt_block_scan_kernel<u64><<<nb, 256, 0, st>>>(ws->d_row_cnt.p, n, ws->d_blk.p, ws->d_offsets.p);
         CUDA_CHECK(cudaGetLastError());
     } else {
         size_t cb = ws->cub_bytes;

@@ -386,7 +386,8 @@ __global__ void query_labels_gather_kernel(const u64 *csr_offsets, const u64 *qu
 // registers per CTA and cannot run beside the descent of the previous chunk; these can (the pipelined descent leaves
 // one CTA slot per SM free), which takes the ordering off the critical path of ggq_get_rows_into.  The order inside
 // a bucket is arrival order of the atomics: irrelevant to the result (perm maps every row back to its position),
-// and as good for locality as the stable order.
+// and as good for locality as the stable order.  The bucket counters are scanned by the block-scan kernels below
+// (a single-CTA scan of 2^16 counters took 116 us; these take ~10).
 __global__ void __launch_bounds__(256)
 order_hist_kernel(const u64 *rows, u64 n, u32 shift, u32 last_bucket, u32 *cnt) {
     const u64 stride = u64(gridDim.x) * blockDim.x;
@@ -394,35 +395,6 @@ order_hist_kernel(const u64 *rows, u64 n, u32 shift, u32 last_bucket, u32 *cnt) 
         const u64 b = rows[i] >> shift;
         atomicAdd(cnt + (b < last_bucket ? u32(b) : last_bucket), 1u);
     }
-}
-
-// counts -> exclusive offsets, in place; one CTA of 256 threads (fits the free slot beside a running descent),
-// n_buckets <= 2^16
-__global__ void __launch_bounds__(256)
-order_scan_kernel(u32 *cnt, u32 n_buckets) {
-    __shared__ u32 warp_sum[8];
-    const u32 per = (n_buckets + 255) / 256;
-    const u32 b0 = threadIdx.x * per;
-    u32 sum = 0;
-    for (u32 j = 0; j < per; ++j)
-        if (b0 + j < n_buckets) sum += cnt[b0 + j];
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    u32 inc = sum;
-    #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-    }
-    if (lane == 31) warp_sum[warp] = inc;
-    __syncthreads();
-    u32 run = inc - sum;
-    for (u32 w = 0; w < warp; ++w) run += warp_sum[w];
-    for (u32 j = 0; j < per; ++j)
-        if (b0 + j < n_buckets) {
-            const u32 c = cnt[b0 + j];
-            cnt[b0 + j] = run;
-            run += c;
-        }
 }
 
 __global__ void __launch_bounds__(256)
@@ -495,8 +467,9 @@ block_sum_scan_kernel(u64 *block_sum, u32 n_blocks) {
     }
 }
 
+template <typename OutT>
 __global__ void __launch_bounds__(256)
-cnt_block_scan_kernel(const u32 *cnt, u64 n_rows, const u64 *block_off, u64 *offsets) {
+cnt_block_scan_kernel(const u32 *cnt, u64 n_rows, const u64 *block_off, OutT *offsets) {
     __shared__ u64 wsum[8];
     const u64 i0 = u64(blockIdx.x) * kScanBlock + u64(threadIdx.x) * kScanItems;
     u32 c[kScanItems];
@@ -522,7 +495,7 @@ cnt_block_scan_kernel(const u32 *cnt, u64 n_rows, const u64 *block_off, u64 *off
     for (u32 w = 0; w < warp; ++w) run += wsum[w];
     #pragma unroll
     for (u32 j = 0; j < kScanItems; ++j) {
-        if (i0 + j <= n_rows) offsets[i0 + j] = run;   // n_rows + 1 offsets
+        if (i0 + j <= n_rows) offsets[i0 + j] = OutT(run);   // n_rows + 1 offsets
         run += c[j];
     }
 }

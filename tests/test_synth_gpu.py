@@ -125,6 +125,19 @@ def test_pipelined_host_api_matches_single_shot(ggq):
             lo = rep * rows.size
             assert np.array_equal(off3[lo:lo + rows.size + 1] - off3[lo], off)
             assert np.array_equal(cols3[int(off3[lo]):int(off3[lo + rows.size])], cols[:total].astype(np.uint32))
+        # out-of-range ids in a pipelined batch (empty rows, ggq.h): the counting sort of the chunks clamps them
+        # into its last bucket
+        bad = rows.copy()
+        bad[::4099] = np.uint64(n + 7)
+        bad[5::8191] = np.uint64(2**64 - 2)
+        offb = np.empty_like(off)
+        colsb = np.empty(cols.size, np.uint32)
+        totb = gm.get_rows_into(bad, offb, colsb)
+        lens, lensb = np.diff(off.astype(np.int64)), np.diff(offb.astype(np.int64))
+        is_bad = bad >= np.uint64(n)
+        assert np.all(lensb[is_bad] == 0) and np.array_equal(lensb[~is_bad], lens[~is_bad])
+        keep = np.repeat(~is_bad, lens)
+        assert np.array_equal(colsb[:totb], cols[:total][keep].astype(np.uint32))
         # compact u32 ids: same CSR
         cols32 = np.empty(cols.size, np.uint32)
         off32 = np.empty_like(off)
