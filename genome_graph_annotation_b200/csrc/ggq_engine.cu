@@ -190,7 +190,11 @@ void Matrix::refresh_img() {
 }
 
 // The instantiation of K1 for a tree: stack spill to global memory, leaves holding several columns.
-static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact) {
+static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact, bool emit_flat = false) {
+    if (emit_flat && !spill) {   // experimental emit (GGQ_EMIT_FLAT=1), see ggq_rows.cuh
+        if (compact) return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true, true> : (const void *)brwt_rows_kernel<false, false, true, true>;
+        return multi_leaf ? (const void *)brwt_rows_kernel<false, true, false, true> : (const void *)brwt_rows_kernel<false, false, false, true>;
+    }
     if (compact) {
         if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, true> : (const void *)brwt_rows_kernel<true, false, true>;
         return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true> : (const void *)brwt_rows_kernel<false, false, true>;
@@ -227,8 +231,10 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
         rb >>= 1;
     }
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
+    // flat emit needs 16-byte aligned per-warp bitmaps and no stack spill
+    emit_flat = env_u32("GGQ_EMIT_FLAT", 0) != 0 && cap_spill == 0 && (size_t(rb) * bm_words) % 4 == 0;
     int per_sm = 0;
-    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec);
+    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec, emit_flat);
     CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
@@ -478,7 +484,7 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     u32 grid = u32(std::min<u64>(full_grid, (batches + kRowsWarps - 1) / kRowsWarps));
     Img img = m->img;
     void *kargs[] = {&img, &a};
-    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid),
+    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->emit_flat), dim3(grid),
                                 dim3(kRowsWarps * 32), kargs, ws->pipelined ? m->rows_smem_p : m->rows_smem, ws->stream));
 }
 

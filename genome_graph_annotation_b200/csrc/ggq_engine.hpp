@@ -66,6 +66,7 @@ struct Matrix {
     DeviceBuf<uint4> group_rec;   // per (group, half): hot word + the two children's lane_info (descent kernel)
     DeviceBuf<uint4> group_rec16; // per group: compact record (trees with < 2^20 - 1 columns), else empty
     bool compact_rec = false;
+    bool emit_flat = false;       // experimental K1 emit (GGQ_EMIT_FLAT=1)
     DeviceBuf<u32> lane_info, lane_aux, lane_sb_off, sel, leaf_col, col_path_off, col_path;
     Img img{};
 

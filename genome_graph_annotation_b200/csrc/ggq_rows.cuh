@@ -77,6 +77,15 @@ __device__ __forceinline__ void sts32(u32 a, u32 v) { asm volatile("st.shared.u3
 __device__ __forceinline__ void reds_or(u32 a, u32 v) { asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void reds_add(u32 a, u32 v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
+__device__ __forceinline__ uint4 lds128(u32 a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128_zero(u32 a) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" :: "r"(a), "r"(0u) : "memory");
+}
+
 template <bool SPILL>
 __device__ __forceinline__ u64 stk_get(u32 stk, const u64 *spill, u32 cap_s, u32 i) {
     if (!SPILL) return lds64(stk + i * 8);
@@ -169,7 +178,7 @@ __device__ __forceinline__ void load_rec(const Img &img, u32 g, u32 half, u64 &b
     }
 }
 
-template <bool SPILL, bool MULTI_LEAF, bool COMPACT>
+template <bool SPILL, bool MULTI_LEAF, bool COMPACT, bool EMIT_FLAT = false>
 __global__ void __launch_bounds__(kRowsWarps * 32)
 brwt_rows_kernel(Img img, RowsArgs a) {
     typedef RecFmt<COMPACT> Fmt;
@@ -335,7 +344,51 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             a.row_tmp_off[q] = base + pre;
             a.row_cnt[q] = my_cnt;
         }
-        if (total) {
+        if (EMIT_FLAT) {
+            // Flat emit (experimental, GGQ_EMIT_FLAT=1): the tile's bitmaps are one contiguous array of nr * bm_words
+            // words and (row, rank) order IS its flat order, so the scan needs no row loop and no queue: 128-bit
+            // loads (4 words per lane), a warp prefix sum of the popcounts, ids stored straight from the bits.
+            // 664 words per C4 tile = 6 iterations instead of 24 (profiles/r01/k1_sass_budget.txt).
+            if (total) {
+                const bool fits = base + total <= a.tmp_cap;
+                const u32 n_vec = (nr * a.bm_words + 3) >> 2;
+                // floor(2^32 / bm_words) + 1: word index within the row by one mulhi (exact for f * bm_words < 2^32)
+                const u32 bm_magic = a.bm_words > 1 ? u32((u64(1) << 32) / a.bm_words) + 1u : 0u;
+                u64 pos = base;
+                for (u32 v0 = 0; v0 < n_vec; v0 += 32) {
+                    const u32 v = v0 + lane;
+                    uint4 b = make_uint4(0u, 0u, 0u, 0u);
+                    if (v < n_vec) b = lds128(bm + v * 16);
+                    const bool any = (b.x | b.y | b.z | b.w) != 0;
+                    if (!__any_sync(0xffffffffu, any)) continue;
+                    if (any) sts128_zero(bm + v * 16);
+                    const u32 c = __popc(b.x) + __popc(b.y) + __popc(b.z) + __popc(b.w);
+                    u32 inc = c;
+                    #pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const u32 x = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += x;
+                    }
+                    if (c && fits) {
+                        u64 p = pos + inc - c;
+                        const u32 wv[4] = {b.x, b.y, b.z, b.w};
+                        #pragma unroll
+                        for (u32 j = 0; j < 4; ++j) {
+                            u32 bits = wv[j];
+                            if (!bits) continue;
+                            const u32 f = v * 4 + j;   // flat word -> word within its row
+                            const u32 w = a.bm_words == 1 ? 0u : f - __umulhi(f, bm_magic) * a.bm_words;
+                            while (bits) {
+                                const u32 bit = __ffs(bits) - 1;
+                                bits &= bits - 1;
+                                a.tmp_cols[p++] = __ldg(img.leaf_col + w * 32 + bit);
+                            }
+                        }
+                    }
+                    pos += __shfl_sync(0xffffffffu, inc, 31);
+                }
+            }
+        } else if (total) {
             const bool fits = base + total <= a.tmp_cap;   // else: the engine grows the arena and reruns
             const u32 rows_mask = __ballot_sync(0xffffffffu, my_cnt != 0);
             u64 pos = base;
