@@ -255,9 +255,6 @@ def test_stack_spill_instantiation_gives_the_same_rows(ggq, orc, monkeypatch):
         gs.close()
 
 
-@pytest.mark.skipif(not __import__("os").environ.get("GGQ_TEST_EXPERIMENTAL"),
-                    reason="experimental K1 emit (GGQ_EMIT_FLAT=1), written after the round's GPU budget was spent: "
-                           "not yet run on a GPU; set GGQ_TEST_EXPERIMENTAL=1 to run")
 @pytest.mark.parametrize("n,m,d,arity", [(20_000, 400, 0.02, 4), (50_000, 2652, 0.003, 4), (9_000, 36, 0.4, 2),
                                          (3_000, 1, 0.5, 4)])
 def test_flat_emit_gives_the_same_rows(ggq, n, m, d, arity, monkeypatch):
