@@ -16,3 +16,5 @@ for name in ("default", "flat"):
     except Exception as e:
         print(name, "failed:", e)
 P
+# chunk size of the pipelined host calls after the pipeline rework (2^20 was tuned for the old pipeline)
+timeout 200 python scripts/trace_e2e.py --chunk-log2 19,20 2> /dev/null
