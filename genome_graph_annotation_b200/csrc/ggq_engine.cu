@@ -503,7 +503,8 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
     const u64 *proc_rows = d_rows;
     const u32 *perm = nullptr;
     if (m->sort_bits && n >= m->sort_min_n && ws->pipelined && m->sort_bits <= 16 && n < (u64(1) << 32)) {
-        // counting sort in three small kernels that fit beside the previous chunk's descent (order_*_kernel)
+        // counting sort (histogram, block scan of the bucket counters, scatter): small kernels that fit beside the
+        // previous chunk's descent
         const u32 n_buckets = 1u << m->sort_bits, shift = m->row_bits - m->sort_bits;
         if (ws->d_order.n < 2 * size_t(n_buckets) + 16) ws->d_order.alloc(2 * size_t(n_buckets) + 16);
         u32 *cnt = ws->d_order.p, *cursor = ws->d_order.p + n_buckets;   // counts | exclusive offsets (n_buckets + 1)

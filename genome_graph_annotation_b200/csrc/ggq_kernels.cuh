@@ -381,8 +381,8 @@ __global__ void query_labels_gather_kernel(const u64 *csr_offsets, const u64 *qu
     }
 }
 
-// Batch ordering of the pipelined host API: a counting sort on the top bits of the row id (<= 2^16 buckets) in three
-// small kernels (no shared memory, few registers).  cub's onesweep passes need 49 KB of shared memory and 30 K
+// Batch ordering of the pipelined host API: a counting sort on the top bits of the row id (<= 2^16 buckets) in small
+// kernels (no shared memory to speak of, few registers).  cub's onesweep passes need 49 KB of shared memory and 30 K
 // registers per CTA and cannot run beside the descent of the previous chunk; these can (the pipelined descent leaves
 // one CTA slot per SM free), which takes the ordering off the critical path of ggq_get_rows_into.  The order inside
 // a bucket is arrival order of the atomics: irrelevant to the result (perm maps every row back to its position),
