@@ -73,7 +73,9 @@ def parse_args():
     ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
                     help="c4: Kingsford-shaped, replicas (headline); c5: RefSeq-shaped 1e9 x 3173 d=3.8%%, column-sharded "
                          "over all ranks with the NCCL exchange (needs --gpus >= 2)")
+    ap.add_argument("--spot-rows", type=int, default=1 << 20, help="rows of the full-scale parity sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bitvector", action="store_true", help="skip the rank1/select1/get block (C3)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-peer", action="store_true",
                     help="c5: exchange partial rows with NCCL instead of merging from peer memory over NVLink")
@@ -162,14 +164,24 @@ class ClockSampler:
 # `omp parallel for` over row ids (oracle/ref_capi.cpp) on all host threads, on an n'-row sub-shape of
 # the same generator (the reference builder cannot make 3.7e9 rows: SURVEY.md §7b(d)).
 # --------------------------------------------------------------------------------------------
+def host_threads():
+    """Host threads this process may run on.  NOT omp_get_max_threads(): torch.distributed.run exports
+    OMP_NUM_THREADS=1 to every rank, which would time the reference on one core (round-1 verdict)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def build_cpu_reference(args):
+    threads = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(threads)   # before libgomp initialises (it is loaded with libggref.so)
     from oracle import ref_binding as R  # checker / baseline only
     import genome_graph_annotation_b200 as g
     if not R.available():
         return None
     n = int(args.cpu_rows)
     thr = g.density_threshold(args.density)
-    threads = R.max_threads()
     cw = R.gen_implicit(n, args.cols, thr, SEED)
     rm = R.RefMatrix.build_brwt(cw, n, arity=args.arity, threads=threads)
     del cw
@@ -219,14 +231,18 @@ def run_reference(args):
               "basic partitioner arity %d); unmodified BRWT::get_row under omp parallel for" %
               (cnt, n, args.cols, args.density, args.arity))
     line.update({"value": v, "ms_per_step": ms,
-                 "config": workload_config(args, 1, sub_rows=n),
-                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
+                 "config": workload_config(args, args.gpus),
+                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample,
+                                  "cpu_sub_shape_rows": n,
+                                  "why_sub_shape": "the reference builder materialises every column on the host: 3.7e9 x 2652 "
+                                                   "cannot be built; 1e6 rows (node vectors cache-resident, which favours the "
+                                                   "CPU) keeps the arm within its time budget (SURVEY.md 8d allows 1e6)"},
                  "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
     emit(line)
 
 
-def workload_config(args, n_gpus, sub_rows=None):
+def workload_config(args, n_gpus):
     c = {"workload": "C4 Kingsford-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner; "
                      "get_rows over %d uniformly random row ids per GPU per step" %
                      (args.rows, args.cols, args.density, args.arity, args.batch),
@@ -234,9 +250,69 @@ def workload_config(args, n_gpus, sub_rows=None):
          "batch_rows_per_gpu": args.batch, "seed": SEED,
          "parallelism": "replicas x%d, batch-sharded, no data-path collective" % n_gpus,
          "l2": "inputs larger than L2 (random gathers over the whole device image)"}
-    if sub_rows is not None:
-        c["cpu_sub_shape_rows"] = sub_rows
     return c
+
+
+def bitvector_block(cpu):
+    """rank1 / select1 / get on 2^32-bit bit_vector_{stat,sd,rrr} at d = 1 % and 50 % (scripts/bench_bv.py holds the
+    full C3 sweep): G ops/s, algorithmic GB/s per SURVEY.md 8(d) against the measured HBM peak, and the unmodified
+    reference's ops/s on all host threads (2^28-bit prefix of the same generator, 2^20 answers compared)."""
+    from scripts import bench_bv
+    t0 = time.time()
+    peak, res = bench_bv.measure(["stat", "sd", "rrr"], [0.01, 0.5], log2_bits=32, log2_queries=26, log2_cpu_bits=28, cpu=cpu)
+    out = {"n_bits": 1 << 32, "queries": 1 << 26, "peak_hbm_gbs": peak, "seconds": None, "results": []}
+    for r in res:
+        e = {"kind": r["kind"], "density": r["density"], "device_bytes": r["device_bytes"], "residency": r["residency"]}
+        for op, o in r["ops"].items():
+            e[op] = {"gops_per_s": o["ops_per_s"] / 1e9, "bytes_per_op": o["algorithmic_bytes_per_op"],
+                     "roofline_frac": o["frac_of_measured_hbm_peak"]}
+            if "cpu_reference_ops_per_s" in o:
+                e[op]["cpu_gops_per_s"] = o["cpu_reference_ops_per_s"] / 1e9
+        if "parity_vs_reference_2^20_samples" in r:
+            e["identical_to_reference"] = all(r["parity_vs_reference_2^20_samples"].values())
+            e["cpu_threads"] = r["cpu"]["threads"]
+        out["results"].append(e)
+    out["seconds"] = time.time() - t0
+    return out
+
+
+def direct_rows(rows, m, density, threads=None):
+    """CSR (counts, column ids) of the given rows by direct evaluation of the implicit matrix
+    M[i][j] = mix64(seed*K + i*m + j) < floor(d*2^64) (SURVEY.md 8d portable generator) in numpy — independent of
+    the engine and of the oracle.  Columns ascending per row, which for the basic partitioner IS the DFS order of
+    BRWT::get_row (BRWT.cpp:45-50).  Chunks of rows are evaluated on `threads` host threads (numpy releases the GIL)."""
+    import genome_graph_annotation_b200 as g
+    from concurrent.futures import ThreadPoolExecutor
+    thr = np.uint64(g.density_threshold(density))
+    base = np.uint64((SEED * g.SEED_MUL) % 2**64)
+    jj = np.arange(m, dtype=np.uint64)[None, :]
+    step = 2048
+
+    def chunk(lo):
+        r = rows[lo:lo + step]
+        with np.errstate(over="ignore"):
+            hit = g.mix64(base + r[:, None] * np.uint64(m) + jj) < thr
+        ri, ci = np.nonzero(hit)
+        return np.bincount(ri, minlength=r.size).astype(np.uint64), ci.astype(np.uint64)
+
+    with ThreadPoolExecutor(max_workers=threads or host_threads()) as ex:
+        parts = list(ex.map(chunk, range(0, rows.size, step)))
+    counts = np.concatenate([p[0] for p in parts]) if parts else np.zeros(0, np.uint64)
+    cols = np.concatenate([p[1] for p in parts]) if parts else np.zeros(0, np.uint64)
+    return counts, cols
+
+
+def spot_check(gm, rows, m, density, what="get_rows_csr"):
+    t0 = time.time()
+    s_off, s_cols = gm.get_rows_csr(rows)
+    counts, cols = direct_rows(rows, m, density)
+    same = (np.array_equal(np.diff(s_off.astype(np.int64)), counts.astype(np.int64)) and
+            np.array_equal(np.asarray(s_cols, dtype=np.uint64), cols))
+    if not same:
+        raise RuntimeError("bench.py: rows of the measured matrix differ from direct evaluation")
+    return {"rows": int(rows.size), "column_ids": int(cols.size), "identical": True, "seconds": time.time() - t0,
+            "against": "direct numpy evaluation of the implicit matrix (SURVEY.md 8d generator) on the full-size "
+                       "matrix: per-row counts and ids in DFS order, every row of the sample"}
 
 
 # --------------------------------------------------------------------------------------------
@@ -313,21 +389,9 @@ def run_ours(args):
     ms_step = float(t.item()) / K
     value = world * B / (ms_step / 1e3)
 
-    # ---- full-scale spot check (outside every timed region): rows of the measured matrix against direct
-    # evaluation of M[i][j] = mix64(seed*K + i*m + j) < T in numpy; for the basic partitioner DFS order = ascending
-    spot_rows = 4096
-    sr = batches[0][:spot_rows].cpu().numpy().view(np.uint64)
-    s_off, s_cols = gm.get_rows_csr(sr)
-    thr = np.uint64(g.density_threshold(args.density))
-    base = np.uint64((SEED * g.SEED_MUL) % 2**64)
-    jj = np.arange(args.cols, dtype=np.uint64)
-    with np.errstate(over="ignore"):
-        for t in range(spot_rows):
-            exp = np.nonzero(g.mix64(base + sr[t] * np.uint64(args.cols) + jj) < thr)[0].astype(np.uint64)
-            if not np.array_equal(s_cols[int(s_off[t]):int(s_off[t + 1])], exp):
-                raise RuntimeError("bench.py: row %d of the measured matrix differs from direct evaluation" % int(sr[t]))
-    spot = {"rows": spot_rows, "identical": True,
-            "against": "direct numpy evaluation of the implicit matrix (SURVEY.md 8d generator), full-size matrix"}
+    # ---- full-scale spot check (outside every timed region; SURVEY.md 8d "C4 / C5 concrete input"): every row of a
+    # 2^20-row sample of the measured batch against direct evaluation of the implicit matrix
+    spot = spot_check(gm, batches[0][:args.spot_rows].cpu().numpy().view(np.uint64), args.cols, args.density)
 
     # ---- the other calls of the BinaryMatrix interface on the same matrix (host to host, outside the headline):
     # get_column (BRWT.cpp:55-85) for a few columns, get (BRWT.cpp:9-24) for 2^22 random cells
@@ -474,9 +538,13 @@ def run_ours(args):
                 "sample": "%d random rows in %.1f s on a %d x %d d=%g sub-shape (same generator; the reference "
                           "builder cannot make the full shape); unmodified BRWT::get_row under omp parallel for" %
                           (cnt, secs, sub_n, args.cols, args.density)}
-    emit(line)
     ws.close()
     gm.close()
+    # ---- the metric's "rank/select ops/s" term (BASELINE.json configs[2]): independent vectors =>
+    # replicas only, measured on rank 0
+    if not args.no_bitvector:
+        line["bitvector"] = bitvector_block(cpu=(world == 1 and not args.no_cpu_baseline))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -236,6 +236,26 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     int per_sm = 0;
     const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec, emit_flat);
     CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
+    CUDA_CHECK(cudaFuncSetAttribute(rows_kernel_fn(true, tree.multi_column_leaves != 0, compact_rec),
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));   // the safe fallback below
+    {   // provable stack bound: the items of one row that are pending at any time head disjoint subtrees of the group
+        // tree (children groups + continuation group), and every such subtree contains a group without successors
+        u64 leaves = 0;
+        const u32 G = tree.n_groups();
+        for (u32 g = 0; g < G; ++g) {
+            const u64 h = tree.group_hot[g];
+            bool succ = ((h >> kGhMoreShift) & 1u) != 0;
+            const u32 cnt = u32(h >> kGhCntShift) & 7u;
+            for (u32 k = 0; k < cnt && !succ; ++k) {
+                const u32 info = tree.lane_info[g * 4 + k];
+                succ = !(info & kLeafFlag);   // (kRemoteLane has the leaf bit: never descended)
+            }
+            leaves += !succ;
+        }
+        cap_safe = u32(std::min<u64>(std::max<u64>(leaves, 1) * rb + 2 * kItemsPerIter, 0x7fffffffu));
+        if (env_u32("GGQ_STACK_UNDERESTIMATE", 0) && cap_spill == 0)   // tests: force the overflow -> safe-mode path
+            cap_s = std::max<u32>(rb + 2, std::min<u32>(cap_s, env_u32("GGQ_STACK_UNDERESTIMATE", 0)) & ~1u);
+    }
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
     if (per_sm < 1) per_sm = 1;
     rows_grid = u32(sm_count * per_sm);
@@ -367,8 +387,6 @@ Workspace::Workspace(const Matrix *m_) : m(m_) {
     CUDA_CHECK(cudaEventCreate(&ev2));
     CUDA_CHECK(cudaEventCreate(&ev3));
     CUDA_CHECK(cudaEventCreateWithFlags(&ev_ctrl, cudaEventDisableTiming));
-    if (m->kind == Matrix::BRWT && m->cap_spill)
-        d_spill.alloc(size_t(m->rows_grid) * kRowsWarps * m->cap_spill);
 }
 
 Workspace::~Workspace() {
@@ -475,16 +493,25 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     a.tmp_cols = ws->d_tmp.p; a.tmp_cap = ws->d_tmp.n;
     a.cursor = ws->d_ctrl.p;
     a.row_tmp_off = ws->d_row_tmp_off.p; a.row_cnt = ws->d_row_cnt.p;
-    a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = m->cap_spill;
+    const bool safe = m->stack_safe.load(std::memory_order_relaxed);
+    const u32 full_grid = ws->pipelined ? m->rows_grid_p : m->rows_grid;
+    const u32 cap_spill = safe ? m->cap_safe : m->cap_spill;   // safe: spill instantiation with the provable capacity
+    u32 grid_cap = m->rows_grid;
+    if (cap_spill) {   // at most ~1 GiB of spill area per workspace: very wide trees run the safe mode on fewer CTAs
+        grid_cap = u32(std::max<u64>(1, std::min<u64>(grid_cap, (u64(1) << 27) / (u64(kRowsWarps) * cap_spill))));
+        const size_t need = size_t(grid_cap) * kRowsWarps * cap_spill;
+        if (ws->d_spill.n < need) { CUDA_CHECK(cudaStreamSynchronize(ws->stream)); ws->d_spill.alloc(need); }
+    }
+    a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = cap_spill;
     a.bm_words = m->bm_words; a.rb = m->rb; a.err = reinterpret_cast<int *>(ws->d_ctrl.p + 4);
     a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
     a.root_base = m->root_base; a.any_more = m->any_more;
     u64 batches = (n + m->rb - 1) / m->rb;
-    const u32 full_grid = ws->pipelined ? m->rows_grid_p : m->rows_grid;
-    u32 grid = u32(std::min<u64>(full_grid, (batches + kRowsWarps - 1) / kRowsWarps));
+    u32 grid = u32(std::min<u64>(std::min(full_grid, grid_cap), (batches + kRowsWarps - 1) / kRowsWarps));
+    ws->ran_safe = safe;
     Img img = m->img;
     void *kargs[] = {&img, &a};
-    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->emit_flat), dim3(grid),
+    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->emit_flat), dim3(grid),
                                 dim3(kRowsWarps * 32), kargs, ws->pipelined ? m->rows_smem_p : m->rows_smem, ws->stream));
 }
 
@@ -568,10 +595,17 @@ static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         ws->launches = 0;
         return;
     }
-    for (int attempt = 0; attempt < 2; ++attempt) {
+    for (int attempt = 0; attempt < 3; ++attempt) {
         if (ws->pipelined) CUDA_CHECK(cudaEventSynchronize(ws->ev_ctrl));
         else CUDA_CHECK(cudaStreamSynchronize(st));
-        if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) throw std::runtime_error("descent stack overflow (engine bug)");
+        if (*reinterpret_cast<int *>(ws->h_ctrl + 4)) {
+            // the estimated stack capacity was too small for this batch: nothing was written out of bounds (K1 checks
+            // before it pushes); switch the matrix to the provable capacity and redo the batch
+            if (ws->ran_safe) throw std::runtime_error("descent stack overflow beyond the provable bound (engine bug)");
+            m->stack_safe.store(true, std::memory_order_relaxed);
+            brwt_rows_begin(m, ws, d_rows, n);
+            continue;
+        }
         u64 total = ws->h_ctrl[0];
         ws->last_probes = ws->h_ctrl[2];
         ws->last_touches = ws->h_ctrl[3];
@@ -1028,8 +1062,8 @@ int ggq_get_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ggq_rows
                                                   u32(n), host, cap_ids);
             CUDA_CHECK(cudaGetLastError());
             CUDA_CHECK(cudaStreamSynchronize(st));
-            if (host[1] & 1) throw std::runtime_error("descent stack overflow (engine bug)");
-            if (!(host[1] & 2)) {
+            if (host[1] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
+            if (!(host[1] & 3)) {
                 ws->launches = 2; ws->kernel_timed = false; ws->last_probes = 0; ws->last_touches = 0;
                 ggq_rows_result *r = new ggq_rows_result();
                 r->m = m; r->ws = ws; r->n = n; r->total = host[0];
@@ -1351,8 +1385,8 @@ static int labels_query(const ggq_matrix *m, const uint64_t *rows, uint64_t n, u
             label_filter_small_kernel<<<1, 1024, 0, st>>>(ws->d_counts.p, u32(nc_s), min_count, ws->d_ctrl.p, ws->d_tmp.n, host);
             CUDA_CHECK(cudaGetLastError());
             CUDA_CHECK(cudaStreamSynchronize(st));
-            if (host[1] & 1) throw std::runtime_error("descent stack overflow (engine bug)");
-            if (!(host[1] & 2)) {
+            if (host[1] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
+            if (!(host[1] & 3)) {
                 const u64 kept = host[0];
                 if (kept && cols) std::memcpy(cols, host + 2, kept * 8);
                 if (kept && counts) std::memcpy(counts, host + 2 + nc_s, kept * 8);
@@ -1516,11 +1550,11 @@ int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64
                 ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p), n, d_slice.p);
             CUDA_CHECK(cudaGetLastError());
         }
-        uint64_t *h = static_cast<uint64_t *>(std::malloc(std::max<u64>(len, 1) * 8));
+        std::unique_ptr<uint64_t, decltype(&std::free)> h(static_cast<uint64_t *>(std::malloc(std::max<u64>(len, 1) * 8)), &std::free);
         if (!h) throw std::bad_alloc();
-        if (len) CUDA_CHECK(cudaMemcpyAsync(h, d_slice.p, len * 8, cudaMemcpyDeviceToHost, ws->stream));
+        if (len) CUDA_CHECK(cudaMemcpyAsync(h.get(), d_slice.p, len * 8, cudaMemcpyDeviceToHost, ws->stream));
         CUDA_CHECK(cudaStreamSynchronize(ws->stream));
-        *out = h;
+        *out = h.release();
         *out_len = len;
     } catch (...) {
         m->release(ws);

@@ -77,6 +77,12 @@ struct Matrix {
 
     // descent kernel configuration
     u32 bm_words = 1, rb = 8, cap_s = 64, cap_spill = 0, rows_grid = 148;
+    // cap_s / cap_spill come from a replay of the kernel's pop/push policy (simulate_stack): an estimate.  The kernel
+    // never writes past it; when a batch would, it raises a flag and the engine switches the matrix to the spill
+    // instantiation with cap_safe = rows per tile x leaves of the group tree (pending items of one row are disjoint
+    // subtrees of the group tree, so this many can never be exceeded) and reruns the batch.
+    u32 cap_safe = 0;
+    mutable std::atomic<bool> stack_safe{false};
     u32 root_child = 0xFFFFFFFFu, root_sl = 0, root_multi_sb = 0, any_more = 0;   // K1 root fast path (RowsArgs)
     u64 root_base = 0;
     size_t rows_smem = 0;
@@ -124,6 +130,7 @@ struct Workspace {
     int pending_sort_launches = 0;   // between brwt_rows_begin and brwt_rows_finish
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query
     bool kernel_timed = false;
+    bool ran_safe = false;           // last descent ran with the provable stack capacity (Matrix::stack_safe)
     bool pipelined = false;          // chunk of a pipelined host call: counting-sort ordering, descent leaves a CTA slot free
     DeviceBuf<u32> d_order;          // bucket counters of the counting sort
     DeviceBuf<u64> d_blk;            // block sums of the chunk's offset scan

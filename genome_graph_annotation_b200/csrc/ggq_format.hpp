@@ -75,7 +75,10 @@ struct IntVector {
     uint64_t size() const { return width ? bit_size / width : 0; }
 
     // value of element i (width <= 64); same bit addressing as sdsl::bits::read_int
-    uint64_t get(uint64_t i) const { return get_bits(i * width, width); }
+    uint64_t get(uint64_t i) const {
+        if (i >= size()) throw ParseError("int_vector index out of range");   // (also keeps i * width from wrapping)
+        return get_bits(i * width, width);
+    }
 
     uint64_t get_bits(uint64_t bit_pos, unsigned len) const {
         if (!len) return 0;
@@ -199,7 +202,9 @@ inline void load_rrr63(Reader &in, PlainBits *out) {
     uint64_t pos = 0;
     for (uint64_t b = 0; b < n_blocks; ++b) {
         if (b % K == 0) {
-            pos = btnrp.get(b / K);
+            const uint64_t p = btnrp.get(b / K);   // file-controlled: must not run backwards or past the offsets
+            if (p > btnr.bit_size || (b && p < pos)) throw ParseError("rrr: superblock pointer out of range");
+            pos = p;
         }
         unsigned stored = unsigned(bt.get(b));
         if (stored > BS) throw ParseError("rrr: block type out of range");
@@ -208,7 +213,7 @@ inline void load_rrr63(Reader &in, PlainBits *out) {
         uint64_t start = b * BS;
         unsigned len = unsigned(std::min<uint64_t>(BS, m_size - std::min(m_size, start)));
         if (sp) {
-            if (pos + sp > btnr.bit_size) throw ParseError("rrr: btnr overrun");
+            if (pos > btnr.bit_size || sp > btnr.bit_size - pos) throw ParseError("rrr: btnr overrun");
             uint64_t nr = btnr.get_bits(pos, sp);
             uint64_t bits = B.decode(k, nr);
             if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");

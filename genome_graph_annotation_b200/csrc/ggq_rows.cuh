@@ -309,8 +309,17 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             const u32 m0 = __ballot_sync(0xffffffffu, push0);
             const u32 m1 = __ballot_sync(0xffffffffu, push1);
             u32 pos = top - c;
-            if (a.any_more) {   // uniform: trees of arity <= 4 have no continuation groups
-                const u32 cont_mask = __ballot_sync(0xffffffffu, push_cont);
+            u32 cont_mask = 0;
+            if (a.any_more) cont_mask = __ballot_sync(0xffffffffu, push_cont);   // uniform: trees of arity <= 4 have no continuation groups
+            const u32 new_top = pos + __popc(cont_mask) + __popc(m0) + __popc(m1);
+            // The capacity comes from a replay of this loop on the host (simulate_stack), which is an estimate, not a
+            // bound: never write past it.  One uniform compare per iteration; the engine reruns the batch with the
+            // spill instantiation and a provable capacity when the flag is set (Matrix::stack_safe).
+            if (new_top > cap_total) {
+                if (lane == 0) *a.err = 1;
+                break;
+            }
+            if (a.any_more) {
                 if (push_cont)
                     stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(cont_mask & lt_mask), item + 1, a.err);
                 pos += __popc(cont_mask);
@@ -318,8 +327,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             if (push0) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m0 & lt_mask), item0, a.err);
             pos += __popc(m0);
             if (push1) stk_set<SPILL>(stk, spill, a.cap_s, cap_total, pos + __popc(m1 & lt_mask), item1, a.err);
-            top = pos + __popc(m1);
-            if (SPILL && top > cap_total) top = cap_total;  // overflow already flagged in *err
+            top = new_top;
             probes += c;
             __syncwarp();
         }

@@ -124,12 +124,48 @@ class GpuMatrixBase : public BinaryMatrix {
         return std::vector<bool>(tmp.begin(), tmp.end());
     }
 
-    // The matrix streams it was loaded from are kept on the host so that serialize() reproduces them
-    // byte for byte (the device image is a different, query-oriented layout).
+    // serialize() reproduces the stream the matrix was loaded from byte for byte (the device image is a different,
+    // query-oriented layout).  By default load() keeps a host copy of that stream; a caller that loads from a file
+    // can avoid the copy (a Kingsford-scale .brwt is ~10 GB): load_file(path), or keep_stream(false) +
+    // set_stream_path(path), re-read the file on demand.  With neither a copy nor a path serialize() THROWS — it
+    // never writes an empty or truncated matrix.
     void serialize(std::ostream &out) const override {
         if (!out.good()) throw std::ofstream::failure("Error when dumping the matrix");
-        out.write(stream_.data(), std::streamsize(stream_.size()));
+        if (have_stream_) { out.write(stream_.data(), std::streamsize(stream_.size())); return; }
+        if (stream_path_.empty())
+            throw std::ofstream::failure("ggq: serialize(): the matrix has neither a host copy of its stream nor a stream path");
+        std::ifstream in(stream_path_, std::ios::binary);
+        if (!in.good()) throw std::ofstream::failure("ggq: cannot read the serialized matrix at " + stream_path_);
+        in.seekg(std::streamoff(stream_offset_));
+        std::vector<char> buf(size_t(1) << 20);
+        uint64_t left = stream_bytes_;
+        while (left) {
+            in.read(buf.data(), std::streamsize(std::min<uint64_t>(left, buf.size())));
+            const std::streamsize got = in.gcount();
+            if (got <= 0) throw std::ofstream::failure("ggq: the serialized matrix at " + stream_path_ + " is shorter than when it was loaded");
+            out.write(buf.data(), got);
+            left -= uint64_t(got);
+        }
     }
+
+    // Do not keep a host copy of the stream read by the next load() (serialize() then needs set_stream_path()).
+    void keep_stream(bool keep) { keep_stream_ = keep; }
+    // Where serialize() re-reads the matrix from: `bytes` bytes at `offset` of `path` (e.g. behind the label encoder
+    // of a .brwt.annodbg, annotate_static.cpp:96-108).
+    void set_stream_path(const std::string &path, uint64_t offset, uint64_t bytes) {
+        stream_path_ = path; stream_offset_ = offset; stream_bytes_ = bytes;
+    }
+    // load() from a file holding only the matrix stream, without the host copy.
+    bool load_file(const std::string &path) {
+        std::ifstream in(path, std::ios::binary);
+        const bool keep = keep_stream_;
+        keep_stream_ = false;
+        const bool ok = in.good() && load(in);
+        keep_stream_ = keep;
+        if (ok) set_stream_path(path, 0, loaded_bytes_);
+        return ok;
+    }
+    uint64_t loaded_stream_bytes() const { return loaded_bytes_; }
 
     int device() const { return device_; }
     uint64_t device_bytes() const { return h_ ? ggq_device_bytes(h_.get()) : 0; }
@@ -140,13 +176,15 @@ class GpuMatrixBase : public BinaryMatrix {
 
     struct Tap {
         std::istream *in;
-        std::string *copy;
+        std::string *copy;   // null: count only
+        uint64_t bytes;
     };
     static size_t read_cb(void *ctx, void *dst, size_t n) {
         Tap *t = static_cast<Tap *>(ctx);
         t->in->read(static_cast<char *>(dst), std::streamsize(n));
         size_t got = size_t(t->in->gcount());
-        t->copy->append(static_cast<const char *>(dst), got);
+        if (t->copy) t->copy->append(static_cast<const char *>(dst), got);
+        t->bytes += got;
         return got;
     }
 
@@ -154,11 +192,14 @@ class GpuMatrixBase : public BinaryMatrix {
         if (!in.good()) return false;
         try {
             std::string bytes;
-            Tap tap{&in, &bytes};
+            Tap tap{&in, keep_stream_ ? &bytes : nullptr, 0};
             ggq_matrix *m = nullptr;
             if (fn(&read_cb, &tap, device_, &m) != GGQ_OK) return false;
             h_.reset(m, [](ggq_matrix *p) { ggq_free(p); });
             stream_.swap(bytes);
+            have_stream_ = keep_stream_;
+            loaded_bytes_ = tap.bytes;
+            stream_path_.clear();
             return true;
         } catch (...) {
             return false;
@@ -175,7 +216,10 @@ class GpuMatrixBase : public BinaryMatrix {
 
     int device_;
     std::shared_ptr<ggq_matrix> h_;   // copies share the immutable device image
-    std::string stream_;
+    std::string stream_;              // host copy of the loaded stream (have_stream_)
+    bool keep_stream_ = true, have_stream_ = false;
+    std::string stream_path_;         // else: where serialize() re-reads it from
+    uint64_t stream_offset_ = 0, stream_bytes_ = 0, loaded_bytes_ = 0;
 };
 
 class GpuBRWT final : public GpuMatrixBase {
@@ -190,24 +234,21 @@ class GpuBRWT final : public GpuMatrixBase {
     // the GPU-resident layout without parsing the stream again.  `stream_path` (optional) names the serialized
     // matrix the image was made from; it is read back only if serialize() is called.
     void save_image(const std::string &path) const { check(ggq_image_save(handle(), path.c_str())); }
+    // Without a stream_path serialize() throws (an image alone cannot reproduce the reference's stream).
     bool load_image(const std::string &path, const std::string &stream_path = std::string()) {
         ggq_matrix *m = nullptr;
         if (ggq_image_load(path.c_str(), device_, &m) != GGQ_OK) return false;
         h_.reset(m, [](ggq_matrix *p) { ggq_free(p); });
         stream_.clear();
-        stream_path_ = stream_path;
+        have_stream_ = false;
+        stream_path_.clear();
+        if (!stream_path.empty()) {
+            std::ifstream in(stream_path, std::ios::binary | std::ios::ate);
+            if (!in.good()) return false;
+            set_stream_path(stream_path, 0, uint64_t(in.tellg()));
+        }
         return true;
     }
-    void serialize(std::ostream &out) const override {
-        if (!stream_.empty() || stream_path_.empty()) { GpuMatrixBase::serialize(out); return; }
-        if (!out.good()) throw std::ofstream::failure("Error when dumping the matrix");
-        std::ifstream in(stream_path_, std::ios::binary);
-        if (!in.good()) throw std::ofstream::failure("ggq: cannot read the serialized matrix behind the image");
-        out << in.rdbuf();
-    }
-
-  private:
-    std::string stream_path_;
 };
 
 class GpuColMajor final : public GpuMatrixBase {

@@ -43,16 +43,17 @@ def host_bits(g, n_bits, thr, seed):
     return words
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--log2-bits", type=int, default=32)
-    ap.add_argument("--log2-queries", type=int, default=26)
-    ap.add_argument("--log2-cpu-bits", type=int, default=28)
-    ap.add_argument("--kinds", default="stat,sd,rrr")
-    ap.add_argument("--densities", default="0.001,0.01,0.1,0.5")
-    ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--out", default=None)
-    a = ap.parse_args()
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def measure(kinds, densities, log2_bits=32, log2_queries=26, log2_cpu_bits=28, cpu=True, emit=None):
+    """One record per (kind, density).  GPU: 2^log2_queries random queries on a 2^log2_bits-bit vector, CUDA events on
+    the launch stream, 3 warm-ups, median of 5.  CPU + parity: the unmodified reference on the 2^log2_cpu_bits-bit
+    prefix of the same generator, all host threads, 2^20 sampled answers compared."""
     import torch
     import genome_graph_annotation_b200 as g
     if not torch.cuda.is_available():
@@ -62,17 +63,20 @@ def main():
     except Exception:
         peak = 6650.0
     R = None
-    if not a.no_cpu:
+    threads = host_threads()
+    if cpu:
+        os.environ["OMP_NUM_THREADS"] = str(threads)   # torchrun exports 1; set before libgomp loads
         from oracle import ref_binding as R  # checker / baseline only
         if not R.available():
             R = None
-    n, Q, nc = 1 << a.log2_bits, 1 << a.log2_queries, 1 << a.log2_cpu_bits
+    n, Q, nc = 1 << log2_bits, 1 << log2_queries, 1 << log2_cpu_bits
+    l2_bytes = 126e6
     gen = torch.Generator(device="cuda")
     results = []
-    for d in [float(x) for x in a.densities.split(",")]:
+    for d in densities:
         thr = g.density_threshold(d)
         cw = host_bits(g, nc, thr, SEED) if R is not None else None
-        for kind in a.kinds.split(","):
+        for kind in kinds:
             t0 = time.time()
             v = g.GpuBitVector.synthesize(kind, n, d, seed=SEED)
             torch.cuda.synchronize()
@@ -80,7 +84,10 @@ def main():
             ones = int(v.num_set_bits)
             rec = {"config": "C3", "kind": kind, "density": d, "n_bits": n, "ones": ones, "queries": Q,
                    "device_bytes": int(v.device_bytes), "bits_per_bit": 8.0 * v.device_bytes / n, "build_s": build_s,
-                   "inverted": bool(v.is_inverted), "ops": {}}
+                   "inverted": bool(v.is_inverted),
+                   "residency": "L2-resident structure (smaller than the 126 MB L2): not an HBM figure"
+                                if v.device_bytes < l2_bytes else "HBM (structure larger than L2)",
+                   "ops": {}}
             gen.manual_seed(SEED)
             pos = torch.randint(0, n, (Q,), device="cuda", dtype=torch.int64, generator=gen)
             rk = torch.randint(1, max(ones, 1) + 1, (Q,), device="cuda", dtype=torch.int64, generator=gen)
@@ -105,6 +112,7 @@ def main():
                 ms = float(np.median(ts))
                 gbs = ALG_BYTES[kind][op] * Q / (ms / 1e3) / 1e9
                 rec["ops"][op] = {"ms": ms, "ms_best": float(min(ts)), "ops_per_s": Q / (ms / 1e3),
+                                  "algorithmic_bytes_per_op": ALG_BYTES[kind][op],
                                   "algorithmic_gb_s": gbs, "frac_of_measured_hbm_peak": gbs / peak}
             v.close()
             # parity + CPU baseline on the n' prefix (same generator => same bits)
@@ -115,7 +123,6 @@ def main():
                 qp = rng.integers(0, nc, 1 << 20).astype(np.uint64)
                 so = int(vs.num_set_bits)
                 qr = rng.integers(1, max(so, 1) + 1, 1 << 20).astype(np.uint64)
-                threads = R.max_threads()
                 par = {}
                 for op, q in (("get", qp), ("rank1", qp), ("select1", qr)):
                     if op == "select1" and so == 0:
@@ -128,8 +135,24 @@ def main():
                 rec["cpu"] = {"threads": threads, "n_bits": nc, "kind": "reference (oracle/_ref, unmodified sdsl-backed " + kind + ")"}
                 vs.close()
                 del rv
-            print(json.dumps(rec), flush=True)
+            if emit is not None:
+                emit(rec)
             results.append(rec)
+    return peak, results
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--log2-bits", type=int, default=32)
+    ap.add_argument("--log2-queries", type=int, default=26)
+    ap.add_argument("--log2-cpu-bits", type=int, default=28)
+    ap.add_argument("--kinds", default="stat,sd,rrr")
+    ap.add_argument("--densities", default="0.001,0.01,0.1,0.5")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    peak, results = measure(a.kinds.split(","), [float(x) for x in a.densities.split(",")], a.log2_bits, a.log2_queries,
+                            a.log2_cpu_bits, cpu=not a.no_cpu, emit=lambda rec: print(json.dumps(rec), flush=True))
     if a.out:
         json.dump({"peak_hbm_gbs": peak, "results": results}, open(a.out, "w"), indent=1)
 

@@ -122,6 +122,21 @@ static void check_brwt(Columns &&cols, int arity, bool relax) {
     REQUIRE(restored.num_nodes() == ref.num_nodes());
     compare(ref, restored, stream);
     REQUIRE(!restored.load_image(ser));   // not an image
+    // an image alone cannot reproduce the reference's stream: serialize() must throw, never write a truncated matrix
+    ggq::GpuBRWT image_only;
+    REQUIRE(image_only.load_image(img));
+    REQUIRE(image_only.get_column(0) == ref.get_column(0));
+    bool threw = false;
+    std::ostringstream sink;
+    try { image_only.serialize(sink); } catch (const std::ios_base::failure &) { threw = true; }
+    REQUIRE(threw && sink.str().empty());
+    // load_file(): no host copy of the stream; serialize() re-reads the file
+    ggq::GpuBRWT from_file;
+    REQUIRE(from_file.load_file(ser));
+    REQUIRE(from_file.loaded_stream_bytes() == stream.size());
+    std::ostringstream again;
+    from_file.serialize(again);
+    REQUIRE(again.str() == stream);
     std::remove(img.c_str());
     std::remove(ser.c_str());
 }

@@ -201,3 +201,27 @@ def test_config2_uniform_rows_multi_brwt(ggq, ref):
             assert np.array_equal(gm.get_column(int(c)), rm.get_column(int(c)))
     finally:
         gm.close()
+
+
+@pytest.mark.parametrize("rb", [4, 8, 16])
+@pytest.mark.parametrize("m,relax,seed", [(825, 8, 1), (422, 5, 2), (1500, 3, 3)])
+def test_irregular_trees_random_row_densities(ggq, ref, m, relax, seed, rb):
+    """Irregular Multi-BRWT shapes (greedy pairing + relax: arities 2..relax, leaves at different depths) queried with
+    rows whose densities differ wildly (empty .. nearly full): the shape that can stack higher in the descent kernel
+    than the host's replay predicts.  Every row against the unmodified reference, for 4 / 8 / 16 rows per warp tile."""
+    n = 1500
+    rng = np.random.default_rng(seed)
+    row_d = rng.choice([0.0, 0.002, 0.02, 0.2, 0.6, 0.97], size=n)
+    col_d = rng.choice([0.2, 1.0, 1.0, 1.5], size=m)
+    dense = (rng.random((n, m)) < np.minimum(1.0, row_d[:, None] * col_d[None, :])).astype(np.uint8)
+    rm = build_ref(ref, dense, arity=2, greedy=True, relax=relax, threads=8)
+    gm = ggq.GpuMatrix.load_brwt(rm.serialize())
+    try:
+        gm.set_option("rows_per_warp", rb)
+        rows = rng.integers(0, n, 20_000).astype(np.uint64)
+        eoff, ecols, _ = rm.get_rows(rows, threads=8)
+        off, cols = gm.get_rows_csr(rows)
+        assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
+        assert np.array_equal(gm.count_labels(rows), np.bincount(ecols.astype(np.int64), minlength=m).astype(np.uint64))
+    finally:
+        gm.close()

@@ -277,3 +277,42 @@ def test_flat_emit_gives_the_same_rows(ggq, n, m, d, arity, monkeypatch):
         assert np.array_equal(gf.count_labels(rows), np.bincount(base[1].astype(np.int64), minlength=m).astype(np.uint64))
     finally:
         gf.close()
+
+
+def test_underestimated_stack_reruns_with_the_provable_capacity(ggq, orc, monkeypatch):
+    """The shared stack capacity of the descent kernel comes from a host replay of its pop/push policy, which is an
+    estimate (round-1 advisor: sparse rows of irregular trees can stack higher than the all-ones row).  The kernel
+    never writes past the capacity: it raises a flag, the engine switches the matrix to the spill instantiation with
+    rows-per-tile x leaf-groups capacity and reruns the batch.  GGQ_STACK_UNDERESTIMATE forces that path."""
+    n, m, d = 20_000, 400, 0.35
+    thr = ggq.density_threshold(d)
+    rows = np.random.default_rng(4).integers(0, n, 30_000).astype(np.uint64)
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=5, arity=4)
+    base = gm.get_rows_csr(rows)
+    gm.close()
+    monkeypatch.setenv("GGQ_STACK_UNDERESTIMATE", "12")
+    for first in ("small", "large", "labels", "pipelined"):
+        gs = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=5, arity=4)
+        try:
+            if first == "small":     # small-batch path notices the flag and falls back to the general path
+                off, cols = gs.get_rows_csr(rows[:40])
+                assert np.array_equal(off, base[0][:41]) and np.array_equal(cols, base[1][:int(base[0][40])])
+            elif first == "labels":
+                lc, lv = gs.get_labels(rows[:300], 0.0)
+                exp = np.bincount(base[1][:int(base[0][300])].astype(np.int64), minlength=m)
+                assert np.array_equal(lc, np.nonzero(exp)[0].astype(np.uint64)) and np.array_equal(lv, exp[exp != 0].astype(np.uint64))
+            elif first == "pipelined":
+                big = np.tile(rows, 80)   # 2.4e6 rows: several chunks in flight when the first one raises the flag
+                off = np.zeros(big.size + 1, np.uint64)
+                cols = np.zeros(int(base[0][-1]) * 80 + 16, np.uint64)
+                tot = gs.get_rows_into(big, off, cols)
+                assert tot == int(base[0][-1]) * 80
+                assert np.array_equal(np.diff(off.astype(np.int64)), np.tile(np.diff(base[0].astype(np.int64)), 80))
+                assert np.array_equal(cols[:tot], np.tile(base[1], 80))
+            off, cols = gs.get_rows_csr(rows)
+            assert np.array_equal(off, base[0]) and np.array_equal(cols, base[1])
+            assert np.array_equal(gs.count_labels(rows), np.bincount(base[1].astype(np.int64), minlength=m).astype(np.uint64))
+        finally:
+            gs.close()
+    for t in range(0, rows.size, 997):
+        assert np.array_equal(base[1][base[0][t]:base[0][t + 1]], orc.synth_row(m, thr, 5, int(rows[t])))
