@@ -360,6 +360,18 @@ def run_ours(args):
     def device_step(i):
         return ws.get_rows_device(batches[i % n_pool].data_ptr(), B, 8)
 
+    # ---- the reference algorithm's work on these batches: V_t = (node, row) touches of BRWT::get_row,
+    # counted by the plain descent (leaf codes off; they skip most of the touches the reference performs).  Untimed.
+    codes = gm.leaf_codes
+    touch_of, plain_ms = {}, []
+    if codes["in_use"]:
+        gm.set_option("leaf_codes", 0)
+        for b in range(n_pool):
+            device_step(b)
+            touch_of[b] = int(ws.stat("touches"))
+            plain_ms.append(ws.stat("kernel_ms"))
+        gm.set_option("leaf_codes", 1)
+
     # ---- device-resident number ----------------------------------------------------------
     clocks = ClockSampler(local)
     clocks.start()
@@ -368,14 +380,16 @@ def run_ours(args):
     barrier()
     clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kern_ms, touches, probes, ids, launches = [], 0, 0, 0, 0
+    kern_ms, touches, probes, ids, launches, code_probes, code_esc = [], 0, 0, 0, 0, 0, 0
     with torch.cuda.stream(stream):
         e0.record()
     for i in range(K):
         _, _, total = device_step(W + i)
         kern_ms.append(ws.stat("kernel_ms"))
-        touches += int(ws.stat("touches"))
+        touches += touch_of.get((W + i) % n_pool, int(ws.stat("touches")))
         probes += int(ws.stat("probes"))
+        code_probes += int(ws.stat("code_probes"))
+        code_esc += int(ws.stat("code_escapes"))
         launches += int(ws.stat("launches"))
         ids += total
     with torch.cuda.stream(stream):
@@ -498,7 +512,8 @@ def run_ours(args):
     peak, peak_src = peaks()
     k_ms = float(np.mean(kern_ms))
     alg_bytes = (16.0 * B * K + 8.0 * ids + 32.0 * touches) / K
-    layout_bytes = (8.0 * B * K + 4.0 * ids + 64.0 * probes) / K   # what this layout must move: 64-B sibling blocks
+    # what this layout must move: 64-byte sibling blocks + one 32-byte sector per 1-byte leaf-code probe
+    layout_bytes = (8.0 * B * K + 4.0 * ids + 64.0 * probes + 32.0 * code_probes) / K
     achieved = alg_bytes / (k_ms / 1e3) / 1e9
     roof = {"bound": "hbm", "kernel": "brwt_rows_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "kernel_ms": k_ms,
@@ -506,7 +521,13 @@ def run_ours(args):
             "bytes_per_row": alg_bytes / B, "node_touches_per_row": touches / (B * K),
             "layout_bytes_per_launch": layout_bytes, "layout_achieved": layout_bytes / (k_ms / 1e3) / 1e9,
             "layout_frac": layout_bytes / (k_ms / 1e3) / 1e9 / peak,
-            "kernel_share_of_step": k_ms / ms_step}
+            "kernel_share_of_step": k_ms / ms_step,
+            "probes_per_row": probes / (B * K), "leaf_code_probes_per_row": code_probes / (B * K),
+            "leaf_code_escapes_per_row": code_esc / (B * K),
+            "touches_note": "node_touches_per_row is V_t of the reference algorithm (SURVEY.md 8d), counted by the plain "
+                            "descent on the same batches; the coded descent performs fewer"}
+    if plain_ms:
+        roof["plain_descent_kernel_ms"] = float(np.mean(plain_ms))
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:
@@ -518,7 +539,7 @@ def run_ours(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic", "config": workload_config(args, world),
             "clocks": clk, "roofline": roof, "gpu_launches": launches,
-            "build_seconds": build_s, "device_image_gb": gm.device_bytes / 1e9,
+            "build_seconds": build_s, "device_image_gb": gm.device_bytes / 1e9, "leaf_codes": codes,
             "column_ids_per_row": ids / (B * K)}
     line["spot_check"] = spot
     if extra is not None:

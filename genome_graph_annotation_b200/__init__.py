@@ -74,6 +74,7 @@ def lib():
         "ggq_num_nodes": (C.c_uint64, [vp]),
         "ggq_total_column_size": (C.c_uint64, [vp]),
         "ggq_device_bytes": (C.c_uint64, [vp]),
+        "ggq_leaf_code_info": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "ggq_last_probe_count": (C.c_uint64, [vp]),
         "ggq_set_option": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
         "ggq_get_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(vp)]),
@@ -116,6 +117,13 @@ def lib():
         "ggq_bv_rank1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
         "ggq_bv_select1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
         "ggq_bv_get_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_bv_rank0": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
+        "ggq_bv_select0": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
+        "ggq_bv_rank0_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_bv_select0_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_bv_get_int": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint32, u64p]),
+        "ggq_bv_to_words": (C.c_int, [vp, u64p]),
+        "ggq_bv_call_ones_into": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -317,6 +325,13 @@ class GpuMatrix:
     num_nodes = property(lambda s: lib().ggq_num_nodes(s._h))
     total_column_size = property(lambda s: lib().ggq_total_column_size(s._h))
     device_bytes = property(lambda s: lib().ggq_device_bytes(s._h))
+
+    @property
+    def leaf_codes(self):
+        """Leaf codes of a BRWT image: dict(nodes, bytes, escape_rate, in_use)."""
+        w = (C.c_uint64 * 4)()
+        _check(lib().ggq_leaf_code_info(self._h, w))
+        return {"nodes": int(w[0]), "bytes": int(w[1]), "escape_rate": w[2] / 1e6, "in_use": bool(w[3])}
     last_probe_count = property(lambda s: lib().ggq_last_probe_count(s._h))
 
     def set_option(self, name, value):
@@ -471,7 +486,8 @@ class Workspace:
     def stat(self, what):
         """what: 'kernel_ms' | 'probes' | 'touches' | 'launches' of the last query on this workspace."""
         return lib().ggq_workspace_stat(self._h, {"kernel_ms": 0, "probes": 1, "touches": 2, "launches": 3,
-                                                  "exchange_ms": 4, "exchange_bytes": 5}[what])
+                                                  "exchange_ms": 4, "exchange_bytes": 5, "code_probes": 6,
+                                                  "code_escapes": 7}[what])
 
     def get_rows_device(self, d_rows_ptr, n, col_bytes=4):
         """d_rows_ptr: device pointer (int).  -> (d_offsets_ptr, d_cols_ptr, n_cols), owned by the workspace."""
@@ -590,6 +606,35 @@ class GpuBitVector:
         out = np.empty(q.size, dtype=np.uint8)
         _check(lib().ggq_bv_get(self._h, qp, q.size, out.ctypes.data_as(u8p)))
         return out
+
+    def rank0(self, q):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        _check(lib().ggq_bv_rank0(self._h, qp, q.size, out.ctypes.data_as(u64p)))
+        return out
+
+    def select0(self, q):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        _check(lib().ggq_bv_select0(self._h, qp, q.size, out.ctypes.data_as(u64p)))
+        return out
+
+    def get_int(self, q, width):
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        _check(lib().ggq_bv_get_int(self._h, qp, q.size, width, out.ctypes.data_as(u64p)))
+        return out
+
+    def to_words(self):
+        out = np.zeros(max((self.size + 63) // 64, 1), dtype=np.uint64)
+        _check(lib().ggq_bv_to_words(self._h, out.ctypes.data_as(u64p)))
+        return out[:(self.size + 63) // 64]
+
+    def call_ones(self):
+        n = C.c_uint64()
+        out = np.empty(max(int(self.num_set_bits), 1), dtype=np.uint64)
+        _check(lib().ggq_bv_call_ones_into(self._h, out.ctypes.data_as(u64p), out.size, C.byref(n)))
+        return out[:n.value]
 
     def rank1_device(self, d_q, n, d_out, stream=0):
         _check(lib().ggq_bv_rank1_device(self._h, d_q, n, d_out, stream))

@@ -252,6 +252,7 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     m->sel.alloc(1);
     m->finalize_arena(t, false);
     m->refresh_img();
+    m->build_leaf_codes();
     m->derive_stats();
     return m.release();
 }

@@ -3,7 +3,7 @@
 
 namespace ggq {
 
-enum BvOp { OP_RANK1 = 0, OP_SELECT1 = 1, OP_GET = 2 };
+enum BvOp { OP_RANK1 = 0, OP_SELECT1 = 1, OP_GET = 2, OP_RANK0 = 3, OP_SELECT0 = 4, OP_GETINT = 5, OP_WORDS = 6 };
 
 struct BvImg {
     int kind;
@@ -52,6 +52,70 @@ __global__ void __launch_bounds__(256) bv_query_kernel(BvImg v, const u64 *q, u6
         }
         out[t] = OutT(res);
     }
+}
+
+// The rest of the reference's bit_vector interface, by composition of rank1 / operator[] (none of it is on the row
+// query path; the reference composes them the same way):
+//   rank0(id)  = min(id + 1, size) - rank1(id)                                  (common/bit_vector.cpp:32-34)
+//   select0(k) = smallest i with rank0(i) = k, k in [1, size - num_set_bits]     (bit_vector_rrr::select0, bit_vector.hpp:199;
+//                by bisection over rank1 — every kind answers it, the reference offers it on rrr only)
+//   get_int(id, width) = bits [id, id + width) as an integer, width <= 64        (bit_vector.hpp:25)
+//   words      = the plain bits, 64 per thread (to_vector / the sdsl::bit_vector copy, bit_vector.cpp:36-46)
+template <int KIND>
+__device__ __forceinline__ u64 bv_rank1_incl(const BvImg &v, const RrrTables &T, u64 i, bool *bit) {   // i < n_bits
+    if (KIND == GGQ_BV_STAT) { u64 r = rb_rank_excl_bit(v.stat, i, bit); return r + *bit; }
+    if (KIND == GGQ_BV_SD) { *bit = sd_get(v.sd, i); return sd_rank1(v.sd, i); }
+    return rrr_rank_incl_bit(v.rrr, T, i, bit);
+}
+
+template <int KIND, int OP>
+__global__ void __launch_bounds__(256) bv_aux_kernel(BvImg v, const u64 *q, const u32 *widths, u32 width, u64 n, u64 *out) {
+    __shared__ RrrTables T;
+    if (KIND == GGQ_BV_RRR) {
+        const u64 *src = reinterpret_cast<const u64 *>(&g_rrr_tables);
+        u64 *dst = reinterpret_cast<u64 *>(&T);
+        for (u32 i = threadIdx.x; i < sizeof(RrrTables) / 8; i += blockDim.x) dst[i] = src[i];
+        __syncthreads();
+    }
+    for (u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += u64(gridDim.x) * blockDim.x) {
+        bool bit;
+        u64 res = 0;
+        if (OP == OP_RANK0) {
+            const u64 x = q[t];
+            if (v.n_bits) {
+                const u64 i = x < v.n_bits ? x : v.n_bits - 1;
+                res = i + 1 - bv_rank1_incl<KIND>(v, T, i, &bit);
+            }
+        } else if (OP == OP_SELECT0) {
+            const u64 k = q[t];
+            res = v.n_bits;   // outside [1, zeros]: undefined in the reference (assert only)
+            if (k >= 1 && k <= v.n_bits - v.n_ones) {
+                u64 lo = 0, hi = v.n_bits - 1;   // smallest i with rank0(i) >= k
+                while (lo < hi) {
+                    const u64 mid = lo + ((hi - lo) >> 1);
+                    if (mid + 1 - bv_rank1_incl<KIND>(v, T, mid, &bit) >= k) hi = mid; else lo = mid + 1;
+                }
+                res = lo;
+            }
+        } else if (OP == OP_GETINT) {
+            const u64 x = q[t];
+            const u32 w = widths ? widths[t] : width;
+            for (u32 j = 0; j < w && j < 64 && x + j < v.n_bits; ++j) {
+                bv_rank1_incl<KIND>(v, T, x + j, &bit);
+                res |= u64(bit) << j;
+            }
+        } else {   // OP_WORDS: word t of the plain bits
+            for (u32 j = 0; j < 64 && t * 64 + j < v.n_bits; ++j) {
+                bv_rank1_incl<KIND>(v, T, t * 64 + j, &bit);
+                res |= u64(bit) << j;
+            }
+        }
+        out[t] = res;
+    }
+}
+
+__global__ void iota1_kernel(u64 *p, u64 n) {
+    for (u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += u64(gridDim.x) * blockDim.x) p[t] = t + 1;
 }
 
 // bit_vector_stat fast paths (config C3).  The generic kernel reads the whole 64-byte block from one thread
@@ -184,6 +248,7 @@ struct BitVec {
     cudaStream_t stream = nullptr;
     DeviceBuf<u64> d_q, d_out;
     std::mutex mu;
+    mutable u32 aux_width = 64;   // get_int width of the next OP_GETINT launch (set under `mu` / by the device call)
 
     ~BitVec() { if (stream) cudaStreamDestroy(stream); }
 
@@ -209,6 +274,15 @@ struct BitVec {
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         u32 grid = u32(std::min<u64>((n + 255) / 256, u64(sms) * (KIND == GGQ_BV_RRR ? 6 : 8) * 4));
         if (!grid) return;
+        if (op >= OP_RANK0) {
+            u64 *o = static_cast<u64 *>(out);
+            if (op == OP_RANK0) bv_aux_kernel<KIND, OP_RANK0><<<grid, 256, 0, st>>>(img, q, nullptr, 0, n, o);
+            else if (op == OP_SELECT0) bv_aux_kernel<KIND, OP_SELECT0><<<grid, 256, 0, st>>>(img, q, nullptr, 0, n, o);
+            else if (op == OP_GETINT) bv_aux_kernel<KIND, OP_GETINT><<<grid, 256, 0, st>>>(img, q, nullptr, aux_width, n, o);
+            else bv_aux_kernel<KIND, OP_WORDS><<<grid, 256, 0, st>>>(img, nullptr, nullptr, 0, n, o);
+            CUDA_CHECK(cudaGetLastError());
+            return;
+        }
         if (KIND == GGQ_BV_STAT && op == OP_GET) {
             stat_get_kernel<<<grid, 256, 0, st>>>(img.stat, q, n, static_cast<unsigned char *>(out));
         } else if (KIND == GGQ_BV_STAT && op == OP_RANK1) {
@@ -230,12 +304,25 @@ struct BitVec {
         else launch_kind<GGQ_BV_RRR>(op, q, n, out, st);
     }
 
-    void query_host(int op, const u64 *q, u64 n, void *out) {
-        if (!n) return;
+    // positions of the set bits, ascending (call_ones / the sparse branch of bit_vector_*::call_ones): select1(1..n_ones)
+    void ones_host(u64 *out) {
+        if (!n_ones) return;
         std::lock_guard<std::mutex> lk(mu);
         CUDA_CHECK(cudaSetDevice(device));
+        if (d_q.n < n_ones) { d_q.alloc(n_ones); d_out.alloc(n_ones); }
+        iota1_kernel<<<u32(std::min<u64>((n_ones + 255) / 256, 4096)), 256, 0, stream>>>(d_q.p, n_ones);
+        launch(OP_SELECT1, d_q.p, n_ones, d_out.p, stream);
+        CUDA_CHECK(cudaMemcpyAsync(out, d_out.p, n_ones * 8, cudaMemcpyDeviceToHost, stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
+
+    void query_host(int op, const u64 *q, u64 n, void *out, u32 width = 64) {
+        if (!n) return;
+        std::lock_guard<std::mutex> lk(mu);
+        aux_width = width;
+        CUDA_CHECK(cudaSetDevice(device));
         if (d_q.n < n) { d_q.alloc(n); d_out.alloc(n); }
-        CUDA_CHECK(cudaMemcpyAsync(d_q.p, q, n * 8, cudaMemcpyHostToDevice, stream));
+        if (q) CUDA_CHECK(cudaMemcpyAsync(d_q.p, q, n * 8, cudaMemcpyHostToDevice, stream));
         launch(op, d_q.p, n, d_out.p, stream);
         CUDA_CHECK(cudaMemcpyAsync(out, d_out.p, op == OP_GET ? n : n * 8, cudaMemcpyDeviceToHost, stream));
         CUDA_CHECK(cudaStreamSynchronize(stream));
@@ -335,6 +422,31 @@ static int bv_host(const ggq_bv *v, int op, const uint64_t *q, uint64_t n, void 
 int ggq_bv_rank1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_RANK1, q, n, out); }
 int ggq_bv_select1(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_SELECT1, q, n, out); }
 int ggq_bv_get(const ggq_bv *v, const uint64_t *q, uint64_t n, uint8_t *out) { return bv_host(v, OP_GET, q, n, out); }
+int ggq_bv_rank0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_RANK0, q, n, out); }
+int ggq_bv_select0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out) { return bv_host(v, OP_SELECT0, q, n, out); }
+int ggq_bv_get_int(const ggq_bv *v, const uint64_t *q, uint64_t n, uint32_t width, uint64_t *out) {
+    GGQ_TRY
+    if (!v || (!q && n) || (!out && n) || width < 1 || width > 64) return fail(GGQ_ERR_ARG, "bad argument");
+    const_cast<ggq_bv *>(v)->query_host(OP_GETINT, reinterpret_cast<const u64 *>(q), n, out, width);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+int ggq_bv_to_words(const ggq_bv *v, uint64_t *words) {
+    GGQ_TRY
+    if (!v || (!words && v->n_bits)) return fail(GGQ_ERR_ARG, "bad argument");
+    const_cast<ggq_bv *>(v)->query_host(OP_WORDS, nullptr, (v->n_bits + 63) / 64, words);
+    return GGQ_OK;
+    GGQ_CATCH
+}
+int ggq_bv_call_ones_into(const ggq_bv *v, uint64_t *positions, uint64_t capacity, uint64_t *n_ones) {
+    GGQ_TRY
+    if (!v || !n_ones) return fail(GGQ_ERR_ARG, "bad argument");
+    *n_ones = v->n_ones;
+    if (capacity < v->n_ones || (!positions && v->n_ones)) return fail(GGQ_ERR_ARG, "capacity too small");
+    const_cast<ggq_bv *>(v)->ones_host(reinterpret_cast<u64 *>(positions));
+    return GGQ_OK;
+    GGQ_CATCH
+}
 
 static int bv_dev(const ggq_bv *v, int op, const uint64_t *d_q, uint64_t n, void *d_out, void *stream) {
     GGQ_TRY
@@ -347,5 +459,7 @@ static int bv_dev(const ggq_bv *v, int op, const uint64_t *d_q, uint64_t n, void
 int ggq_bv_rank1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_RANK1, d_q, n, d_out, stream); }
 int ggq_bv_select1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_SELECT1, d_q, n, d_out, stream); }
 int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t *d_out, void *stream) { return bv_dev(v, OP_GET, d_q, n, d_out, stream); }
+int ggq_bv_rank0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_RANK0, d_q, n, d_out, stream); }
+int ggq_bv_select0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_SELECT0, d_q, n, d_out, stream); }
 
 }  // extern "C"

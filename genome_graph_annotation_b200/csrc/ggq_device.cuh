@@ -27,6 +27,8 @@ struct Img {
     const u32 *leaf_col;
     const u32 *col_path_off;
     const u32 *col_path;
+    const unsigned char *codes;   // leaf codes of all coded lanes (ggq_rows.cuh), null if none
+    const uint4 *code_rec;        // [g*4 + lane] = { codes offset lo, hi, DFS rank of the subtree's first leaf, leaves }
     u64 n_rows;
     u32 n_cols;
     u32 n_groups;

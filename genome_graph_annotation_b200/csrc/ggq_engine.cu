@@ -122,18 +122,25 @@ void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
     CUDA_CHECK(cudaDeviceSynchronize());
 }
 
-void Matrix::upload_tables(const FlatTree &t) {
-    upload_vec(group_hot, t.group_hot);
-    upload_vec(group_nblocks, t.group_nblocks);
+// Group records of the descent kernel (ggq_rows.cuh: load_rec), with the leaf-code marks of the coded lanes when
+// leaf codes are in use.
+void Matrix::upload_records(const FlatTree &t) {
+    const bool codes_on = use_codes && !t.lane_coded.empty();
+    auto is_coded = [&](u32 li) { return codes_on && t.lane_coded[li] != 0; };
     {
         std::vector<uint4> rec(size_t(t.n_groups()) * 2);
         for (u32 g = 0; g < t.n_groups(); ++g)
-            for (u32 h = 0; h < 2; ++h)
-                rec[2 * g + h] = make_uint4(u32(t.group_hot[g]), u32(t.group_hot[g] >> 32), t.lane_info[4 * g + 2 * h],
-                                            t.lane_info[4 * g + 2 * h + 1]);
+            for (u32 h = 0; h < 2; ++h) {
+                u32 c[2];
+                for (u32 k = 0; k < 2; ++k) {
+                    const u32 li = 4 * g + 2 * h + k;
+                    c[k] = t.lane_info[li] | (is_coded(li) ? kCodedFlag : 0u);   // (coded lanes are internal: bit 31 clear)
+                }
+                rec[2 * g + h] = make_uint4(u32(t.group_hot[g]), u32(t.group_hot[g] >> 32), c[0], c[1]);
+            }
         upload_vec(group_rec, rec);
     }
-    {   // compact 16-byte records: 21-bit children (leaf bit 20), base in units of 4 slots
+    {   // compact 16-byte records: 21-bit children (leaf bit 20), base in units of 4 slots, coded mask in y[28..31]
         compact_rec = t.leaf_col.size() < (1u << 20) - 1 && t.n_groups() < (1u << 20) && !std::getenv("GGQ_WIDE_REC");
         std::vector<uint4> rec16(compact_rec ? size_t(t.n_groups()) : 0);
         for (u32 g = 0; compact_rec && g < t.n_groups(); ++g) {
@@ -141,19 +148,27 @@ void Matrix::upload_tables(const FlatTree &t) {
             const u64 base = hot & kGhBaseMask;
             if ((base & 3) || (base >> 2) > 0xFFFFFFFFull) { compact_rec = false; break; }
             u32 c[4] = {0, 0, 0, 0};
+            u32 cmask = 0;
             for (u32 k = 0; k < 4; ++k) {
                 const u32 info = t.lane_info[4 * g + k];
                 if (info == kRemoteLane) c[k] = (1u << 21) - 1u;
                 else if (info & kLeafFlag) c[k] = (1u << 20) | (info & ~kLeafFlag);
                 else c[k] = info;
                 if (info != kRemoteLane && (info & ~kLeafFlag) >= (1u << 20) - 1) { compact_rec = false; break; }
+                if (is_coded(4 * g + k)) cmask |= 1u << k;
             }
             const u32 flags = u32(hot >> kGhStrideShift) & 0x7fu;
-            rec16[g] = make_uint4(u32(base >> 2), flags | (c[0] << 7), c[1] | (c[2] << 21), (c[2] >> 11) | (c[3] << 10));
+            rec16[g] = make_uint4(u32(base >> 2), flags | (c[0] << 7) | (cmask << 28), c[1] | (c[2] << 21), (c[2] >> 11) | (c[3] << 10));
         }
         if (compact_rec) upload_vec(group_rec16, rec16);
         else group_rec16.release();
     }
+}
+
+void Matrix::upload_tables(const FlatTree &t) {
+    upload_vec(group_hot, t.group_hot);
+    upload_vec(group_nblocks, t.group_nblocks);
+    upload_records(t);
     upload_vec(lane_info, t.lane_info);
     upload_vec(lane_aux, t.lane_aux);
     upload_vec(lane_sb_off, t.lane_sb_off);
@@ -183,6 +198,8 @@ void Matrix::refresh_img() {
     img.leaf_col = leaf_col.p;
     img.col_path_off = col_path_off.p;
     img.col_path = col_path.p;
+    img.codes = codes.p;
+    img.code_rec = code_rec.p;
     img.n_rows = tree.n_rows;
     img.n_cols = u32(tree.n_cols);
     img.n_groups = tree.n_groups();
@@ -190,11 +207,7 @@ void Matrix::refresh_img() {
 }
 
 // The instantiation of K1 for a tree: stack spill to global memory, leaves holding several columns.
-static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact, bool emit_flat = false) {
-    if (emit_flat && !spill) {   // experimental emit (GGQ_EMIT_FLAT=1), see ggq_rows.cuh
-        if (compact) return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true, true> : (const void *)brwt_rows_kernel<false, false, true, true>;
-        return multi_leaf ? (const void *)brwt_rows_kernel<false, true, false, true> : (const void *)brwt_rows_kernel<false, false, false, true>;
-    }
+static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact) {
     if (compact) {
         if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, true> : (const void *)brwt_rows_kernel<true, false, true>;
         return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true> : (const void *)brwt_rows_kernel<false, false, true>;
@@ -231,10 +244,8 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
         rb >>= 1;
     }
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
-    // flat emit needs 16-byte aligned per-warp bitmaps and no stack spill
-    emit_flat = env_u32("GGQ_EMIT_FLAT", 0) != 0 && cap_spill == 0 && (size_t(rb) * bm_words) % 4 == 0;
     int per_sm = 0;
-    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec, emit_flat);
+    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec);
     CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
     CUDA_CHECK(cudaFuncSetAttribute(rows_kernel_fn(true, tree.multi_column_leaves != 0, compact_rec),
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));   // the safe fallback below
@@ -314,8 +325,131 @@ void Matrix::derive_stats() {
         }
     }
     configure_rows(0, ~0u);
-    device_bytes = slots.bytes() + sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
+    device_bytes = slots.bytes() + codes.bytes() * (code_bytes != 0) + code_rec.bytes() * (code_bytes != 0) +
+                   sel.bytes() + sb_base.bytes() + group_hot.bytes() + group_nblocks.bytes() +
                    lane_info.bytes() * 3 + lane_sel_off.bytes() * 2 + leaf_col.bytes() + col_path.bytes() + col_path_off.bytes();
+}
+
+// Leaf codes (ggq_rows.cuh).  Which nodes get codes is decided here, top-down: a node Z qualifies
+// when its subtree has at most 255 single-column leaves and fewer than kCodeStack groups; its escape rate e(Z)
+// (positions with several labels below Z) is sampled on the device, and codes pay when they save probes:
+//   gain(Z) = C(Z) - (1 + e(Z) * C(Z)),  C(Z) = expected probes of the plain descent below Z per visit
+//           = sum over internal Y in subtree(Z) of ones(Y) * groups(Y) / ones(Z)      (uniformly random rows).
+// A node that does not pay hands the question to its children.  Accepted nodes are kept in order of gain while their
+// code bytes (ones(Z) each) fit the budget: GGQ_CODE_BUDGET_MB, default half the slot arena, never more than the
+// free device memory minus a reserve for workspaces.
+void Matrix::build_leaf_codes() {
+    tree.lane_coded.clear();
+    tree.code_rec.clear();
+    codes.release();
+    code_rec.release();
+    code_bytes = 0; n_coded = 0; code_escape_rate = 0;
+    auto &N = tree.nodes;
+    const char *off = std::getenv("GGQ_NO_CODES");
+    if (kind != BRWT || N.size() < 2 || tree.multi_column_leaves || tree.n_shards > 1 || (off && *off && *off != '0')) {
+        refresh_img();
+        return;
+    }
+    CUDA_CHECK(cudaSetDevice(device));
+    const size_t nn = N.size();
+    std::vector<u32> sub_groups(nn, 0), first_rank(nn, 0);
+    std::vector<double> probe_mass(nn, 0.0);   // sum over internal Y in the subtree of ones(Y) * groups(Y)
+    for (size_t id = nn; id-- > 0;) {          // BFS ids: children have larger ids than their parent
+        const FlatNode &n = N[id];
+        if (n.children.empty()) { first_rank[id] = n.leaf_rank; continue; }
+        sub_groups[id] = n.n_child_groups;
+        probe_mass[id] = double(n.ones) * n.n_child_groups;
+        first_rank[id] = first_rank[n.children[0]];
+        for (int c : n.children) { sub_groups[id] += sub_groups[c]; probe_mass[id] += probe_mass[c]; }
+    }
+    const double min_gain = 0.5;
+    struct Pick { u32 id; double gain, esc; };
+    std::vector<Pick> picks;
+    DeviceBuf<unsigned long long> d_esc;
+    d_esc.alloc(1);
+    std::vector<int> todo;
+    for (size_t i = N[0].children.size(); i-- > 0;) todo.push_back(N[0].children[i]);   // (the root itself is never coded)
+    while (!todo.empty()) {
+        const int id = todo.back();
+        todo.pop_back();
+        const FlatNode &n = N[id];
+        if (n.children.empty() || !tree.present(u32(id))) continue;
+        bool taken = false;
+        if (n.cols.size() <= kCodeEscape && sub_groups[id] < u32(kCodeStack) && n.ones > 0) {
+            const double C = probe_mass[id] / double(n.ones);
+            if (C - 1.0 >= min_gain) {   // (even with no escapes at all a 1-probe subtree gains nothing)
+                const u64 samples = std::min<u64>(n.ones, u64(1) << 16);
+                const u64 stride = std::max<u64>(1, n.ones / samples);
+                const u64 n_work = (n.ones + stride - 1) / stride;
+                CUDA_CHECK(cudaMemset(d_esc.p, 0, 8));
+                leaf_code_kernel<<<u32((n_work + 255) / 256), 256>>>(img, n.first_child_group, n.ones, first_rank[id], stride,
+                                                                    true, nullptr, d_esc.p);
+                CUDA_CHECK(cudaGetLastError());
+                unsigned long long esc = 0;
+                CUDA_CHECK(cudaMemcpy(&esc, d_esc.p, 8, cudaMemcpyDeviceToHost));
+                const double e = double(esc) / double(n_work);
+                const double gain = C - (1.0 + e * C);
+                if (gain >= min_gain) { picks.push_back({u32(id), gain, e}); taken = true; }
+            }
+        }
+        if (!taken)
+            for (size_t i = n.children.size(); i-- > 0;) todo.push_back(n.children[i]);
+    }
+    if (picks.empty()) { refresh_img(); return; }
+    // budget
+    size_t free_b = 0, total_b = 0;
+    CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    u64 budget = slots.bytes() / 2;
+    if (const char *b = std::getenv("GGQ_CODE_BUDGET_MB")) budget = std::strtoull(b, nullptr, 10) << 20;
+    const u64 reserve = u64(12) << 30;
+    budget = std::min<u64>(budget, free_b > reserve ? free_b - reserve : 0);
+    std::stable_sort(picks.begin(), picks.end(), [](const Pick &a, const Pick &b) { return a.gain > b.gain; });
+    std::vector<Pick> kept;
+    u64 bytes = 0;
+    for (const Pick &p : picks) {
+        const u64 need = (N[p.id].ones + 63) & ~u64(63);
+        if (bytes + need > budget) continue;
+        bytes += need;
+        kept.push_back(p);
+    }
+    if (kept.empty()) { refresh_img(); return; }
+    codes.alloc(bytes);
+    tree.lane_coded.assign(size_t(tree.n_groups()) * 4, 0);
+    tree.code_rec.assign(size_t(tree.n_groups()) * 16, 0);
+    int sms = 148;
+    CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    u64 at = 0;
+    double visits = 0, esc_visits = 0;
+    for (const Pick &p : kept) {
+        const FlatNode &n = N[p.id];
+        const u32 li = n.group * 4 + n.lane;
+        const u32 grid = u32(std::min<u64>((n.ones + 255) / 256, u64(sms) * 32));
+        leaf_code_kernel<<<grid, 256>>>(img, n.first_child_group, n.ones, first_rank[p.id], 1, false, codes.p + at, nullptr);
+        CUDA_CHECK(cudaGetLastError());
+        tree.lane_coded[li] = 1;
+        tree.code_rec[4 * size_t(li) + 0] = u32(at);
+        tree.code_rec[4 * size_t(li) + 1] = u32(at >> 32);
+        tree.code_rec[4 * size_t(li) + 2] = first_rank[p.id];
+        tree.code_rec[4 * size_t(li) + 3] = u32(n.cols.size());
+        at += (n.ones + 63) & ~u64(63);
+        visits += double(n.ones);
+        esc_visits += double(n.ones) * p.esc;
+    }
+    CUDA_CHECK(cudaDeviceSynchronize());
+    code_bytes = bytes;
+    n_coded = u32(kept.size());
+    code_escape_rate = visits > 0 ? esc_visits / visits : 0;
+    upload_codes_tables();
+}
+
+// code_rec + group records after tree.lane_coded / tree.code_rec changed (or use_codes was switched)
+void Matrix::upload_codes_tables() {
+    if (!tree.code_rec.empty()) {
+        code_rec.alloc(tree.code_rec.size() / 4);
+        CUDA_CHECK(cudaMemcpy(code_rec.p, tree.code_rec.data(), tree.code_rec.size() * 4, cudaMemcpyHostToDevice));
+    }
+    upload_records(tree);
+    refresh_img();
 }
 
 // host-parsed tree (plain bits per node) -> device image
@@ -369,6 +503,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     for (FlatNode &n : t.nodes) { n.bits.w.clear(); n.bits.w.shrink_to_fit(); }
     m->finalize_arena(t, true);
     m->refresh_img();
+    m->build_leaf_codes();
     m->derive_stats();
     return m.release();
 }
@@ -511,7 +646,7 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     ws->ran_safe = safe;
     Img img = m->img;
     void *kargs[] = {&img, &a};
-    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->emit_flat), dim3(grid),
+    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid),
                                 dim3(kRowsWarps * 32), kargs, ws->pipelined ? m->rows_smem_p : m->rows_smem, ws->stream));
 }
 
@@ -580,7 +715,7 @@ static void brwt_rows_begin(const Matrix *m, Workspace *ws, const u64 *d_rows, u
         // offsets[0..n] : exclusive sum over n+1 counts (the last one is a zero pad)
         CUDA_CHECK(cudaMemsetAsync(ws->d_row_cnt.p + n, 0, 4, st));
         cub::DeviceScan::ExclusiveSum(ws->d_cub.p, cb, ws->d_row_cnt.p, ws->d_offsets.p, n + 1, st);
-        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 5 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl, ws->d_ctrl.p, 8 * sizeof(u64), cudaMemcpyDeviceToHost, st));
     }
     GGQ_MARK(st, "scan+ctrl");
 }
@@ -609,6 +744,8 @@ static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, 
         u64 total = ws->h_ctrl[0];
         ws->last_probes = ws->h_ctrl[2];
         ws->last_touches = ws->h_ctrl[3];
+        ws->last_code_probes = ws->h_ctrl[5];
+        ws->last_code_escapes = ws->h_ctrl[6];
         ws->kernel_timed = true;
         // descent + ordering + (2 cub scan kernels | pipelined: ctrl publish + 3 scan kernels, none for a histogram)
         ws->launches = 1 + ws->pending_sort_launches + (ws->pipelined ? (ws->hist_mode ? 1 : 4) : 2);
@@ -848,6 +985,12 @@ uint64_t ggq_num_nodes(const ggq_matrix *m) { return m->n_nodes; }
 uint64_t ggq_total_column_size(const ggq_matrix *m) { return m->total_column_size; }
 uint64_t ggq_device_bytes(const ggq_matrix *m) { return m->device_bytes; }
 uint64_t ggq_last_probe_count(const ggq_matrix *m) { return m->last_probes; }
+int ggq_leaf_code_info(const ggq_matrix *m, uint64_t what[4]) {
+    if (!m || !what) return fail(GGQ_ERR_ARG, "bad argument");
+    what[0] = m->n_coded; what[1] = m->code_bytes; what[2] = uint64_t(m->code_escape_rate * 1e6 + 0.5);
+    what[3] = m->use_codes && m->n_coded;
+    return GGQ_OK;
+}
 
 int ggq_set_option(ggq_matrix *m, const char *name, uint64_t value) {
     GGQ_TRY
@@ -858,6 +1001,13 @@ int ggq_set_option(ggq_matrix *m, const char *name, uint64_t value) {
     m->pool.clear();
     CUDA_CHECK(cudaSetDevice(m->device));
     std::string k(name);
+    if (k == "leaf_codes") {   // 0: plain descent everywhere (A/B, and the reference's touch count V_t); 1: use the codes
+        m->use_codes = value != 0;
+        CUDA_CHECK(cudaSetDevice(m->device));
+        CUDA_CHECK(cudaDeviceSynchronize());
+        m->upload_codes_tables();
+        return GGQ_OK;
+    }
     if (k == "rows_per_warp") m->configure_rows(u32(value), m->sort_bits);
     else if (k == "sort_bits") m->configure_rows(m->rb, u32(std::min<uint64_t>(value, 64)));
     else if (k == "sort_min_rows") m->sort_min_n = value;
@@ -891,6 +1041,8 @@ double ggq_workspace_stat(const ggq_workspace *ws, int what) {
             return ms;
         }
         case GGQ_STAT_EXCHANGE_BYTES: return double(ws->exchange_bytes);
+        case GGQ_STAT_CODE_PROBES: return double(ws->last_code_probes);
+        case GGQ_STAT_CODE_ESCAPES: return double(ws->last_code_escapes);
         default: return -1.0;
     }
 }

@@ -66,8 +66,14 @@ struct Matrix {
     DeviceBuf<uint4> group_rec;   // per (group, half): hot word + the two children's lane_info (descent kernel)
     DeviceBuf<uint4> group_rec16; // per group: compact record (trees with < 2^20 - 1 columns), else empty
     bool compact_rec = false;
-    bool emit_flat = false;       // experimental K1 emit (GGQ_EMIT_FLAT=1)
     DeviceBuf<u32> lane_info, lane_aux, lane_sb_off, sel, leaf_col, col_path_off, col_path;
+    // leaf codes (ggq_rows.cuh): one byte per position of the coded nodes' child vectors
+    DeviceBuf<unsigned char> codes;
+    DeviceBuf<uint4> code_rec;
+    bool use_codes = true;        // ggq_set_option("leaf_codes", 0/1)
+    u64 code_bytes = 0;
+    u32 n_coded = 0;
+    double code_escape_rate = 0;  // visit-weighted escape fraction of the coded nodes (sampled at build time)
     Img img{};
 
     // stats
@@ -101,6 +107,9 @@ struct Matrix {
     Matrix() = default;
     ~Matrix();
     void upload_tables(const FlatTree &t);
+    void upload_records(const FlatTree &t);
+    void build_leaf_codes();
+    void upload_codes_tables();
     void finalize_arena(const FlatTree &t, bool ones_known);
     void refresh_img();
     void derive_stats();
@@ -125,7 +134,7 @@ struct Workspace {
     u64 *h_ctrl = nullptr;
     unsigned char *h_stage = nullptr;
     size_t h_stage_bytes = 0;
-    u64 last_probes = 0, last_touches = 0;
+    u64 last_probes = 0, last_touches = 0, last_code_probes = 0, last_code_escapes = 0;
     int launches = 0;
     int pending_sort_launches = 0;   // between brwt_rows_begin and brwt_rows_finish
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the dominant kernel of the last query

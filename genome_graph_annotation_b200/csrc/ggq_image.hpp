@@ -2,9 +2,9 @@
 // .brwt.annodbg it came from, so that a restart uploads the arrays as they are instead of re-parsing the
 // reference stream (RRR decode, BRWT.cpp:87-111), re-flattening it and rebuilding rank headers / select samples.
 //
-//   header   magic "GGQIMG01", endianness tag, matrix shape, the BRWT stats the reference API reports
+//   header   magic "GGQIMG02", endianness tag, layout constants, matrix shape, the BRWT stats the reference API reports
 //   tables   the host-side geometry (group records, lane tables, leaf order, column paths, shard plan) + FNV-1a
-//   arrays   slots (16-byte slots with inline rank headers), select samples, superblock bases, lane totals
+//   arrays   slots (16-byte slots with inline rank headers), select samples, superblock bases, lane totals, leaf codes
 //   trailer  end tag (a truncated file is rejected)
 //
 // Host words are little-endian (sm_100a hosts are); the tag makes a foreign file fail loudly instead of misreading.
@@ -16,7 +16,7 @@
 
 namespace ggq {
 
-static const char kImageMagic[8] = {'G', 'G', 'Q', 'I', 'M', 'G', '0', '1'};
+static const char kImageMagic[8] = {'G', 'G', 'Q', 'I', 'M', 'G', '0', '2'};
 static const u64 kImageEnd = 0x454e44474751494dull;
 static const u32 kImageEndian = 0x01020304u;
 
@@ -25,8 +25,11 @@ struct ImageHeader {
     u32 endian, kind;
     u64 n_rows, n_cols, n_nodes, total_column_size, num_relations;
     u64 total_slots, total_sb, total_sel;
-    u32 max_depth, multi_leaf, shard, n_shards, cut_depth, reserved;
+    u32 max_depth, multi_leaf, shard, n_shards, cut_depth, layout;   // layout: kImageLayout of the writing build
+    u64 code_bytes, n_coded, code_escape_ppm, reserved2;
 };
+// the kernel constants an image depends on: a file written with other values must not be indexed with these
+static const u32 kImageLayout = kSlotBits | (kSuperShift << 8) | (kSelectShift << 16) | (kGroupLanes << 24);
 
 struct Fnv {
     u64 h = 0xcbf29ce484222325ull;
@@ -99,6 +102,59 @@ struct PinnedStage {
     ~PinnedStage() { if (p) cudaFreeHost(p); }
 };
 
+// The checksum proves the tables are the ones that were written, not that they are sane: a file from a damaged
+// writer (or a forged one) must come back as GGQ_ERR_FORMAT, never as an out-of-bounds index on the host or device.
+inline void image_check_tables(const FlatTree &t, const ImageHeader &h, const std::vector<u64> &lane_ones_h) {
+    const u64 G = t.group_hot.size();
+    const u64 n_leaf_cols = t.leaf_col.size();
+    auto bad = [](const char *what) { throw ParseError(std::string("image file: ") + what); };
+    if (n_leaf_cols != h.n_cols && !(h.n_cols == 0 && n_leaf_cols == 0)) bad("leaf order does not cover the columns");
+    for (u32 c : t.leaf_col) if (c >= h.n_cols) bad("leaf column out of range");
+    for (u64 g = 0; g < G; ++g) {
+        const u64 hot = t.group_hot[g];
+        const u64 base = hot & kGhBaseMask, nb = t.group_nblocks[g];
+        const u32 sl = u32(hot >> kGhStrideShift) & 3u, cnt = u32(hot >> kGhCntShift) & 7u;
+        if (cnt > kGroupLanes || (cnt > (1u << sl))) bad("group shape");
+        if (nb > (u64(1) << 40) || base + (nb << sl) > h.total_slots) bad("group outside the slot arena");
+        if (((hot >> kGhMoreShift) & 1u) && g + 1 >= G) bad("continuation group missing");
+        const u64 n_sb = nb ? ((nb - 1) >> kSuperShift) + 1 : 1;
+        for (u32 k = 0; k < cnt; ++k) {
+            const u64 li = g * 4 + k;
+            const u32 info = t.lane_info[li];
+            if (info == kRemoteLane) continue;
+            if (info & kLeafFlag) {
+                if (u64(info & ~kLeafFlag) + t.lane_aux[li] > n_leaf_cols) bad("leaf rank out of range");
+            } else if (info >= G || info <= g) {
+                bad("child group out of range");   // (level order: children come after their parent)
+            }
+            if (u64(t.lane_sb_off[li]) + n_sb > std::max<u64>(h.total_sb, 1)) bad("superblock bases out of range");
+            if (!(info & kLeafFlag) || g == 0) {
+                const u64 n_sel = ((lane_ones_h[li] + (u64(1) << kSelectShift) - 1) >> kSelectShift) + 1;
+                if (nb && t.lane_sel_off[li] + n_sel > std::max<u64>(h.total_sel, 1)) bad("select samples out of range");
+            }
+        }
+    }
+    u32 prev = 0;
+    for (u64 c = 0; c <= h.n_cols; ++c) {
+        const u32 o = t.col_path_off[c];
+        if (o < prev || o > t.col_path.size()) bad("column paths");
+        prev = o;
+    }
+    for (u32 e : t.col_path) if ((e >> 2) >= G) bad("column path entry out of range");
+    if (!t.lane_coded.empty() || !t.code_rec.empty() || h.code_bytes) {
+        if (t.lane_coded.size() != 4 * G || t.code_rec.size() != 16 * G) bad("leaf-code tables");
+        for (u64 li = 0; li < 4 * G; ++li) {
+            if (!t.lane_coded[li]) continue;
+            const u32 info = t.lane_info[li];
+            if ((info & kLeafFlag) || info >= G) bad("coded lane is not internal");
+            const u64 off = (u64(t.code_rec[4 * li + 1]) << 32) | t.code_rec[4 * li];
+            if (off > h.code_bytes || lane_ones_h[li] > h.code_bytes - off) bad("leaf codes out of range");
+            if (t.code_rec[4 * li + 3] > kCodeEscape || u64(t.code_rec[4 * li + 2]) + t.code_rec[4 * li + 3] > n_leaf_cols)
+                bad("leaf-code ranks out of range");
+        }
+    }
+}
+
 inline void image_save(const Matrix *m, const char *path) {
     if (m->kind != Matrix::BRWT) throw std::runtime_error("only BRWT images can be saved");
     CUDA_CHECK(cudaSetDevice(m->device));
@@ -112,13 +168,15 @@ inline void image_save(const Matrix *m, const char *path) {
     h.n_nodes = m->n_nodes; h.total_column_size = m->total_column_size; h.num_relations = m->num_relations;
     h.total_slots = m->slots.n; h.total_sb = m->sb_base.n; h.total_sel = m->sel.n;
     h.max_depth = t.max_depth; h.multi_leaf = t.multi_column_leaves; h.shard = t.shard; h.n_shards = t.n_shards;
-    h.cut_depth = t.cut_depth;
+    h.cut_depth = t.cut_depth; h.layout = kImageLayout;
+    h.code_bytes = m->code_bytes; h.n_coded = m->n_coded; h.code_escape_ppm = u64(m->code_escape_rate * 1e6 + 0.5);
     io.put(&h, sizeof(h));
     io.put_vec(t.group_hot); io.put_vec(t.group_nblocks);
     io.put_vec(t.lane_info); io.put_vec(t.lane_aux); io.put_vec(t.lane_sb_off); io.put_vec(t.lane_sel_off);
     io.put_vec(t.leaf_col); io.put_vec(t.col_path_off); io.put_vec(t.col_path);
     io.put_vec(t.col_owned); io.put_vec(t.col_owner);
     io.put_vec(m->lane_size_h); io.put_vec(m->lane_ones_h);
+    io.put_vec(t.lane_coded); io.put_vec(t.code_rec);
     const u64 check = io.sum.h;
     if (std::fwrite(&check, 1, 8, io.f) != 8) throw std::runtime_error("image write failed");
     PinnedStage st;
@@ -126,6 +184,7 @@ inline void image_save(const Matrix *m, const char *path) {
     image_put_device(io, m->sel, st.p, st.bytes);
     image_put_device(io, m->sb_base, st.p, st.bytes);
     image_put_device(io, m->lane_ones, st.p, st.bytes);
+    if (m->code_bytes) image_put_device(io, m->codes, st.p, st.bytes);
     if (std::fwrite(&kImageEnd, 1, 8, io.f) != 8 || std::fflush(io.f) != 0) throw std::runtime_error("image write failed");
 }
 
@@ -135,6 +194,7 @@ inline Matrix *image_load(const char *path, int device) {
     io.get(&h, sizeof(h));
     if (std::memcmp(h.magic, kImageMagic, 8) != 0) throw ParseError("not a ggq image file (or another version)");
     if (h.endian != kImageEndian || h.kind != 0) throw ParseError("image file of a foreign byte order / kind");
+    if (h.layout != kImageLayout) throw ParseError("image file written by a build with another slot layout");
     if (h.n_rows >= kMaxRows || h.n_cols >= (u64(1) << 31)) throw LimitError("image exceeds engine limits");
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
@@ -149,6 +209,7 @@ inline Matrix *image_load(const char *path, int device) {
     io.get_vec(&t.leaf_col, lim); io.get_vec(&t.col_path_off, lim); io.get_vec(&t.col_path, lim);
     io.get_vec(&t.col_owned, lim); io.get_vec(&t.col_owner, lim);
     io.get_vec(&m->lane_size_h, u64(kMaxGroups) * 4); io.get_vec(&m->lane_ones_h, u64(kMaxGroups) * 4);
+    io.get_vec(&t.lane_coded, u64(kMaxGroups) * 4); io.get_vec(&t.code_rec, u64(kMaxGroups) * 16);
     const u64 expect = io.sum.h;
     u64 check = 0;
     if (std::fread(&check, 1, 8, io.f) != 8 || check != expect) throw ParseError("image file: table checksum mismatch");
@@ -158,6 +219,7 @@ inline Matrix *image_load(const char *path, int device) {
         m->lane_ones_h.size() != 4 * G || t.col_path_off.size() != t.n_cols + 1 ||
         (!t.col_owned.empty() && t.col_owned.size() != t.n_cols))
         throw ParseError("image file: inconsistent tables");
+    image_check_tables(t, h, m->lane_ones_h);
     t.total_slots = h.total_slots; t.total_sb = h.total_sb; t.total_sel = h.total_sel;
     t.max_depth = h.max_depth; t.multi_column_leaves = h.multi_leaf != 0;
     t.shard = h.shard; t.n_shards = h.n_shards; t.cut_depth = h.cut_depth;
@@ -167,6 +229,11 @@ inline Matrix *image_load(const char *path, int device) {
     image_get_device(io, m->sel, h.total_sel, st.p, st.bytes);
     image_get_device(io, m->sb_base, h.total_sb, st.p, st.bytes);
     image_get_device(io, m->lane_ones, u64(G) * 4, st.p, st.bytes);
+    if (h.code_bytes) {
+        image_get_device(io, m->codes, h.code_bytes, st.p, st.bytes);
+        m->code_bytes = h.code_bytes; m->n_coded = u32(h.n_coded); m->code_escape_rate = double(h.code_escape_ppm) / 1e6;
+        m->upload_codes_tables();
+    }
     u64 end = 0;
     if (std::fread(&end, 1, 8, io.f) != 8 || end != kImageEnd) throw ParseError("image file truncated");
     m->refresh_img();

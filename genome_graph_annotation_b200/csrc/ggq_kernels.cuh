@@ -503,7 +503,7 @@ cnt_block_scan_kernel(const u32 *cnt, u64 n_rows, const u64 *block_off, OutT *of
 // control words -> pinned host memory by a store from the device: a cudaMemcpyAsync of 40 bytes would queue behind
 // the previous chunk's 40 MB device->host copy on the copy engine and delay the host's "chunk k is done"
 __global__ void publish_ctrl_kernel(const u64 *ctrl, u64 *host) {
-    if (threadIdx.x < 5) host[threadIdx.x] = ctrl[threadIdx.x];
+    if (threadIdx.x < 8) host[threadIdx.x] = ctrl[threadIdx.x];
     __threadfence_system();
 }
 
@@ -570,6 +570,64 @@ __global__ void slice_rows_kernel(const u64 *offsets, const u32 *cols, u64 n, u6
     u64 o = b + t;
     for (u64 i = b; i < e; ++i) out[o++] = cols[i];
     out[o] = ~0ull;
+}
+
+// ------------------------------------------------------------------------------------------
+// Leaf codes (ggq_rows.cuh): for an internal node Z with first child group g0 and ones(Z) = n_pos positions in its
+// children's vectors, codes[p] = DFS index (relative to the subtree's first leaf, rank0) of the only leaf set below
+// Z at position p, or kCodeEscape when the subtree holds several (or, in a damaged tree, none).  One thread per
+// position walks the subtree depth-first and stops at the second leaf.  `sample`: positions i * stride are examined,
+// nothing is stored, *escapes counts the escape codes (the engine decides per node
+// whether codes pay: DESIGN.md 1.1b).
+// ------------------------------------------------------------------------------------------
+constexpr int kCodeStack = 64;   // pending groups of one walk; the engine codes only subtrees with fewer groups
+
+__global__ void __launch_bounds__(256)
+leaf_code_kernel(Img img, u32 g0, u64 n_pos, u32 rank0, u64 stride, bool sample, unsigned char *codes, unsigned long long *escapes) {
+    const u64 n_work = (n_pos + stride - 1) / stride;
+    u32 esc_local = 0;
+    for (u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x; i < n_work; i += u64(gridDim.x) * blockDim.x) {
+        const u64 p = i * stride;
+        u32 st_g[kCodeStack];
+        u64 st_r[kCodeStack];
+        int sp = 0;
+        st_g[0] = g0; st_r[0] = p; sp = 1;
+        u32 found = 0, code = kCodeEscape;
+        while (sp > 0 && found < 2) {
+            --sp;
+            const u32 g = st_g[sp];
+            const u64 r = st_r[sp];
+            const u64 hot = __ldg(img.group_hot + g);
+            const u32 cnt = u32(hot >> kGhCntShift) & 7u;
+            if (((hot >> kGhMoreShift) & 1u) && sp < kCodeStack) { st_g[sp] = g + 1; st_r[sp] = r; ++sp; }
+            const u64 blk = r / kSlotBits;
+            const u32 bit = u32(r - blk * kSlotBits);
+            // children in reverse so that the walk is depth-first in child order (irrelevant to the result)
+            for (int k = int(cnt) - 1; k >= 0; --k) {
+                const u32 li = g * 4 + u32(k);
+                const uint4 s = ld_slot_cached(slot_addr(img, hot, blk, u32(k)));
+                if (!slot_test(s, bit)) continue;
+                const u32 info = __ldg(img.lane_info + li);
+                if (info & kLeafFlag) {
+                    ++found;
+                    code = (info & ~kLeafFlag) - rank0;
+                } else if (sp < kCodeStack) {
+                    st_g[sp] = info;
+                    st_r[sp] = lane_rank_base(img, li, blk, s) + slot_rank_before(s, bit);
+                    ++sp;
+                } else {
+                    found = 2;   // cannot happen for subtrees the engine selects; be safe: escape
+                }
+            }
+        }
+        const u32 out = (found == 1 && code < kCodeEscape) ? code : kCodeEscape;
+        if (sample) esc_local += out == kCodeEscape;
+        else codes[p] = (unsigned char)out;
+    }
+    if (sample) {
+        for (int o = 16; o; o >>= 1) esc_local += __shfl_xor_sync(0xffffffffu, esc_local, o);
+        if ((threadIdx.x & 31) == 0 && esc_local) atomicAdd(escapes, (unsigned long long)esc_local);
+    }
 }
 
 // ------------------------------------------------------------------------------------------

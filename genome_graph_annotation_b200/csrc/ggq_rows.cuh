@@ -30,6 +30,9 @@ constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
 constexpr int kItemsPerIter = 16;
 constexpr int kEmitQueue = 32;         // entries of the per-warp queue of non-zero bitmap words
 constexpr int kRowCounters = 16;       // per-warp row counters (>= kMaxRowsPerWarp)
+constexpr int kStatCounters = 4;       // per-warp kernel statistics: code probes, code escapes (flushed at kernel end)
+constexpr u32 kCodeEscape = 255;       // leaf code "more than one leaf set below: descend"
+constexpr u32 kCodedFlag = 1u << 30;   // wide group records: internal child with leaf codes
 
 struct RowsArgs {
     const u64 *rows;          // query row ids in PROCESSING order (sorted by the engine, or the caller's order)
@@ -37,7 +40,8 @@ struct RowsArgs {
     u64 n;                    // number of queries
     u32 *tmp_cols;            // unordered chunk arena
     u64 tmp_cap;
-    u64 *cursor;              // [0] chunk cursor, [1] tile ticket, [2] probe counter, [3] (node,row) touches
+    u64 *cursor;              // [0] chunk cursor, [1] tile ticket, [2] probe counter, [3] (node,row) touches, [4] overflow
+                              // flag, [5] leaf-code probes, [6] leaf-code escapes
     u64 *row_tmp_off;         // per query (caller's index): start in tmp_cols
     u32 *row_cnt;             // per query (caller's index): number of columns
     u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
@@ -56,9 +60,9 @@ struct RowsArgs {
 constexpr u32 kNoRootFast = 0xFFFFFFFFu;
 
 // Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][queues: warps x 32 u64][per warp: rb*bm_words
-// bitmap words + 16 row counters (u32)]
+// bitmap words + 16 row counters + 4 statistics counters (u32)]
 inline size_t rows_smem_bytes(u32 cap_s, u32 rb, u32 bm_words) {
-    return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(kEmitQueue) * 8 + (size_t(rb) * bm_words + kRowCounters) * 4);
+    return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(kEmitQueue) * 8 + (size_t(rb) * bm_words + kRowCounters + kStatCounters) * 4);
 }
 
 // Shared memory through 32-bit shared-window addresses (computed once per kernel).
@@ -76,15 +80,6 @@ __device__ __forceinline__ u32 lds32(u32 a) {
 __device__ __forceinline__ void sts32(u32 a, u32 v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void reds_or(u32 a, u32 v) { asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void reds_add(u32 a, u32 v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-
-__device__ __forceinline__ uint4 lds128(u32 a) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
-    return v;
-}
-__device__ __forceinline__ void sts128_zero(u32 a) {
-    asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" :: "r"(a), "r"(0u) : "memory");
-}
 
 template <bool SPILL>
 __device__ __forceinline__ u64 stk_get(u32 stk, const u64 *spill, u32 cap_s, u32 i) {
@@ -161,24 +156,39 @@ template <> struct RecFmt<false> { static constexpr u32 kLeaf = kLeafFlag, kRemo
 template <> struct RecFmt<true> { static constexpr u32 kLeaf = 1u << 20, kRemote = (1u << 21) - 1u; };
 
 template <bool COMPACT>
-__device__ __forceinline__ void load_rec(const Img &img, u32 g, u32 half, u64 &base, u32 &flags, u32 &child0, u32 &child1) {
+__device__ __forceinline__ void load_rec(const Img &img, u32 g, u32 half, u64 &base, u32 &flags, u32 &child0, u32 &child1,
+                                         u32 &coded) {
     if (!COMPACT) {
         const uint4 rec = __ldg(img.group_rec + 2 * g + half);
         base = (u64(rec.y & 0xffu) << 32) | rec.x;
         flags = (rec.y >> (kGhStrideShift - 32)) & 0x7fu;
-        child0 = rec.z;
-        child1 = rec.w;
+        // bit 30 of an internal child: the child carries leaf codes (a leaf / remote lane has bit 31 set)
+        coded = ((rec.z >> 31) ? 0u : (rec.z >> 30) & 1u) | ((rec.w >> 31) ? 0u : (rec.w >> 29) & 2u);
+        child0 = (rec.z >> 31) ? rec.z : rec.z & ~kCodedFlag;
+        child1 = (rec.w >> 31) ? rec.w : rec.w & ~kCodedFlag;
     } else {
-        const uint4 rec = __ldg(img.group_rec16 + g);   // x: base / 4; y: flags | c0 << 7; z: c1 | c2 << 21; w: c2 >> 11 | c3 << 10
+        // x: base / 4; y: flags | c0 << 7 | coded mask << 28; z: c1 | c2 << 21; w: c2 >> 11 | c3 << 10
+        const uint4 rec = __ldg(img.group_rec16 + g);
         base = u64(rec.x) << 2;
         flags = rec.y & 0x7fu;
         const u32 m = (1u << 21) - 1u;
         child0 = half ? ((rec.z >> 21) | (rec.w << 11)) & m : (rec.y >> 7) & m;
         child1 = half ? (rec.w >> 10) & m : rec.z & m;
+        coded = (rec.y >> (28 + 2 * half)) & 3u;
     }
 }
 
-template <bool SPILL, bool MULTI_LEAF, bool COMPACT, bool EMIT_FLAT = false>
+// Leaf codes: an internal child Z whose subtree has at most 255 leaves can carry one byte per
+// position p of its children's vectors: the DFS index (within the subtree) of the ONLY leaf set below Z at p, or 255
+// when several are — then the subtree is descended as usual.  One 1-byte probe replaces the whole sub-descent
+// (for the C4 tree: 3 levels, 22.9 of 33.4 probes per row) whenever a row has a single label under Z.
+__device__ __forceinline__ u32 ld_code(const unsigned char *p) {
+    u32 v;
+    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+template <bool SPILL, bool MULTI_LEAF, bool COMPACT>
 __global__ void __launch_bounds__(kRowsWarps * 32)
 brwt_rows_kernel(Img img, RowsArgs a) {
     typedef RecFmt<COMPACT> Fmt;
@@ -189,7 +199,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     const u32 smem0 = u32(__cvta_generic_to_shared(smem_raw));
     u32 stk = smem0 + warp * a.cap_s * 8;
     u32 que = smem0 + kRowsWarps * a.cap_s * 8 + warp * (kEmitQueue * 8);
-    u32 bm = smem0 + kRowsWarps * (a.cap_s * 8 + kEmitQueue * 8) + warp * ((bm_total + kRowCounters) * 4);
+    u32 bm = smem0 + kRowsWarps * (a.cap_s * 8 + kEmitQueue * 8) + warp * ((bm_total + kRowCounters + kStatCounters) * 4);
     u32 cnt0 = bm + bm_total * 4;
     // keep the per-warp bases in registers: ptxas otherwise rematerialises them (S2R + IMAD chains) inside the
     // descent loop, which is instruction-issue bound; a shuffle is opaque to it
@@ -198,6 +208,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     bm = __shfl_sync(0xffffffffu, bm, lane);
     cnt0 = __shfl_sync(0xffffffffu, cnt0, lane);
     const u32 bm_row_bytes = a.bm_words * 4;
+    const u32 stat0 = cnt0 + kRowCounters * 4;
     u64 *spill = SPILL ? a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill : nullptr;
     const u32 cap_total = a.cap_s + a.cap_spill;
     u32 idx = lane >> 1, half = lane & 1;   // 2 lanes serve one item; lane `half` owns children 2*half, 2*half+1
@@ -206,7 +217,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
 
     // bitmaps and counters start clean; every tile leaves them clean
-    for (u32 i = lane; i < bm_total + kRowCounters; i += 32) sts32(bm + i * 4, 0);
+    for (u32 i = lane; i < bm_total + kRowCounters + kStatCounters; i += 32) sts32(bm + i * 4, 0);
     __syncwarp();
 
     for (;;) {
@@ -261,8 +272,8 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                 const u32 g = ilo & (kMaxGroups - 1);
                 const u32 tq = ilo & ((kMaxRowsPerWarp - 1) << kItemGroupBits);   // t, in place
                 u64 gbase;
-                u32 flags, child0, child1;
-                load_rec<COMPACT>(img, g, half, gbase, flags, child0, child1);
+                u32 flags, child0, child1, coded;
+                load_rec<COMPACT>(img, g, half, gbase, flags, child0, child1, coded);
                 const u32 sl = flags & 3u;
                 const u32 cnt = (flags >> 2) & 7u;
                 push_cont = half == 0 && ((flags >> 5) & 1u);
@@ -301,6 +312,27 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                         const u64 sb = blk >> kSuperShift;
                         if (push0) ones0 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half] + sb];   // entry 0 of a lane is 0
                         if (push1) ones1 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half + 1] + sb];
+                    }
+                    if (coded) {   // leaf codes: a single label below the child is marked right here, no push
+                        const bool c0 = push0 && (coded & 1u), c1 = push1 && (coded & 2u);
+                        if (c0 | c1) {
+                            const u32 li = g * 4 + 2 * half;
+                            u32 code0 = kCodeEscape, code1 = kCodeEscape, lr0 = 0, lr1 = 0;
+                            if (c0) {
+                                const uint4 cr = __ldg(img.code_rec + li);
+                                code0 = ld_code(img.codes + ((u64(cr.y) << 32) | cr.x) + ones0);
+                                lr0 = cr.z;
+                            }
+                            if (c1) {
+                                const uint4 cr = __ldg(img.code_rec + li + 1);
+                                code1 = ld_code(img.codes + ((u64(cr.y) << 32) | cr.x) + ones1);
+                                lr1 = cr.z;
+                            }
+                            if (code0 != kCodeEscape) { mark_leaf<false>(img, lr0 + code0, 0, bm_row, cnt0 + t * 4); push0 = false; }
+                            if (code1 != kCodeEscape) { mark_leaf<false>(img, lr1 + code1, 0, bm_row, cnt0 + t * 4); push1 = false; }
+                            reds_add(stat0, u32(c0) + u32(c1));                                          // code probes
+                            reds_add(stat0 + 4, u32(c0 && push0) + u32(c1 && push1));                    // escapes
+                        }
                     }
                     item0 = (ones0 << kItemRShift) | tq | child0;   // (only pushed for internal children: plain group index)
                     item1 = (ones1 << kItemRShift) | tq | child1;
@@ -352,51 +384,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             a.row_tmp_off[q] = base + pre;
             a.row_cnt[q] = my_cnt;
         }
-        if (EMIT_FLAT) {
-            // Flat emit (experimental, GGQ_EMIT_FLAT=1): the tile's bitmaps are one contiguous array of nr * bm_words
-            // words and (row, rank) order IS its flat order, so the scan needs no row loop and no queue: 128-bit
-            // loads (4 words per lane), a warp prefix sum of the popcounts, ids stored straight from the bits.
-            // 664 words per C4 tile = 6 iterations instead of 24 (profiles/r01/k1_sass_budget.txt).
-            if (total) {
-                const bool fits = base + total <= a.tmp_cap;
-                const u32 n_vec = (nr * a.bm_words + 3) >> 2;
-                // floor(2^32 / bm_words) + 1: word index within the row by one mulhi (exact for f * bm_words < 2^32)
-                const u32 bm_magic = a.bm_words > 1 ? u32((u64(1) << 32) / a.bm_words) + 1u : 0u;
-                u64 pos = base;
-                for (u32 v0 = 0; v0 < n_vec; v0 += 32) {
-                    const u32 v = v0 + lane;
-                    uint4 b = make_uint4(0u, 0u, 0u, 0u);
-                    if (v < n_vec) b = lds128(bm + v * 16);
-                    const bool any = (b.x | b.y | b.z | b.w) != 0;
-                    if (!__any_sync(0xffffffffu, any)) continue;
-                    if (any) sts128_zero(bm + v * 16);
-                    const u32 c = __popc(b.x) + __popc(b.y) + __popc(b.z) + __popc(b.w);
-                    u32 inc = c;
-                    #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const u32 x = __shfl_up_sync(0xffffffffu, inc, o);
-                        if (lane >= o) inc += x;
-                    }
-                    if (c && fits) {
-                        u64 p = pos + inc - c;
-                        const u32 wv[4] = {b.x, b.y, b.z, b.w};
-                        #pragma unroll
-                        for (u32 j = 0; j < 4; ++j) {
-                            u32 bits = wv[j];
-                            if (!bits) continue;
-                            const u32 f = v * 4 + j;   // flat word -> word within its row
-                            const u32 w = a.bm_words == 1 ? 0u : f - __umulhi(f, bm_magic) * a.bm_words;
-                            while (bits) {
-                                const u32 bit = __ffs(bits) - 1;
-                                bits &= bits - 1;
-                                a.tmp_cols[p++] = __ldg(img.leaf_col + w * 32 + bit);
-                            }
-                        }
-                    }
-                    pos += __shfl_sync(0xffffffffu, inc, 31);
-                }
-            }
-        } else if (total) {
+        if (total) {
             const bool fits = base + total <= a.tmp_cap;   // else: the engine grows the arena and reruns
             const u32 rows_mask = __ballot_sync(0xffffffffu, my_cnt != 0);
             u64 pos = base;
@@ -433,6 +421,10 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     if (lane == 0 && probes) atomicAdd(a.cursor + 2, u64(probes));
     touches = __reduce_add_sync(0xffffffffu, touches);
     if (lane == 0 && touches) atomicAdd(a.cursor + 3, u64(touches));
+    if (lane < 2) {   // code probes -> cursor[5], escapes -> cursor[6]
+        const u32 v = lds32(stat0 + lane * 4);
+        if (v) atomicAdd(a.cursor + 5 + lane, u64(v));
+    }
 }
 
 }  // namespace ggq

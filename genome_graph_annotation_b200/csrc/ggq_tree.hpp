@@ -45,6 +45,9 @@ struct FlatTree {
     std::vector<uint32_t> leaf_col;       // DFS rank -> global column
     std::vector<uint32_t> col_path_off;   // n_cols + 1
     std::vector<uint32_t> col_path;       // (group << 2 | lane), root first
+    // leaf codes (ggq_rows.cuh): per lane, 1 if the lane's node carries codes; code_rec[li] = {offset lo, hi, rank0, leaves}
+    std::vector<uint8_t> lane_coded;
+    std::vector<uint32_t> code_rec;       // 4 words per lane (empty when no lane is coded)
     uint64_t total_slots = 0, total_sb = 0, total_sel = 0;
     uint32_t max_depth = 0;
     bool multi_column_leaves = false;

@@ -91,6 +91,9 @@ uint64_t ggq_num_relations(const ggq_matrix *m);
 uint64_t ggq_num_nodes(const ggq_matrix *m);
 uint64_t ggq_total_column_size(const ggq_matrix *m);
 uint64_t ggq_device_bytes(const ggq_matrix *m);
+/* Leaf codes of a BRWT image: what[0] = coded nodes, what[1] = code bytes on the device,
+ * what[2] = sampled escape rate x 1e6 (visit-weighted), what[3] = 1 if the descent currently uses them. */
+int ggq_leaf_code_info(const ggq_matrix *m, uint64_t what[4]);
 /* Algorithmic work of the last ggq_get_rows* call on this workspace/matrix: number of sibling-group
  * probes (one 16/32/64-byte block read each).  For roofline accounting. */
 uint64_t ggq_last_probe_count(const ggq_matrix *m);
@@ -177,7 +180,8 @@ void *ggq_workspace_stream(ggq_workspace *ws);  /* cudaStream_t */
  * device time of the dominant kernel between two CUDA events on the workspace stream; sibling-group
  * probes (one 16/32/64-byte block each); (node,row) bit tests (V_t of SURVEY.md 8d); kernel launches. */
 enum { GGQ_STAT_KERNEL_MS = 0, GGQ_STAT_PROBES = 1, GGQ_STAT_TOUCHES = 2, GGQ_STAT_LAUNCHES = 3,
-       GGQ_STAT_EXCHANGE_MS = 4 /* NCCL exchange of the last sharded query */, GGQ_STAT_EXCHANGE_BYTES = 5 };
+       GGQ_STAT_EXCHANGE_MS = 4 /* NCCL exchange of the last sharded query */, GGQ_STAT_EXCHANGE_BYTES = 5,
+       GGQ_STAT_CODE_PROBES = 6 /* 1-byte leaf-code probes of the last query */, GGQ_STAT_CODE_ESCAPES = 7 };
 double ggq_workspace_stat(const ggq_workspace *ws, int what);
 int ggq_get_rows_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,
                         int col_bytes, const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols);
@@ -275,6 +279,22 @@ int ggq_bv_get(const ggq_bv *v, const uint64_t *q, uint64_t n, uint8_t *out);
 int ggq_bv_rank1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
 int ggq_bv_select1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
 int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t *d_out, void *stream);
+/* The rest of the reference's bit_vector interface (not on the row-query path; composed from rank1 / operator[] on
+ * the device, as the reference composes them on the host):
+ *   rank0(id) = min(id + 1, size) - rank1(id)                         (common/bit_vector.cpp:32-34)
+ *   select0(k): position of the k-th zero, k in [1, size - num_set_bits] (bit_vector_rrr::select0, bit_vector.hpp:199;
+ *               answered for every kind, by bisection over rank1)
+ *   get_int(id, width): bits [id, id + width) LSB first, width in [1, 64] (bit_vector.hpp:25); bits past the end read 0
+ *   to_words: the plain bits, (size + 63) / 64 LSB-first words         (to_vector / copy, bit_vector.cpp:36-46)
+ *   call_ones_into: positions of the set bits, ascending               (call_ones, bit_vector.cpp:442-451, 767-790, 958-983);
+ *               *n_ones is always set; GGQ_ERR_ARG if capacity < num_set_bits */
+int ggq_bv_rank0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
+int ggq_bv_select0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
+int ggq_bv_rank0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
+int ggq_bv_select0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);
+int ggq_bv_get_int(const ggq_bv *v, const uint64_t *q, uint64_t n, uint32_t width, uint64_t *out);
+int ggq_bv_to_words(const ggq_bv *v, uint64_t *words);
+int ggq_bv_call_ones_into(const ggq_bv *v, uint64_t *positions, uint64_t capacity, uint64_t *n_ones);
 
 #ifdef __cplusplus
 }

@@ -247,6 +247,33 @@ class RefBitVector:
     def get(self, q, threads=1):
         return self._q(2, q, threads)[0]
 
+    def _aux(self, op, q, width=64):
+        q = np.ascontiguousarray(q, dtype=np.uint64)
+        out = np.empty(q.size, dtype=np.uint64)
+        f = lib().ggref_bv_query_aux
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p]
+        if f(self.h, op, _p(q), q.size, width, _p(out)) != 0:
+            raise ValueError("the reference does not offer this operation on %s" % self.kind)
+        return out
+
+    def rank0(self, q):
+        return self._aux(3, q)
+
+    def select0(self, q):
+        return self._aux(4, q)
+
+    def get_int(self, q, width):
+        return self._aux(5, q, width)
+
+    def call_ones(self):
+        out = np.empty(max(int(self.num_set_bits), 1), dtype=np.uint64)
+        f = lib().ggref_bv_call_ones
+        f.restype = C.c_uint64
+        f.argtypes = [C.c_void_p, C.c_void_p]
+        k = f(self.h, _p(out))
+        return out[:k]
+
     def timed(self, op, q, threads):
         return self._q({"rank1": 0, "select1": 1, "get": 2}[op], q, threads)
 

@@ -267,6 +267,32 @@ int ggref_bv_is_inverted(const void *h) {
     return sd ? sd->is_inverted() : 0;
 }
 
+// The rest of the bit_vector interface (common/bit_vector.hpp:18-44,199), for the parity tests of ggq_bv_rank0 /
+// select0 / get_int / call_ones_into.  op: 3 = rank0, 4 = select0 (bit_vector_rrr only, else returns -1),
+// 5 = get_int(q[i], width).
+int ggref_bv_query_aux(const void *h, int op, const uint64_t *q, uint64_t n, uint32_t width, uint64_t *out) {
+    const bit_vector &v = *static_cast<const BV *>(h)->v;
+    if (op == 3) {
+        for (uint64_t i = 0; i < n; ++i) out[i] = v.rank0(q[i]);
+    } else if (op == 4) {
+        auto *rrr = dynamic_cast<const bit_vector_rrr<> *>(&v);
+        if (!rrr) return -1;
+        for (uint64_t i = 0; i < n; ++i) out[i] = rrr->select0(q[i]);
+    } else if (op == 5) {
+        for (uint64_t i = 0; i < n; ++i) out[i] = v.get_int(q[i], width);
+    } else {
+        return -1;
+    }
+    return 0;
+}
+
+// call_ones (bit_vector.hpp:44): positions in callback order; out must hold num_set_bits entries.
+uint64_t ggref_bv_call_ones(const void *h, uint64_t *out) {
+    uint64_t k = 0;
+    static_cast<const BV *>(h)->v->call_ones([&](uint64_t i) { out[k++] = i; });
+    return k;
+}
+
 // op: 0 = rank1, 1 = select1, 2 = operator[].  Returns seconds of the loop.
 double ggref_bv_query(const void *h, int op, const uint64_t *q, uint64_t n,
                       uint64_t *out, int threads) {

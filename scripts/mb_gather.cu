@@ -107,6 +107,15 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&sink, 8));
     CK(cudaMemset(buf, 1, bytes));
     printf("buffer %.1f GB\n", bytes / 1e9);
+    if (argc > 3) {   // quick: the K1-shaped probe (2 lanes x 256-bit) at footprints argv[3..] GiB within the buffer
+        for (int i = 3; i < argc; ++i) {
+            const uint64_t fp = strtoull(argv[i], nullptr, 10) << 30;
+            if (fp > bytes) continue;
+            printf(" footprint %8.2f GiB\n", fp / double(1ull << 30));
+            if (run<2, 1, 32, 4, H_NA>(buf, fp, sink, "nc.na v8", 8)) return 1;
+        }
+        return 0;
+    }
     // footprint sweep: is the probe rate a TLB / page-walk limit?
     for (uint64_t fp = 1ull << 26; fp <= bytes; fp <<= 2) {
         printf(" footprint %8.2f GiB\n", fp / double(1ull << 30));

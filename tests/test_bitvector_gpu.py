@@ -1,4 +1,5 @@
-"""GPU parity of bit_vector_{stat,sd,rrr} rank1 / select1 / get (K5) through the C ABI vs the unmodified
+"""GPU parity of bit_vector_{stat,sd,rrr} rank1 / select1 / get (K5) and rank0 / select0 / get_int / to_vector /
+call_ones through the C ABI vs the unmodified
 reference classes (common/bit_vector.cpp:281-304, 690-718, 857-888 behind oracle/_ref/libggref.so).
 Cases follow tests/test_bit_vector.cpp: the 16-bit golden pattern (:88-89), all-0 / all-1 vectors incl.
 rank1 far beyond the end (:58-86), rank clamping (:25-29), the sd inversion rule over all 10-bit words
@@ -54,6 +55,25 @@ def check(ggq, ref, kind, bits, via_stream=False):
             sel = gv.select1(ks)
             assert np.array_equal(sel, rv.select1(ks))
             assert np.array_equal(sel, np.nonzero(bits)[0][ks.astype(np.int64) - 1].astype(np.uint64))
+        # the rest of the bit_vector interface: rank0, select0, get_int, to_vector, call_ones
+        rq0 = np.concatenate([pos, np.array([n, n + 1, n + 990, 2**40], dtype=np.uint64)])
+        assert np.array_equal(gv.rank0(rq0), rv.rank0(rq0))
+        zeros = n - ones
+        if zeros:
+            kz = np.arange(1, zeros + 1, dtype=np.uint64) if zeros <= 5000 else \
+                np.unique(np.concatenate([np.random.default_rng(2).integers(1, zeros + 1, 4000), [1, 2, zeros]])).astype(np.uint64)
+            sel0 = gv.select0(kz)
+            assert np.array_equal(sel0, np.nonzero(bits == 0)[0][kz.astype(np.int64) - 1].astype(np.uint64))
+            if kind == "rrr":   # the only kind the reference offers select0 on (bit_vector.hpp:199)
+                assert np.array_equal(sel0, rv.select0(kz))
+        for width in (1, 7, 32, 64):
+            if n >= width:
+                pq = pos[pos + np.uint64(width) <= np.uint64(n)][:2000]
+                assert np.array_equal(gv.get_int(pq, width), rv.get_int(pq, width)), (kind, width)
+        assert np.array_equal(gv.to_words(), words[:(n + 63) // 64])
+        mine = gv.call_ones()
+        assert np.array_equal(mine, np.nonzero(bits)[0].astype(np.uint64))
+        assert np.array_equal(np.sort(rv.call_ones()), mine)
     finally:
         gv.close()
 
@@ -69,7 +89,7 @@ def test_golden_and_degenerate(ggq, ref, kind):
 
 
 def test_sd_inversion_all_10bit_words(ggq, ref):
-    for w in range(0, 1024, 7):
+    for w in range(1024):   # every word the reference pins (tests/test_bit_vector.cpp:642-658)
         bits = [(w >> i) & 1 for i in range(10)]
         check(ggq, ref, "sd", bits)
 

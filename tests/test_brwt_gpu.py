@@ -225,3 +225,26 @@ def test_irregular_trees_random_row_densities(ggq, ref, m, relax, seed, rb):
         assert np.array_equal(gm.count_labels(rows), np.bincount(ecols.astype(np.int64), minlength=m).astype(np.uint64))
     finally:
         gm.close()
+
+
+def test_leaf_codes_on_reference_built_multi_brwt(ggq, ref):
+    """Leaf codes on a tree made by the reference's own builder (greedy pairing + relax: irregular arities, leaves at
+    different depths, non-identity column arrangement): rows with codes on and off against the unmodified reference."""
+    n, m = 60_000, 600
+    cw = ref.gen_norepl(n, m, 0.004, seed=7)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=6, threads=8)
+    gm = ggq.GpuMatrix.load_brwt(rm.serialize())
+    try:
+        info = gm.leaf_codes
+        assert info["nodes"] > 0 and info["in_use"], info
+        rows = ref.gen_random_ints(50_000, 0, n, seed=3)
+        eoff, ecols, _ = rm.get_rows(rows, threads=8)
+        for on in (1, 0):
+            gm.set_option("leaf_codes", on)
+            off, cols = gm.get_rows_csr(rows)
+            assert np.array_equal(off, eoff) and np.array_equal(cols, ecols), on
+            lc, lv = gm.get_labels(rows[:300], 0.0)
+            h = np.bincount(ecols[:int(eoff[300])].astype(np.int64), minlength=m)
+            assert np.array_equal(lc, np.nonzero(h)[0].astype(np.uint64)) and np.array_equal(lv, h[h != 0].astype(np.uint64))
+    finally:
+        gm.close()

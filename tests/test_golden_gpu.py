@@ -124,3 +124,58 @@ def test_image_file_of_a_device_built_shard(ggq, tmp_path):
                 assert np.array_equal(np.isin(rows, col_rows), np.array([c in cols[off[t]:off[t + 1]] for t in range(rows.size)]))
         finally:
             gi.close()
+
+
+def _fnv1a(data):
+    h = 0xcbf29ce484222325
+    for b in data:
+        h = ((h ^ b) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def test_image_with_valid_checksum_but_insane_tables_is_rejected(ggq, tmp_path):
+    """The FNV sum only proves the tables are what the writer wrote.  Forge files whose checksum matches but whose
+    tables index outside the arrays (child group, leaf rank, slot base, column path): GGQ_ERR_FORMAT, not a crash."""
+    import struct
+    n, m, d = 4000, 37, 0.05
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=3, arity=3)
+    img = str(tmp_path / "t.ggqimg")
+    gm.save_image(img)
+    exp = gm.get_rows_csr(np.arange(0, n, 7, dtype=np.uint64))
+    gm.close()
+    raw = bytearray(open(img, "rb").read())
+    hdr = 8 + 8 + 5 * 8 + 3 * 8 + 6 * 4 + 4 * 8   # ImageHeader (ggq_image.hpp)
+    # walk the length-prefixed tables to find where each starts and where the checksum sits
+    widths = [8, 8, 4, 4, 4, 8, 4, 4, 4, 1, 4, 8, 8, 1, 4]
+    pos, starts = hdr, []
+    for w in widths:
+        cnt = struct.unpack_from("<Q", raw, pos)[0]
+        starts.append((pos + 8, cnt, w))
+        pos += 8 + cnt * w
+    sum_at = pos
+    assert struct.unpack_from("<Q", raw, sum_at)[0] == _fnv1a(raw[:sum_at])   # the walk matches the writer
+
+    def forged(table, index, value):
+        b = bytearray(raw)
+        off, cnt, w = starts[table]
+        assert index < cnt
+        struct.pack_into({1: "<B", 4: "<I", 8: "<Q"}[w], b, off + index * w, value)
+        struct.pack_into("<Q", b, sum_at, _fnv1a(b[:sum_at]))
+        return bytes(b)
+
+    cases = [forged(0, 1, (1 << 39) | (2 << 40) | (3 << 42)),   # group_hot: slot base far outside the arena
+             forged(2, 0, 5_000_000),                            # lane_info: root's child group out of range
+             forged(2, starts[2][1] - 4, 0x80000000 | 10_000),   # lane_info: leaf rank beyond the columns
+             forged(6, 0, 77_777),                               # leaf_col: column id out of range
+             forged(8, 0, 0xFFFFFFF0),                           # col_path: group out of range
+             forged(7, 1, 0xFFFFFFF0)]                           # col_path_off: not monotone / beyond the paths
+    for bad in cases:
+        open(img, "wb").write(bad)
+        with pytest.raises(ggq.GgqError) as e:
+            ggq.GpuMatrix.load_image(img)
+        assert e.value.code == -1
+    open(img, "wb").write(bytes(raw))
+    gi = ggq.GpuMatrix.load_image(img)
+    off, cols = gi.get_rows_csr(np.arange(0, n, 7, dtype=np.uint64))
+    assert np.array_equal(off, exp[0]) and np.array_equal(cols, exp[1])
+    gi.close()

@@ -316,3 +316,55 @@ def test_underestimated_stack_reruns_with_the_provable_capacity(ggq, orc, monkey
             gs.close()
     for t in range(0, rows.size, 997):
         assert np.array_equal(base[1][base[0][t]:base[0][t + 1]], orc.synth_row(m, thr, 5, int(rows[t])))
+
+
+@pytest.mark.parametrize("n,m,d,arity", [(50_000, 2652, 0.003, 4), (80_000, 1000, 0.004, 2), (30_000, 300, 0.01, 5),
+                                         (20_000, 64, 0.3, 4)])
+def test_leaf_codes_give_the_same_rows(ggq, orc, n, m, d, arity, tmp_path):
+    """Leaf codes (one byte per position of a coded node's child vectors: the single label below it, or 'descend')
+    are an accelerator of the descent, chosen per node at load time.  With codes on and off the engine must return
+    the same rows — order included — the same histograms, and both must match direct evaluation; the image file
+    carries the codes."""
+    rows = np.random.default_rng(11).integers(0, n, 60_000).astype(np.uint64)
+    rows[::777] = np.uint64(n + 5)
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=8, arity=arity)
+    try:
+        info = gm.leaf_codes
+        if d < 0.05:
+            assert info["nodes"] > 0 and info["in_use"] and info["bytes"] > 0, info   # sparse rows: codes must pay
+        with_codes = gm.get_rows_csr(rows)
+        small = gm.get_rows_csr(rows[:50])
+        hist = gm.count_labels(rows)
+        ws = gm.workspace()
+        if info["nodes"]:
+            import torch
+            d_rows = torch.from_numpy(rows.view(np.int64)).cuda()
+            ws.get_rows_device(d_rows.data_ptr(), rows.size, 4)
+            assert ws.stat("code_probes") > 0
+            assert ws.stat("code_escapes") <= ws.stat("code_probes")
+        ws.close()
+        gm.set_option("leaf_codes", 0)
+        assert not gm.leaf_codes["in_use"]
+        plain = gm.get_rows_csr(rows)
+        assert np.array_equal(plain[0], with_codes[0]) and np.array_equal(plain[1], with_codes[1])
+        assert np.array_equal(small[0], plain[0][:51]) and np.array_equal(small[1], plain[1][:int(plain[0][50])])
+        assert np.array_equal(gm.count_labels(rows), hist)
+        assert np.array_equal(hist, np.bincount(plain[1].astype(np.int64), minlength=m).astype(np.uint64))
+        gm.set_option("leaf_codes", 1)
+        again = gm.get_rows_csr(rows)
+        assert np.array_equal(again[0], plain[0]) and np.array_equal(again[1], plain[1])
+        thr = ggq.density_threshold(d)
+        for t in range(0, rows.size, 499):
+            exp = orc.synth_row(m, thr, 8, int(rows[t])) if rows[t] < n else np.zeros(0, np.uint64)
+            assert np.array_equal(plain[1][plain[0][t]:plain[0][t + 1]], exp)
+        img = str(tmp_path / "codes.ggqimg")
+        gm.save_image(img)
+    finally:
+        gm.close()
+    gi = ggq.GpuMatrix.load_image(img)
+    try:
+        assert gi.leaf_codes == info
+        off, cols = gi.get_rows_csr(rows)
+        assert np.array_equal(off, plain[0]) and np.array_equal(cols, plain[1])
+    finally:
+        gi.close()
