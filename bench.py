@@ -449,7 +449,7 @@ def run_ours(args):
                  "get": {"cells": nq, "cells_per_s": nq / tcell, "set_fraction": float(np.mean(cells))}}
 
     # ---- end to end through the host-buffer C ABI ------------------------------------------
-    e2e = e2e_u64 = None
+    e2e = e2e_u32 = e2e_u64 = None
     if not args.no_e2e:
         cap = int(ids / K * 1.05) + 1024
         h_rows = [b.cpu().pin_memory() for b in batches[:min(n_pool, 3)]]
@@ -474,10 +474,49 @@ def run_ours(args):
             return {"value": world * B * Ke / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": B * 8,
                     "d2h_bytes_per_step": d2h // Ke, "steps": Ke, "api": api}
 
-        # headline: compact ids (u32; the engine holds < 2^31 columns) — half the PCIe bytes of the u64 form
+        # headline: the compact call — u32 row ids in (the matrix has < 2^32 rows), u8 per-row counts + u16 column ids
+        # out (< 65536 columns): 22 instead of 56 bytes per row over the host link, same rows (tests/test_synth_gpu.py)
+        compact_ok = n <= 2**32 and args.cols <= 65536
+        if compact_ok:
+            h_rows32 = [torch.from_numpy(r.astype(np.uint32).view(np.int32)).pin_memory() for r in np_rows]
+            np_rows32 = [r.numpy().view(np.uint32) for r in h_rows32]
+            h_cnt8 = torch.empty(B, dtype=torch.uint8).pin_memory()
+            h_cols16 = torch.empty(cap, dtype=torch.int16).pin_memory()
+            np_cnt8, np_cols16 = h_cnt8.numpy(), h_cols16.numpy().view(np.uint16)
+
+            def compact_api():
+                for i in range(We):
+                    gm.get_rows_compact(np_rows32[i % len(np_rows32)], np_cnt8, np_cols16)
+                barrier()
+                tw = time.perf_counter()
+                d2h = 0
+                for i in range(Ke):
+                    total = gm.get_rows_compact(np_rows32[(We + i) % len(np_rows32)], np_cnt8, np_cols16)
+                    d2h += B + total * 2
+                torch.cuda.synchronize()
+                te = torch.tensor([time.perf_counter() - tw], device="cuda", dtype=torch.float64)
+                if dist is not None:
+                    dist.all_reduce(te, op=dist.ReduceOp.MAX)
+                return {"value": world * B * Ke / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": B * 4,
+                        "d2h_bytes_per_step": d2h // Ke, "steps": Ke,
+                        "api": "ggq_get_rows_compact (host u32 row ids in; host u8 per-row counts + u16 column ids out)"}
+
+            e2e = compact_api()
+            # the timed call's last answer against the u32-id call on the same batch (outside the timed region)
+            last = (We + Ke - 1) % len(np_rows32)
+            tot_c = gm.get_rows_compact(np_rows32[last], np_cnt8, np_cols16)
+            chk_cols = np.empty(cap, np.uint32)
+            tot_r = gm.get_rows_into(np_rows[last], np_off, chk_cols)
+            if tot_c != tot_r or not np.array_equal(np_cnt8.astype(np.int64), np.diff(np_off.astype(np.int64))) or \
+                    not np.array_equal(np_cols16[:tot_c], chk_cols[:tot_r].astype(np.uint16)):
+                raise RuntimeError("bench.py: ggq_get_rows_compact differs from ggq_get_rows_into_u32")
+            e2e["identical_to_get_rows_into_u32"] = True
+            del h_cnt8, h_cols16, chk_cols
         h_cols32 = torch.empty(cap, dtype=torch.int32).pin_memory()
-        e2e = host_api(h_cols32.numpy().view(np.uint32), 4,
-                       "ggq_get_rows_into_u32 (host row ids in, host CSR offsets + u32 column ids out)")
+        e2e_u32 = host_api(h_cols32.numpy().view(np.uint32), 4,
+                           "ggq_get_rows_into_u32 (host u64 row ids in, host CSR offsets + u32 column ids out)")
+        if e2e is None:
+            e2e = e2e_u32
         del h_cols32
         h_cols = torch.empty(cap, dtype=torch.int64).pin_memory()
         e2e_u64 = host_api(h_cols.numpy().view(np.uint64), 8,
@@ -546,6 +585,7 @@ def run_ours(args):
         line["other_calls_host_to_host"] = extra
     if e2e is not None:
         line["e2e"] = e2e
+        line["e2e_u32"] = e2e_u32
         line["e2e_u64"] = e2e_u64
     if cl is not None:
         line["count_labels_e2e"] = cl

@@ -91,6 +91,7 @@ def lib():
         "ggq_get_top_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u64p, u64p, u64p]),
         "ggq_get_labels_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p, C.c_uint64, u64p]),
         "ggq_get_rows_into_u32": (C.c_int, [vp, u64p, C.c_uint64, u64p, C.c_void_p, C.c_uint64, u64p]),
+        "ggq_get_rows_compact": (C.c_int, [vp, C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_uint64, u64p]),
         "ggq_count_labels": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
         "ggq_count_labels_device": (C.c_int, [vp, vp, vp, C.c_uint64, C.POINTER(vp)]),
         "ggq_slice_rows": (C.c_int, [vp, u64p, C.c_uint64, C.POINTER(u64p), u64p]),
@@ -370,6 +371,16 @@ class GpuMatrix:
                                            offsets.ctypes.data_as(u64p), cols.ctypes.data_as(u64p),
                                            cols.size, C.byref(n_cols)))
         return n_cols.value
+
+    def get_rows_compact(self, rows, counts, cols):
+        """ggq_get_rows_compact: rows u32 or u64, counts u8 / u16 / u32 (one per row), cols u16 / u32 / u64 — all
+        caller-provided numpy arrays (pinned for speed).  Returns the number of column ids."""
+        assert rows.dtype in (np.uint32, np.uint64) and counts.dtype in (np.uint8, np.uint16, np.uint32)
+        assert cols.dtype in (np.uint16, np.uint32, np.uint64) and counts.size >= rows.size
+        n = C.c_uint64()
+        _check(lib().ggq_get_rows_compact(self._h, rows.ctypes.data, rows.dtype.itemsize, rows.size, counts.ctypes.data,
+                                          counts.dtype.itemsize, cols.ctypes.data, cols.dtype.itemsize, cols.size, C.byref(n)))
+        return n.value
 
     def get_rows(self, rows):
         off, cols = self.get_rows_csr(rows)

@@ -763,6 +763,9 @@ static void brwt_rows_finish(const Matrix *m, Workspace *ws, const u64 *d_rows, 
             if (col_bytes == 8)
                 gather_rows_kernel<u64><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
                                                           reinterpret_cast<u64 *>(ws->d_out.p));
+            else if (col_bytes == 2)
+                gather_rows_kernel<unsigned short><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
+                                                                     reinterpret_cast<unsigned short *>(ws->d_out.p));
             else
                 gather_rows_kernel<u32><<<g, 256, 0, st>>>(ws->d_tmp.p, ws->d_row_tmp_off.p, ws->d_offsets.p, n,
                                                           reinterpret_cast<u32 *>(ws->d_out.p));
@@ -1268,11 +1271,18 @@ static u64 pipeline_chunk() {
 static const u64 kCountChunk = u64(1) << 22;
 static const u64 kPipelineDepth = 4;   // workspaces (streams) a pipelined host call rotates over
 
-static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, void *cols_v,
-                         uint64_t cols_capacity, uint64_t *n_cols, int col_bytes) {
+// rows: u64 ids (row_bytes 8) or u32 ids (4).  Row boundaries come back as CSR offsets (count_bytes 0: n + 1 u64 in
+// `offsets`) or as per-row counts of count_bytes = 1 / 2 / 4 bytes in `counts_v`.  Column ids of col_bytes = 8 / 4 / 2.
+static int get_rows_into(const ggq_matrix *m, const void *rows_v, int row_bytes, uint64_t n, uint64_t *offsets,
+                         void *counts_v, int count_bytes, void *cols_v, uint64_t cols_capacity, uint64_t *n_cols,
+                         int col_bytes) {
     unsigned char *cols = static_cast<unsigned char *>(cols_v);
+    unsigned char *counts = static_cast<unsigned char *>(counts_v);
+    const unsigned char *rows = static_cast<const unsigned char *>(rows_v);
     GGQ_TRY
-    if (!m || !offsets || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (!m || (!offsets && !count_bytes) || (count_bytes && !counts && n) || (!rows && n)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (col_bytes == 2 && m->tree.n_cols > 65536) return fail(GGQ_ERR_ARG, "u16 column ids need a matrix of at most 65536 columns");
+    if (row_bytes == 4 && m->tree.n_rows > (u64(1) << 32)) return fail(GGQ_ERR_ARG, "u32 row ids need a matrix of at most 2^32 rows");
     CUDA_CHECK(cudaSetDevice(m->device));
     // Chunks rotate over kPipelineDepth workspaces (streams).  Chunk k+1 is enqueued (H2D, ordering, descent, scan)
     // BEFORE the host waits for chunk k's size, so the device never idles on a host round trip, and the device->host
@@ -1306,7 +1316,11 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
     if (std::getenv("GGQ_TRACE") && n_chunks > 1 && !g_trace) g_trace = new Trace();
     try {
         const bool room = n_chunks > 1 && !std::getenv("GGQ_NO_PIPE_ROOM");
-        for (auto &p : w) { p = m->acquire(); p->pipelined = room; }
+        for (auto &p : w) {
+            p = m->acquire();
+            p->pipelined = room;
+            if (count_bytes) CUDA_CHECK(cudaMemsetAsync(p->d_err.p, 0, sizeof(int), p->stream));
+        }
         u64 base = 0;
         bool fits = true;
         int launches = 0;
@@ -1318,7 +1332,14 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             ws->reserve_rows(nc);
             g_trace_chunk = k;
             GGQ_MARK(ws->stream, "begin");
-            if (nc) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + start[k], nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            if (nc && row_bytes == 8) {
+                CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows + start[k] * 8, nc * 8, cudaMemcpyHostToDevice, ws->stream));
+            } else if (nc) {
+                if (ws->d_rows32.n < nc) ws->d_rows32.alloc(ws->cap_rows);
+                CUDA_CHECK(cudaMemcpyAsync(ws->d_rows32.p, rows + start[k] * 4, nc * 4, cudaMemcpyHostToDevice, ws->stream));
+                widen_rows_kernel<<<u32((nc + 255) / 256), 256, 0, ws->stream>>>(ws->d_rows32.p, nc, ws->d_rows.p);
+                CUDA_CHECK(cudaGetLastError());
+            }
             GGQ_MARK(ws->stream, "h2d");
             if (brwt) brwt_rows_begin(m, ws, ws->d_rows.p, nc);
         };
@@ -1333,25 +1354,47 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
             else rows_device(m, ws, ws->d_rows.p, nc, col_bytes, &total);
             GGQ_MARK(ws->stream, "gather");
             launches += ws->launches; probes += ws->last_probes; touches += ws->last_touches;
-            if (base) {
-                add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
+            if (count_bytes && nc) {   // per-row counts, narrowed on the device (colmajor: from the offsets)
+                if (ws->d_cnt_out.n < size_t(nc) * 4) ws->d_cnt_out.alloc(size_t(ws->cap_rows) * 4);
+                if (!brwt) {
+                    offsets_to_counts_kernel<<<u32((nc + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc, ws->d_row_cnt.p);
+                }
+                u32 *flag = reinterpret_cast<u32 *>(ws->d_err.p);   // sticky over the chunks of this call
+                const u32 g = u32((nc + 255) / 256);
+                if (count_bytes == 1) narrow_counts_kernel<unsigned char><<<g, 256, 0, ws->stream>>>(ws->d_row_cnt.p, nc, ws->d_cnt_out.p, flag);
+                else if (count_bytes == 2) narrow_counts_kernel<unsigned short><<<g, 256, 0, ws->stream>>>(ws->d_row_cnt.p, nc, reinterpret_cast<unsigned short *>(ws->d_cnt_out.p), flag);
+                else narrow_counts_kernel<u32><<<g, 256, 0, ws->stream>>>(ws->d_row_cnt.p, nc, reinterpret_cast<u32 *>(ws->d_cnt_out.p), flag);
                 CUDA_CHECK(cudaGetLastError());
                 ++launches;
+                CUDA_CHECK(cudaMemcpyAsync(counts + r0 * count_bytes, ws->d_cnt_out.p, nc * count_bytes, cudaMemcpyDeviceToHost, ws->stream));
+            } else if (!count_bytes) {
+                if (base) {
+                    add_base_kernel<<<u32((nc + 1 + 255) / 256), 256, 0, ws->stream>>>(ws->d_offsets.p, nc + 1, base);
+                    CUDA_CHECK(cudaGetLastError());
+                    ++launches;
+                }
+                CUDA_CHECK(cudaMemcpyAsync(offsets + r0, ws->d_offsets.p, (nc + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
             }
-            CUDA_CHECK(cudaMemcpyAsync(offsets + r0, ws->d_offsets.p, (nc + 1) * 8, cudaMemcpyDeviceToHost, ws->stream));
             if (base + total > cols_capacity || (total && !cols)) fits = false;
             if (fits && total)
                 CUDA_CHECK(cudaMemcpyAsync(cols + base * col_bytes, ws->d_out.p, total * col_bytes, cudaMemcpyDeviceToHost, ws->stream));
             GGQ_MARK(ws->stream, "d2h");
             base += total;
         }
+        if (count_bytes)
+            for (Workspace *ws : w)
+                CUDA_CHECK(cudaMemcpyAsync(ws->h_ctrl + 16, ws->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, ws->stream));
         for (Workspace *ws : w)
             if (ws) CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+        bool count_overflow = false;
+        if (count_bytes)
+            for (Workspace *ws : w) count_overflow |= *reinterpret_cast<const int *>(ws->h_ctrl + 16) != 0;
         if (g_trace) { g_trace->dump(); delete g_trace; g_trace = nullptr; }
         w[0]->launches = launches; w[0]->last_probes = probes; w[0]->last_touches = touches;
         m->last_probes = probes;
         if (n_cols) *n_cols = base;
         if (!fits) rc = fail(GGQ_ERR_ARG, "cols_capacity too small");
+        else if (count_overflow) rc = fail(GGQ_ERR_LIMIT, "a row has more columns than count_bytes can hold (counts are saturated)");
     } catch (...) {
         for (Workspace *ws : w)
             if (ws) { cudaStreamSynchronize(ws->stream); m->release(ws); }
@@ -1366,12 +1409,20 @@ static int get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, 
 
 int ggq_get_rows_into(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint64_t *cols,
                       uint64_t cols_capacity, uint64_t *n_cols) {
-    return get_rows_into(m, rows, n, offsets, cols, cols_capacity, n_cols, 8);
+    return get_rows_into(m, rows, 8, n, offsets, nullptr, 0, cols, cols_capacity, n_cols, 8);
+}
+
+int ggq_get_rows_compact(const ggq_matrix *m, const void *rows, int row_bytes, uint64_t n, void *counts, int count_bytes,
+                         void *cols, int col_bytes, uint64_t cols_capacity, uint64_t *n_cols) {
+    if ((row_bytes != 4 && row_bytes != 8) || (count_bytes != 1 && count_bytes != 2 && count_bytes != 4) ||
+        (col_bytes != 2 && col_bytes != 4 && col_bytes != 8))
+        return fail(GGQ_ERR_ARG, "row_bytes must be 4 or 8, count_bytes 1, 2 or 4, col_bytes 2, 4 or 8");
+    return get_rows_into(m, rows, row_bytes, n, nullptr, counts, count_bytes, cols, cols_capacity, n_cols, col_bytes);
 }
 
 int ggq_get_rows_into_u32(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t *offsets, uint32_t *cols,
                           uint64_t cols_capacity, uint64_t *n_cols) {
-    return get_rows_into(m, rows, n, offsets, cols, cols_capacity, n_cols, 4);
+    return get_rows_into(m, rows, 8, n, offsets, nullptr, 0, cols, cols_capacity, n_cols, 4);
 }
 
 static void launch_col_hist(const ggq_matrix *m, Workspace *ws, const u32 *ids, u64 total, u64 *d_counts) {

@@ -123,7 +123,8 @@ struct Workspace {
     const Matrix *m;
     cudaStream_t stream = nullptr;
     DeviceBuf<u64> d_rows, d_row_tmp_off, d_offsets, d_bytes8, d_ctrl, d_spill;
-    DeviceBuf<u32> d_row_cnt, d_tmp, d_iota, d_perm;
+    DeviceBuf<u32> d_row_cnt, d_tmp, d_iota, d_perm, d_rows32;   // d_rows32: u32 row ids of the compact host call
+    DeviceBuf<unsigned char> d_cnt_out;                          // narrowed per-row counts of the compact host call
     DeviceBuf<u64> d_rows_sorted;
     DeviceBuf<unsigned char> d_sort_tmp;
     size_t sort_tmp_bytes = 0;

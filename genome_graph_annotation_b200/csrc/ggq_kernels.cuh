@@ -562,6 +562,25 @@ __global__ void add_base_kernel(u64 *p, u64 n, u64 base) {
     if (i < n) p[i] += base;
 }
 
+// compact host API: u32 row ids in, per-row counts narrowed to 1 / 2 / 4 bytes out (flag[0] |= 1 if one does not fit)
+__global__ void widen_rows_kernel(const u32 *in, u64 n, u64 *out) {
+    u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i];
+}
+__global__ void offsets_to_counts_kernel(const u64 *off, u64 n, u32 *cnt) {
+    u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) cnt[i] = u32(off[i + 1] - off[i]);
+}
+template <typename T>
+__global__ void narrow_counts_kernel(const u32 *cnt, u64 n, T *out, u32 *flag) {
+    u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 c = cnt[i];
+    const u32 lim = sizeof(T) >= 4 ? 0xFFFFFFFFu : (1u << (8 * sizeof(T))) - 1u;
+    if (c > lim) atomicOr(flag, 1u);
+    out[i] = T(c < lim ? c : lim);
+}
+
 // slice_rows: CSR -> rows separated by UINT64_MAX
 __global__ void slice_rows_kernel(const u64 *offsets, const u32 *cols, u64 n, u64 *out) {
     u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x;

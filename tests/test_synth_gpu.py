@@ -368,3 +368,51 @@ def test_leaf_codes_give_the_same_rows(ggq, orc, n, m, d, arity, tmp_path):
         assert np.array_equal(off, plain[0]) and np.array_equal(cols, plain[1])
     finally:
         gi.close()
+
+
+@pytest.mark.parametrize("n,m,d", [(3_000_000, 2652, 0.003), (50_000, 300, 0.02), (5_000, 70_000, 0.0002)])
+def test_compact_host_call_matches_get_rows_into(ggq, n, m, d):
+    """ggq_get_rows_compact (u32 row ids in, u8 / u16 counts and u16 / u32 ids out) returns exactly the CSR of
+    ggq_get_rows_into: counts = differences of its offsets, ids bit-identical, for batches below and above the
+    pipelining threshold; too-narrow count or id types are refused, never truncated."""
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=12, arity=4)
+    try:
+        for nq in (1, 777, 2_500_000):
+            rows = np.random.default_rng(nq).integers(0, n, nq).astype(np.uint64)
+            rows[::1001] = np.uint64(n + 1)
+            off = np.zeros(nq + 1, np.uint64)
+            cap = int(nq * (m * d * 1.5 + 4)) + 64
+            cols = np.zeros(cap, np.uint64)
+            tot = gm.get_rows_into(rows, off, cols)
+            for rdt in (np.uint32, np.uint64):
+                for cdt in (np.uint8, np.uint16, np.uint32):
+                    for idt in ((np.uint16, np.uint32, np.uint64) if m <= 65536 else (np.uint32, np.uint64)):
+                        if nq > 1000 and (rdt, cdt, idt) not in ((np.uint32, np.uint8, np.uint16 if m <= 65536 else np.uint32),
+                                                                 (np.uint64, np.uint32, np.uint64)):
+                            continue   # every combination on the small batches, two on the large one
+                        cnt = np.zeros(nq, cdt)
+                        ids = np.zeros(cap, idt)
+                        r = rows.astype(rdt) if rdt == np.uint64 or n + 1 < 2**32 else rows
+                        got = gm.get_rows_compact(r, cnt, ids)
+                        assert got == tot
+                        assert np.array_equal(cnt.astype(np.int64), np.diff(off.astype(np.int64)))
+                        assert np.array_equal(ids[:tot].astype(np.uint64), cols[:tot])
+        if m > 65536:
+            with pytest.raises(ggq.GgqError):
+                gm.get_rows_compact(rows[:10].astype(np.uint32), np.zeros(10, np.uint8), np.zeros(100, np.uint16))
+    finally:
+        gm.close()
+    # a row with more ids than a u8 count can hold: GGQ_ERR_LIMIT, and it works with u16 counts
+    gd = ggq.GpuMatrix.synthesize_brwt(2_000, 600, 0.9, seed=1, arity=4)
+    try:
+        rows = np.arange(100, dtype=np.uint32)
+        with pytest.raises(ggq.GgqError) as e:
+            gd.get_rows_compact(rows, np.zeros(100, np.uint8), np.zeros(100 * 600, np.uint16))
+        assert e.value.code == -5   # GGQ_ERR_LIMIT
+        cnt = np.zeros(100, np.uint16)
+        ids = np.zeros(100 * 600, np.uint16)
+        tot = gd.get_rows_compact(rows, cnt, ids)
+        o, c = gd.get_rows_csr(rows.astype(np.uint64))
+        assert tot == c.size and np.array_equal(cnt, np.diff(o.astype(np.int64)).astype(np.uint16)) and np.array_equal(ids[:tot], c.astype(np.uint16))
+    finally:
+        gd.close()
