@@ -268,6 +268,19 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
             cap_s = std::max<u32>(rb + 2, std::min<u32>(cap_s, env_u32("GGQ_STACK_UNDERESTIMATE", 0)) & ~1u);
     }
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
+    if (cap_spill == 0 && !env_u32("GGQ_STACK_UNDERESTIMATE", 0)) {
+        // The 8 entries of slack above the replayed stack height are a courtesy, not a guarantee (the kernel checks):
+        // give some of them up when that is what keeps one more CTA resident per SM (C4: 6 instead of 5).
+        const u32 worst = (std::max<u32>(simulate_stack(tree, rb, kItemsPerIter) + 2, 32) + 1) & ~1u;
+        int occ_tight = per_sm;
+        if (worst < cap_s)
+            CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_tight, fn, kRowsWarps * 32, rows_smem_bytes(worst, rb, bm_words)));
+        while (occ_tight > per_sm && cap_s > worst) {
+            cap_s -= 2;
+            rows_smem = rows_smem_bytes(cap_s, rb, bm_words);
+            CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kRowsWarps * 32, rows_smem));
+        }
+    }
     if (per_sm < 1) per_sm = 1;
     rows_grid = u32(sm_count * per_sm);
     rows_grid_p = rows_grid;
@@ -638,7 +651,9 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
         if (ws->d_spill.n < need) { CUDA_CHECK(cudaStreamSynchronize(ws->stream)); ws->d_spill.alloc(need); }
     }
     a.spill = ws->d_spill.p; a.cap_s = m->cap_s; a.cap_spill = cap_spill;
-    a.bm_words = m->bm_words; a.rb = m->rb; a.err = reinterpret_cast<int *>(ws->d_ctrl.p + 4);
+    a.bm_words = m->bm_words; a.rb = m->rb;
+    a.sum_words = rows_sum_words(m->bm_words); a.sum_magic = u32((u64(1) << 32) / a.sum_words) + 1u;
+    a.err = reinterpret_cast<int *>(ws->d_ctrl.p + 4);
     a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
     a.root_base = m->root_base; a.any_more = m->any_more;
     u64 batches = (n + m->rb - 1) / m->rb;

@@ -11,7 +11,8 @@
 // column's DFS rank in the row's bitmap (shared memory) and bumps the row's counter; a set bit of an internal
 // child pushes the child's first group with r' = rank1(r) - 1.  When the stack drains, the bitmaps of the tile
 // are scanned once in (row, word) order — which IS the reference's output order (DFS over child_nodes_,
-// BRWT.cpp:45-50) — non-zero words go through a 32-entry warp queue and are expanded a queue at a time.
+// BRWT.cpp:45-50) — through per-row summary words (one bit per non-zero bitmap word), so that only the ~8 words
+// per row that hold an id are visited instead of all 83.
 //
 // v3 vs v2 (profiles/r01: the kernel is instruction-issue bound, 27 warp instructions per probe): the two
 // children of a lane are handled without divergent branches (rank computed unconditionally, leaf marks
@@ -28,7 +29,6 @@ constexpr int kRowsWarps = 8;          // warps per CTA of the descent kernel
 // and iteration (two independent slot loads in flight per lane, 64 registers -> 4 CTAs/SM instead of 6) was measured
 // slower on B200: 12.3 vs 11.8 ms on the C4 shape at 1e9 rows.
 constexpr int kItemsPerIter = 16;
-constexpr int kEmitQueue = 32;         // entries of the per-warp queue of non-zero bitmap words
 constexpr int kRowCounters = 16;       // per-warp row counters (>= kMaxRowsPerWarp)
 constexpr int kStatCounters = 4;       // per-warp kernel statistics: code probes, code escapes (flushed at kernel end)
 constexpr u32 kCodeEscape = 255;       // leaf code "more than one leaf set below: descend"
@@ -47,6 +47,8 @@ struct RowsArgs {
     u64 *spill;               // per-warp stack overflow area (cap_spill entries each)
     u32 cap_s, cap_spill;     // shared / global stack capacity per warp
     u32 bm_words;             // bitmap words per row
+    u32 sum_words;            // summary words per row = ceil(bm_words / 32)
+    u32 sum_magic;            // floor(2^32 / sum_words) + 1: e / sum_words by one mulhi
     u32 rb;                   // rows per warp tile
     // root fast path: the root is a group of one vector; when it is internal the seeding step probes it directly
     // (one 16-byte slot per row, all lanes busy) instead of spending a whole stack iteration on rb items
@@ -59,10 +61,14 @@ struct RowsArgs {
 };
 constexpr u32 kNoRootFast = 0xFFFFFFFFu;
 
-// Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][queues: warps x 32 u64][per warp: rb*bm_words
-// bitmap words + 16 row counters + 4 statistics counters (u32)]
+// Dynamic shared memory of one CTA: [stacks: warps x cap_s u64][per warp: rb*bm_words bitmap words + rb*sum_words
+// summary words + 16 row counters + 4 statistics counters (u32), padded to 16 bytes]
+inline u32 rows_sum_words(u32 bm_words) { return (bm_words + 31) / 32; }
+inline u32 rows_warp_words(u32 rb, u32 bm_words) {
+    return (rb * (bm_words + rows_sum_words(bm_words)) + kRowCounters + kStatCounters + 3u) & ~3u;
+}
 inline size_t rows_smem_bytes(u32 cap_s, u32 rb, u32 bm_words) {
-    return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(kEmitQueue) * 8 + (size_t(rb) * bm_words + kRowCounters + kStatCounters) * 4);
+    return size_t(kRowsWarps) * (size_t(cap_s) * 8 + size_t(rows_warp_words(rb, bm_words)) * 4);
 }
 
 // Shared memory through 32-bit shared-window addresses (computed once per kernel).
@@ -104,45 +110,22 @@ __device__ __forceinline__ u32 slot_ones_before(const uint4 &s, u32 w, u32 wsel,
 }
 
 // Set bit of a leaf child: mark the DFS ranks of its columns in the row's bitmap, bump the row's counter.
+// Besides the bitmap bit, a mark sets bit (word index & 31) of the row's summary word (word index >> 5): the emit
+// visits only the bitmap words that are not zero.
 template <bool MULTI_LEAF>
-__device__ __forceinline__ void mark_leaf(const Img &img, u32 rank, u32 li, u32 bm_row, u32 cnt_addr) {
+__device__ __forceinline__ void mark_leaf(const Img &img, u32 rank, u32 li, u32 bm_row, u32 sum_row, u32 cnt_addr) {
     if (!MULTI_LEAF) {
         reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
+        reds_or(sum_row + (rank >> 10) * 4, 1u << ((rank >> 5) & 31));
         reds_add(cnt_addr, 1u);
     } else {
         const u32 ncol = __ldg(img.lane_aux + li);
-        for (u32 k = 0; k < ncol; ++k, ++rank) reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
+        for (u32 k = 0; k < ncol; ++k, ++rank) {
+            reds_or(bm_row + (rank >> 5) * 4, 1u << (rank & 31));
+            reds_or(sum_row + (rank >> 10) * 4, 1u << ((rank >> 5) & 31));
+        }
         reds_add(cnt_addr, ncol);
     }
-}
-
-// Expand `cnt` (<= 32) queued non-zero bitmap words (entry = word index within the row << 32 | bits), in queue
-// order, to column ids at tmp_cols[pos...] (only if `store`); returns the number of ids.
-__device__ __forceinline__ u32 emit_flush(const Img &img, u32 que, u32 cnt, u32 lane, u32 lt_mask, u32 *tmp_cols, u64 pos,
-                                          bool store) {
-    u64 e = 0;
-    if (lane < cnt) e = lds64(que + lane * 8);
-    u32 bits = u32(e);
-    const u32 w = u32(e >> 32);
-    const u32 c = __popc(bits);
-    if (!__any_sync(0xffffffffu, c > 1)) {   // common case: one id per word
-        const u32 nz = __ballot_sync(0xffffffffu, c != 0);
-        if (c && store) tmp_cols[pos + __popc(nz & lt_mask)] = __ldg(img.leaf_col + w * 32 + __ffs(bits) - 1);
-        return __popc(nz);
-    }
-    u32 inc = c;
-    #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-    }
-    u64 p = pos + inc - c;
-    while (bits && store) {
-        const u32 b = __ffs(bits) - 1;
-        bits &= bits - 1;
-        tmp_cols[p++] = __ldg(img.leaf_col + w * 32 + b);
-    }
-    return __shfl_sync(0xffffffffu, inc, 31);
 }
 
 // Group record seen by one lane: where the group's blocks are, its shape flags (stride_log2 | cnt << 2 | more << 5 |
@@ -197,17 +180,19 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     const u32 lt_mask = (1u << lane) - 1u;
     const u32 bm_total = a.rb * a.bm_words;
     const u32 smem0 = u32(__cvta_generic_to_shared(smem_raw));
+    const u32 sum_total = a.rb * a.sum_words;
+    const u32 warp_words = (bm_total + sum_total + kRowCounters + kStatCounters + 3u) & ~3u;
     u32 stk = smem0 + warp * a.cap_s * 8;
-    u32 que = smem0 + kRowsWarps * a.cap_s * 8 + warp * (kEmitQueue * 8);
-    u32 bm = smem0 + kRowsWarps * (a.cap_s * 8 + kEmitQueue * 8) + warp * ((bm_total + kRowCounters + kStatCounters) * 4);
-    u32 cnt0 = bm + bm_total * 4;
+    u32 bm = smem0 + kRowsWarps * a.cap_s * 8 + warp * warp_words * 4;
+    u32 sum0 = bm + bm_total * 4;
+    u32 cnt0 = sum0 + sum_total * 4;
     // keep the per-warp bases in registers: ptxas otherwise rematerialises them (S2R + IMAD chains) inside the
     // descent loop, which is instruction-issue bound; a shuffle is opaque to it
     stk = __shfl_sync(0xffffffffu, stk, lane);
-    que = __shfl_sync(0xffffffffu, que, lane);
     bm = __shfl_sync(0xffffffffu, bm, lane);
+    sum0 = __shfl_sync(0xffffffffu, sum0, lane);
     cnt0 = __shfl_sync(0xffffffffu, cnt0, lane);
-    const u32 bm_row_bytes = a.bm_words * 4;
+    const u32 bm_row_bytes = a.bm_words * 4, sum_row_bytes = a.sum_words * 4;
     const u32 stat0 = cnt0 + kRowCounters * 4;
     u64 *spill = SPILL ? a.spill + (size_t(blockIdx.x) * kRowsWarps + warp) * a.cap_spill : nullptr;
     const u32 cap_total = a.cap_s + a.cap_spill;
@@ -217,7 +202,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
     u32 touches = 0;   // per lane: sibling vectors bit-tested (= V_t of SURVEY.md 8d, summed)
 
     // bitmaps and counters start clean; every tile leaves them clean
-    for (u32 i = lane; i < bm_total + kRowCounters + kStatCounters; i += 32) sts32(bm + i * 4, 0);
+    for (u32 i = lane; i < warp_words; i += 32) sts32(bm + i * 4, 0);
     __syncwarp();
 
     for (;;) {
@@ -300,9 +285,9 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                     const bool set1 = (2 * half + 1 < cnt) && ((w1 >> sh) & 1u);
                     const bool leaf0 = child0 & Fmt::kLeaf, leaf1 = child1 & Fmt::kLeaf;
                     const u32 t = tq >> kItemGroupBits;
-                    const u32 bm_row = bm + t * bm_row_bytes;
-                    if (set0 && leaf0 && child0 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child0 & (Fmt::kLeaf - 1u), g * 4 + 2 * half, bm_row, cnt0 + t * 4);
-                    if (set1 && leaf1 && child1 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child1 & (Fmt::kLeaf - 1u), g * 4 + 2 * half + 1, bm_row, cnt0 + t * 4);
+                    const u32 bm_row = bm + t * bm_row_bytes, sum_row = sum0 + t * sum_row_bytes;
+                    if (set0 && leaf0 && child0 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child0 & (Fmt::kLeaf - 1u), g * 4 + 2 * half, bm_row, sum_row, cnt0 + t * 4);
+                    if (set1 && leaf1 && child1 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child1 & (Fmt::kLeaf - 1u), g * 4 + 2 * half + 1, bm_row, sum_row, cnt0 + t * 4);
                     push0 = set0 && !leaf0;
                     push1 = set1 && !leaf1;
                     // r' = rank1(r) - 1 = ones strictly before r (BRWT.cpp:43-50)
@@ -328,10 +313,11 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                                 code1 = ld_code(img.codes + ((u64(cr.y) << 32) | cr.x) + ones1);
                                 lr1 = cr.z;
                             }
-                            if (code0 != kCodeEscape) { mark_leaf<false>(img, lr0 + code0, 0, bm_row, cnt0 + t * 4); push0 = false; }
-                            if (code1 != kCodeEscape) { mark_leaf<false>(img, lr1 + code1, 0, bm_row, cnt0 + t * 4); push1 = false; }
+                            if (code0 != kCodeEscape) { mark_leaf<false>(img, lr0 + code0, 0, bm_row, sum_row, cnt0 + t * 4); push0 = false; }
+                            if (code1 != kCodeEscape) { mark_leaf<false>(img, lr1 + code1, 0, bm_row, sum_row, cnt0 + t * 4); push1 = false; }
                             reds_add(stat0, u32(c0) + u32(c1));                                          // code probes
-                            reds_add(stat0 + 4, u32(c0 && push0) + u32(c1 && push1));                    // escapes
+                            const u32 esc = u32(c0 && push0) + u32(c1 && push1);
+                            if (esc) reds_add(stat0 + 4, esc);                                           // escapes
                         }
                     }
                     item0 = (ones0 << kItemRShift) | tq | child0;   // (only pushed for internal children: plain group index)
@@ -385,35 +371,44 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             a.row_cnt[q] = my_cnt;
         }
         if (total) {
+            // Lane e of a pass owns summary word e = (row t, word group wg): it walks the set bits of the summary —
+            // the non-zero bitmap words wg*32 + b of row t — once to count its ids and once to store them.  Flat
+            // order (t, wg, b, bit) IS (row, rank) order, the reference's output order (BRWT.cpp:45-50).  Summary and
+            // bitmap words are cleared as they are read: the next tile starts clean.
             const bool fits = base + total <= a.tmp_cap;   // else: the engine grows the arena and reruns
-            const u32 rows_mask = __ballot_sync(0xffffffffu, my_cnt != 0);
+            const u32 n_sum = nr * a.sum_words;
             u64 pos = base;
-            u32 q = 0;
-            for (u32 t = 0; t < nr; ++t) {
-                if (!((rows_mask >> t) & 1u)) continue;
-                const u32 bm_row = bm + t * bm_row_bytes;
-                for (u32 w0 = 0; w0 < a.bm_words; w0 += 32) {
-                    const u32 w = w0 + lane;
-                    const u32 bits = w < a.bm_words ? lds32(bm_row + w * 4) : 0u;
-                    const u32 nz = __ballot_sync(0xffffffffu, bits != 0);
-                    if (!nz) continue;
-                    const u32 add = __popc(nz);
-                    if (q + add > kEmitQueue) {   // no room: expand what is queued (reads before the writes below)
-                        __syncwarp();
-                        pos += emit_flush(img, que, q, lane, lt_mask, a.tmp_cols, pos, fits);
-                        q = 0;
-                        __syncwarp();
-                    }
-                    if (bits) {
-                        sts32(bm_row + w * 4, 0);
-                        sts64(que + (q + __popc(nz & lt_mask)) * 8, (u64(w) << 32) | bits);
-                    }
-                    q += add;
+            for (u32 e0 = 0; e0 < n_sum; e0 += 32) {
+                const u32 e = e0 + lane;
+                u32 sm = 0;
+                if (e < n_sum) sm = lds32(sum0 + e * 4);
+                if (!__any_sync(0xffffffffu, sm != 0)) continue;
+                if (sm) sts32(sum0 + e * 4, 0);
+                const u32 t = a.sum_words == 1 ? e : __umulhi(e, a.sum_magic);
+                const u32 wg = e - t * a.sum_words;
+                const u32 words = bm + t * bm_row_bytes + wg * 128;   // bitmap word wg*32 of row t
+                u32 c = 0;
+                for (u32 x = sm; x; x &= x - 1) c += __popc(lds32(words + (__ffs(x) - 1) * 4));
+                u32 inc = c;
+                #pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const u32 v = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += v;
                 }
-            }
-            if (q) {
-                __syncwarp();
-                emit_flush(img, que, q, lane, lt_mask, a.tmp_cols, pos, fits);
+                u64 p = pos + inc - c;
+                for (u32 x = sm; x; x &= x - 1) {
+                    const u32 b = __ffs(x) - 1;
+                    u32 bits = lds32(words + b * 4);
+                    sts32(words + b * 4, 0);
+                    const u32 *col = img.leaf_col + (wg * 32 + b) * 32;
+                    while (bits) {
+                        const u32 bit = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        if (fits) a.tmp_cols[p] = __ldg(col + bit);
+                        ++p;
+                    }
+                }
+                pos += __shfl_sync(0xffffffffu, inc, 31);
             }
         }
         __syncwarp();

@@ -19,3 +19,16 @@ def test_cpp_adapters_match_reference():
     p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert p.returncode == 0, p.stdout[-3000:]
     assert "all checks passed" in p.stdout
+
+
+def test_reference_annotator_instantiated_over_the_gpu_matrix():
+    """annotate::StaticBinRelAnnotator<ggq::GpuBRWT, std::string> — the reference's own caller template over the GPU
+    matrix (tests/cpp/annotator_test.cpp): loads the .brwt.annodbg the reference wrote, and answers the known-answer
+    cases of the reference's tests/test_annotation_BRWT.cpp (get / has_labels / get_top_labels = Label2:4, Label8:3,
+    Label1:2, Label0:1 / get_labels at every ratio) plus a random annotation against the reference annotator."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "annotator_test")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/annotator_test not built (needs /root/reference at build time)")
+    p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:]
+    assert "all checks passed" in p.stdout
