@@ -90,6 +90,7 @@ def lib():
         "ggq_get_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p]),
         "ggq_get_top_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_uint64, u64p, u64p, u64p]),
         "ggq_get_labels_batch": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p, C.c_uint64, u64p]),
+        "ggq_get_labels_batch_ratios": (C.c_int, [vp, u64p, u64p, C.c_uint64, C.POINTER(C.c_double), u64p, u64p, u64p, C.c_uint64, u64p]),
         "ggq_get_rows_into_u32": (C.c_int, [vp, u64p, C.c_uint64, u64p, C.c_void_p, C.c_uint64, u64p]),
         "ggq_get_rows_compact": (C.c_int, [vp, C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_uint64, u64p]),
         "ggq_count_labels": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
@@ -118,6 +119,8 @@ def lib():
         "ggq_bv_rank1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
         "ggq_bv_select1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
         "ggq_bv_get_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
+        "ggq_map_rank1": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p]),
+        "ggq_map_rank1_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
         "ggq_bv_rank0": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
         "ggq_bv_select0": (C.c_int, [vp, u64p, C.c_uint64, u64p]),
         "ggq_bv_rank0_device": (C.c_int, [vp, vp, C.c_uint64, vp, vp]),
@@ -407,8 +410,9 @@ class GpuMatrix:
         return cols[:k.value], cnt[:k.value]
 
     def get_labels_batch(self, rows, query_offsets, presence_ratio=0.0, capacity=None):
-        """get_labels for many queries in one launch (ggq_get_labels_batch): query q owns
-        rows[query_offsets[q]:query_offsets[q+1]].  Returns (label_offsets, cols, counts)."""
+        """get_labels for many queries in one launch (ggq_get_labels_batch / _ratios): query q owns
+        rows[query_offsets[q]:query_offsets[q+1]]; presence_ratio is one number or one per query.
+        Returns (label_offsets, cols, counts)."""
         rows, rp = _u64(rows)
         qo, qp = _u64(query_offsets)
         nq = qo.size - 1
@@ -416,8 +420,15 @@ class GpuMatrix:
             capacity = max(nq * int(self.num_columns), 1)
         loff = np.zeros(nq + 1, np.uint64)
         cols, cnt, k = np.zeros(capacity, np.uint64), np.zeros(capacity, np.uint64), C.c_uint64()
-        _check(lib().ggq_get_labels_batch(self._h, rp, qp, nq, float(presence_ratio), loff.ctypes.data_as(u64p),
-                                          cols.ctypes.data_as(u64p), cnt.ctypes.data_as(u64p), capacity, C.byref(k)))
+        if np.ndim(presence_ratio) == 0:
+            _check(lib().ggq_get_labels_batch(self._h, rp, qp, nq, float(presence_ratio), loff.ctypes.data_as(u64p),
+                                              cols.ctypes.data_as(u64p), cnt.ctypes.data_as(u64p), capacity, C.byref(k)))
+        else:
+            pr = np.ascontiguousarray(presence_ratio, dtype=np.float64)
+            assert pr.size == nq
+            _check(lib().ggq_get_labels_batch_ratios(self._h, rp, qp, nq, pr.ctypes.data_as(C.POINTER(C.c_double)),
+                                                     loff.ctypes.data_as(u64p), cols.ctypes.data_as(u64p),
+                                                     cnt.ctypes.data_as(u64p), capacity, C.byref(k)))
         return loff, cols[:k.value], cnt[:k.value]
 
     def get_top_labels(self, rows, num_top):
@@ -617,6 +628,15 @@ class GpuBitVector:
         out = np.empty(q.size, dtype=np.uint8)
         _check(lib().ggq_bv_get(self._h, qp, q.size, out.ctypes.data_as(u8p)))
         return out
+
+    def map_rank1(self, q):
+        """graph index -> annotation row (AnnotatedDBG::graph_to_anno_index): rank1(i) - 1, UINT64_MAX where unset.
+        Returns (anno_idx, n_unmapped)."""
+        q, qp = _u64(q)
+        out = np.empty(q.size, dtype=np.uint64)
+        bad = C.c_uint64()
+        _check(lib().ggq_map_rank1(self._h, qp, q.size, out.ctypes.data_as(u64p), C.byref(bad)))
+        return out, bad.value
 
     def rank0(self, q):
         q, qp = _u64(q)

@@ -215,6 +215,11 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     int sms = 148;
     CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     size_t smem = size_t(kBuildWarps) * std::max<u32>(NI, 1) * 4;
+    {
+        int max_smem = 0;
+        CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+        if (smem > size_t(max_smem)) throw LimitError("too many internal nodes for the device builder (benchmark harness)");
+    }
     CUDA_CHECK(cudaFuncSetAttribute(brwt_build_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     CUDA_CHECK(cudaFuncSetAttribute(brwt_build_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     int per_sm = 1;

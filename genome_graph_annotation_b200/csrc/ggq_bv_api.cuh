@@ -3,7 +3,7 @@
 
 namespace ggq {
 
-enum BvOp { OP_RANK1 = 0, OP_SELECT1 = 1, OP_GET = 2, OP_RANK0 = 3, OP_SELECT0 = 4, OP_GETINT = 5, OP_WORDS = 6 };
+enum BvOp { OP_RANK1 = 0, OP_SELECT1 = 1, OP_GET = 2, OP_RANK0 = 3, OP_SELECT0 = 4, OP_GETINT = 5, OP_WORDS = 6, OP_MAPRANK = 7 };
 
 struct BvImg {
     int kind;
@@ -103,6 +103,16 @@ __global__ void __launch_bounds__(256) bv_aux_kernel(BvImg v, const u64 *q, cons
             for (u32 j = 0; j < w && j < 64 && x + j < v.n_bits; ++j) {
                 bv_rank1_incl<KIND>(v, T, x + j, &bit);
                 res |= u64(bit) << j;
+            }
+        } else if (OP == OP_MAPRANK) {
+            // AnnotatedDBG::graph_to_anno_index (common/annotated_dbg.cpp:142-156): rank1(i) - 1 where the mask is set;
+            // the reference throws where it is not — here such an index maps to UINT64_MAX, which every row query
+            // treats as an empty row
+            const u64 x = q[t];
+            res = ~0ull;
+            if (x < v.n_bits) {
+                const u64 r = bv_rank1_incl<KIND>(v, T, x, &bit);
+                if (bit) res = r - 1;
             }
         } else {   // OP_WORDS: word t of the plain bits
             for (u32 j = 0; j < 64 && t * 64 + j < v.n_bits; ++j) {
@@ -279,6 +289,7 @@ struct BitVec {
             if (op == OP_RANK0) bv_aux_kernel<KIND, OP_RANK0><<<grid, 256, 0, st>>>(img, q, nullptr, 0, n, o);
             else if (op == OP_SELECT0) bv_aux_kernel<KIND, OP_SELECT0><<<grid, 256, 0, st>>>(img, q, nullptr, 0, n, o);
             else if (op == OP_GETINT) bv_aux_kernel<KIND, OP_GETINT><<<grid, 256, 0, st>>>(img, q, nullptr, aux_width, n, o);
+            else if (op == OP_MAPRANK) bv_aux_kernel<KIND, OP_MAPRANK><<<grid, 256, 0, st>>>(img, q, nullptr, 0, n, o);
             else bv_aux_kernel<KIND, OP_WORDS><<<grid, 256, 0, st>>>(img, nullptr, nullptr, 0, n, o);
             CUDA_CHECK(cudaGetLastError());
             return;
@@ -459,6 +470,18 @@ static int bv_dev(const ggq_bv *v, int op, const uint64_t *d_q, uint64_t n, void
 int ggq_bv_rank1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_RANK1, d_q, n, d_out, stream); }
 int ggq_bv_select1_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_SELECT1, d_q, n, d_out, stream); }
 int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t *d_out, void *stream) { return bv_dev(v, OP_GET, d_q, n, d_out, stream); }
+int ggq_map_rank1(const ggq_bv *mask, const uint64_t *graph_idx, uint64_t n, uint64_t *anno_idx, uint64_t *n_unmapped) {
+    int rc = bv_host(mask, OP_MAPRANK, graph_idx, n, anno_idx);
+    if (rc == GGQ_OK && n_unmapped) {
+        uint64_t bad = 0;
+        for (uint64_t i = 0; i < n; ++i) bad += anno_idx[i] == ~uint64_t(0);
+        *n_unmapped = bad;
+    }
+    return rc;
+}
+int ggq_map_rank1_device(const ggq_bv *mask, const uint64_t *d_graph_idx, uint64_t n, uint64_t *d_anno_idx, void *stream) {
+    return bv_dev(mask, OP_MAPRANK, d_graph_idx, n, d_anno_idx, stream);
+}
 int ggq_bv_rank0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_RANK0, d_q, n, d_out, stream); }
 int ggq_bv_select0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream) { return bv_dev(v, OP_SELECT0, d_q, n, d_out, stream); }
 

@@ -1652,12 +1652,21 @@ int ggq_get_top_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ui
     GGQ_CATCH
 }
 
-int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
-                         double presence_ratio, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
-                         uint64_t capacity, uint64_t *n_out) {
+// min_labels_discovered of StaticBinRelAnnotator::get_labels (annotate_static.cpp:79-81), per query
+static u64 min_label_count(u64 n_indices, double ratio) {
+    return ratio == 0 ? 1 : u64(std::ceil(double(n_indices) * ratio));
+}
+
+constexpr u64 kBatchSmallRows = u64(1) << 14;   // direct form of the label batch: indices of all queries together
+constexpr u64 kBatchSmallQueries = 1024;
+
+int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                                const double *presence_ratios, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                                uint64_t capacity, uint64_t *n_out) {
     GGQ_TRY
-    if (!m || !query_offsets || !label_offsets || !n_out) return fail(GGQ_ERR_ARG, "bad argument");
-    if (!(presence_ratio >= 0.0 && presence_ratio <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
+    if (!m || !query_offsets || !label_offsets || !n_out || (!presence_ratios && n_queries)) return fail(GGQ_ERR_ARG, "bad argument");
+    for (u64 q = 0; q < n_queries; ++q)
+        if (!(presence_ratios[q] >= 0.0 && presence_ratios[q] <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
     if (query_offsets[0] != 0) return fail(GGQ_ERR_ARG, "query_offsets[0] must be 0");
     for (u64 q = 0; q < n_queries; ++q)
         if (query_offsets[q + 1] < query_offsets[q]) return fail(GGQ_ERR_ARG, "query_offsets must be non-decreasing");
@@ -1677,41 +1686,106 @@ int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64
     try {
         ws->reserve_rows(n);
         cudaStream_t st = ws->stream;
-        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
-        if (ws->d_qoff.n < n_queries + 2) {
-            ws->d_qoff.alloc(n_queries + 2); ws->d_qlab_off.alloc(n_queries + 2); ws->d_qkept.alloc(n_queries + 2);
+        if (ws->d_qoff.n < 2 * n_queries + 2) {
+            ws->d_qoff.alloc(2 * n_queries + 2); ws->d_qlab_off.alloc(n_queries + 2); ws->d_qkept.alloc(n_queries + 2);
         }
-        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, query_offsets, (n_queries + 1) * 8, cudaMemcpyHostToDevice, st));
-        u64 total = 0;
-        rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
-        if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
-        CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
-        query_labels_kernel<<<u32(n_queries), 256, hist_smem, st>>>(ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p),
-                                                                   ws->d_qoff.p, u32(nc), presence_ratio, ws->d_qstage_cols.p,
-                                                                   ws->d_qstage_cnt.p, ws->d_qkept.p);
-        CUDA_CHECK(cudaGetLastError());
-        CUDA_CHECK(cudaMemsetAsync(ws->d_qkept.p + n_queries, 0, 4, st));
-        size_t need = 0;
-        cub::DeviceScan::ExclusiveSum(nullptr, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
-        if (ws->d_lab_sort.n < need + 16) ws->d_lab_sort.alloc(need + 16);
-        cub::DeviceScan::ExclusiveSum(ws->d_lab_sort.p, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
-        CUDA_CHECK(cudaMemcpyAsync(label_offsets, ws->d_qlab_off.p, (n_queries + 1) * 8, cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        const u64 kept = label_offsets[n_queries];
-        *n_out = kept;
-        ws->launches += 3;
-        if (kept > capacity || (kept && !cols)) {
-            rc = fail(GGQ_ERR_ARG, "capacity too small");
-        } else if (kept) {
-            if (ws->d_qout_cols.n < kept) { ws->d_qout_cols.alloc(kept + kept / 8 + 1024); ws->d_qout_cnt.alloc(kept + kept / 8 + 1024); }
-            query_labels_gather_kernel<<<u32((n_queries * 8 + 255) / 256), 256, 0, st>>>(
-                ws->d_offsets.p, ws->d_qoff.p, ws->d_qlab_off.p, ws->d_qstage_cols.p, ws->d_qstage_cnt.p, n_queries,
-                ws->d_qout_cols.p, ws->d_qout_cnt.p);
+        // small batches: one pinned block [rows | query offsets | per-query minimum counts]; large ones copy the rows
+        // straight from the caller's memory
+        const u64 cap_pairs = u64(1) << 16;
+        const bool direct = m->kind == Matrix::BRWT && n >= 1 && n <= kBatchSmallRows && n_queries <= kBatchSmallQueries;
+        const size_t n_staged = direct ? size_t(n) : 0;
+        const size_t in_words = n_staged + (n_queries + 1) + n_queries;
+        ws->stage_reserve((in_words + 2 + 2 * n_queries + (direct ? cap_pairs : 0)) * 8);
+        u64 *h_in = reinterpret_cast<u64 *>(ws->h_stage);
+        if (n_staged) std::memcpy(h_in, rows, n * 8);
+        std::memcpy(h_in + n_staged, query_offsets, (n_queries + 1) * 8);
+        for (u64 q = 0; q < n_queries; ++q)
+            h_in[n_staged + n_queries + 1 + q] = min_label_count(query_offsets[q + 1] - query_offsets[q], presence_ratios[q]);
+        // device: rows -> d_rows; offsets + minimum counts -> d_qoff (n_queries + 1 | n_queries)
+        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, direct ? static_cast<const void *>(h_in) : static_cast<const void *>(rows), n * 8, cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in + n_staged, (2 * n_queries + 1) * 8, cudaMemcpyHostToDevice, st));
+        const u64 *d_minc = ws->d_qoff.p + n_queries + 1;
+        bool done = false;
+        if (direct) {
+            // descent in the caller's order, per-query histogram + threshold writing into pinned memory: ONE wait
+            u64 *host = h_in + in_words;
+            host[0] = 0;
+            if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
+            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
+            CUDA_CHECK(cudaFuncSetAttribute(query_labels_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
+            query_labels_direct_kernel<<<u32(n_queries), 256, hist_smem, st>>>(
+                ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p, ws->d_qoff.p, d_minc, u32(nc),
+                u32(n_queries), host, cap_pairs);
             CUDA_CHECK(cudaGetLastError());
-            ws->launches += 1;
-            CUDA_CHECK(cudaMemcpyAsync(cols, ws->d_qout_cols.p, kept * 8, cudaMemcpyDeviceToHost, st));
-            if (counts) CUDA_CHECK(cudaMemcpyAsync(counts, ws->d_qout_cnt.p, kept * 8, cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaStreamSynchronize(st));
+            ws->launches = 2; ws->kernel_timed = false;
+            if (host[0] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
+            bool ok = (host[0] & 3) == 0;
+            u64 kept = 0;
+            for (u64 q = 0; ok && q < n_queries; ++q) {
+                if (host[2 + 2 * q] + host[3 + 2 * q] > cap_pairs) ok = false;
+                kept += host[3 + 2 * q];
+            }
+            if (ok) {
+                *n_out = kept;
+                if (kept > capacity || (kept && !cols)) {
+                    u64 o = 0;
+                    for (u64 q = 0; q < n_queries; ++q) { label_offsets[q] = o; o += host[3 + 2 * q]; }
+                    label_offsets[n_queries] = o;
+                    rc = fail(GGQ_ERR_ARG, "capacity too small");
+                } else {
+                    const u64 *pairs = host + 2 + 2 * n_queries;
+                    u64 o = 0;
+                    for (u64 q = 0; q < n_queries; ++q) {
+                        label_offsets[q] = o;
+                        const u64 *src = pairs + host[2 + 2 * q];
+                        const u64 k = host[3 + 2 * q];
+                        for (u64 i = 0; i < k; ++i) {
+                            cols[o + i] = src[i] & 0xFFFFFFFFull;
+                            if (counts) counts[o + i] = src[i] >> 32;
+                        }
+                        o += k;
+                    }
+                    label_offsets[n_queries] = o;
+                }
+                done = true;
+            } else if (host[0] & 2) {
+                ws->d_tmp.alloc(std::max<u64>(n * 64, ws->d_tmp.n * 4));   // the general path grows it exactly
+            }
+        }
+        if (!done) {
+            u64 total = 0;
+            rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
+            if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
+            CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
+            query_labels_kernel<<<u32(n_queries), 256, hist_smem, st>>>(ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p),
+                                                                       ws->d_qoff.p, u32(nc), d_minc, ws->d_qstage_cols.p,
+                                                                       ws->d_qstage_cnt.p, ws->d_qkept.p);
+            CUDA_CHECK(cudaGetLastError());
+            CUDA_CHECK(cudaMemsetAsync(ws->d_qkept.p + n_queries, 0, 4, st));
+            size_t need = 0;
+            cub::DeviceScan::ExclusiveSum(nullptr, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
+            if (ws->d_lab_sort.n < need + 16) ws->d_lab_sort.alloc(need + 16);
+            cub::DeviceScan::ExclusiveSum(ws->d_lab_sort.p, need, ws->d_qkept.p, ws->d_qlab_off.p, n_queries + 1, st);
+            CUDA_CHECK(cudaMemcpyAsync(label_offsets, ws->d_qlab_off.p, (n_queries + 1) * 8, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            const u64 kept = label_offsets[n_queries];
+            *n_out = kept;
+            ws->launches += 3;
+            if (kept > capacity || (kept && !cols)) {
+                rc = fail(GGQ_ERR_ARG, "capacity too small");
+            } else if (kept) {
+                if (ws->d_qout_cols.n < kept) { ws->d_qout_cols.alloc(kept + kept / 8 + 1024); ws->d_qout_cnt.alloc(kept + kept / 8 + 1024); }
+                query_labels_gather_kernel<<<u32((n_queries * 8 + 255) / 256), 256, 0, st>>>(
+                    ws->d_offsets.p, ws->d_qoff.p, ws->d_qlab_off.p, ws->d_qstage_cols.p, ws->d_qstage_cnt.p, n_queries,
+                    ws->d_qout_cols.p, ws->d_qout_cnt.p);
+                CUDA_CHECK(cudaGetLastError());
+                ws->launches += 1;
+                CUDA_CHECK(cudaMemcpyAsync(cols, ws->d_qout_cols.p, kept * 8, cudaMemcpyDeviceToHost, st));
+                if (counts) CUDA_CHECK(cudaMemcpyAsync(counts, ws->d_qout_cnt.p, kept * 8, cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+            }
         }
     } catch (...) {
         m->release(ws);
@@ -1720,6 +1794,14 @@ int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64
     m->release(ws);
     return rc;
     GGQ_CATCH
+}
+
+int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                         double presence_ratio, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                         uint64_t capacity, uint64_t *n_out) {
+    std::vector<double> ratios;
+    try { ratios.assign(size_t(n_queries), presence_ratio); } catch (const std::bad_alloc &) { return fail(GGQ_ERR_OOM, "out of memory"); }
+    return ggq_get_labels_batch_ratios(m, rows, query_offsets, n_queries, ratios.data(), label_offsets, cols, counts, capacity, n_out);
 }
 
 int ggq_count_labels_device(const ggq_matrix *m, ggq_workspace *ws, const uint64_t *d_rows, uint64_t n,

@@ -324,7 +324,7 @@ label_filter_kernel(const u64 *counts, u32 n_cols, u64 min_count, u64 *out_cols,
 // applies the get_labels threshold (annotate_static.cpp:79-91) and writes the kept (column, count) pairs,
 // ascending, to a staging area at the query's CSR start (kept <= ids of the query, so the ranges never overlap).
 __global__ void __launch_bounds__(256)
-query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_offsets, u32 n_cols, double ratio,
+query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_offsets, u32 n_cols, const u64 *min_counts,
                     u32 *stage_cols, u32 *stage_counts, u32 *kept) {
     extern __shared__ u32 s_hist[];
     __shared__ u32 warp_cnt[8];
@@ -337,8 +337,9 @@ query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_off
     __syncthreads();
     for (u64 i = i0 + threadIdx.x; i < i1; i += 256) atomicAdd(s_hist + ids[i], 1u);
     __syncthreads();
-    // size_t min_labels_discovered = ratio == 0 ? 1 : std::ceil(indices.size() * ratio)
-    const u64 min_count = ratio == 0 ? 1 : u64(ceil(double(r1 - r0) * ratio));
+    // min_counts[q] = ratio == 0 ? 1 : ceil(indices.size() * ratio), evaluated on the host exactly as
+    // annotate_static.cpp:79-81 does
+    const u64 min_count = min_counts[q];
     for (u32 j0 = 0; j0 < n_cols; j0 += 256) {
         const u32 j = j0 + threadIdx.x;
         const u32 c = j < n_cols ? s_hist[j] : 0;
@@ -364,6 +365,77 @@ query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_off
         __syncthreads();
     }
     if (threadIdx.x == 0) kept[q] = base_s;
+}
+
+// Small batches of query sequences (a handful of concurrent `classify` tasks: <= 16 K indices in all): no CSR at all.
+// One CTA per query builds the histogram straight from the unordered chunks the descent left in its arena
+// (order is irrelevant to a histogram), thresholds it, reserves room with one atomic and writes the kept
+// (column | count << 32) pairs, ascending, into PINNED HOST memory; the host waits once.
+//   host[0] = status, zeroed by the host before the launch (bit 0: descent stack overflow, bit 1: arena too small)
+//   host[2 + 2q], host[3 + 2q] = first pair and number of pairs of query q (first + number > capacity: the pairs
+//   were not written; the host falls back to the general path);  pairs from host[2 + 2 n_queries]
+__global__ void __launch_bounds__(256)
+query_labels_direct_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_cols, u64 tmp_cap, u64 *ctrl,
+                           const u64 *query_offsets, const u64 *min_counts, u32 n_cols, u32 n_queries, u64 *host,
+                           u64 host_cap_pairs) {
+    extern __shared__ u32 s_hist[];
+    __shared__ u32 warp_cnt[8];
+    __shared__ u32 base_s;
+    __shared__ u64 out_base_s;
+    const u32 q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool overflow = *reinterpret_cast<const int *>(ctrl + 4) != 0, too_small = ctrl[0] > tmp_cap;
+    if (overflow || too_small) {
+        if (q == 0 && threadIdx.x == 0) { host[0] = (overflow ? 1u : 0u) | (too_small ? 2u : 0u); __threadfence_system(); }
+        return;
+    }
+    const u64 r0 = query_offsets[q], r1 = query_offsets[q + 1];
+    for (u32 j = threadIdx.x; j < n_cols; j += 256) s_hist[j] = 0;
+    __syncthreads();
+    for (u64 r = r0 + threadIdx.x; r < r1; r += 256) {
+        const u64 off = row_tmp_off[r];
+        const u32 c = row_cnt[r];
+        for (u32 i = 0; i < c; ++i) atomicAdd(s_hist + tmp_cols[off + i], 1u);
+    }
+    __syncthreads();
+    const u64 min_count = min_counts[q];
+    u32 mine = 0;
+    for (u32 j = threadIdx.x; j < n_cols; j += 256) { const u32 c = s_hist[j]; mine += c != 0 && c >= min_count; }
+    for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if (lane == 0) warp_cnt[warp] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u32 kept = 0;
+        for (u32 w = 0; w < 8; ++w) kept += warp_cnt[w];
+        const u64 at = atomicAdd(reinterpret_cast<unsigned long long *>(ctrl + 7), (unsigned long long)kept);
+        host[2 + 2 * u64(q)] = at;
+        host[3 + 2 * u64(q)] = kept;
+        out_base_s = at + kept > host_cap_pairs ? ~0ull : at;
+        base_s = 0;
+    }
+    __syncthreads();
+    const u64 out_base = out_base_s;
+    u64 *pairs = host + 2 + 2 * u64(n_queries);
+    for (u32 j0 = 0; j0 < n_cols && out_base != ~0ull; j0 += 256) {
+        const u32 j = j0 + threadIdx.x;
+        const u32 c = j < n_cols ? s_hist[j] : 0;
+        const bool keep = c != 0 && c >= min_count;
+        const u32 bal = __ballot_sync(0xffffffffu, keep);
+        __syncthreads();
+        if (lane == 0) warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        u32 before = 0, total = 0;
+        #pragma unroll
+        for (u32 w = 0; w < 8; ++w) {
+            const u32 v = warp_cnt[w];
+            if (w < warp) before += v;
+            total += v;
+        }
+        const u32 base = base_s;
+        if (keep) pairs[out_base + base + before + __popc(bal & ((1u << lane) - 1u))] = u64(j) | (u64(c) << 32);
+        __syncthreads();
+        if (threadIdx.x == 0) base_s = base + total;
+    }
+    __threadfence_system();
 }
 
 // staging -> dense per-query lists (8 lanes copy one query)

@@ -173,6 +173,13 @@ int ggq_get_top_labels(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ui
 int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
                          double presence_ratio, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
                          uint64_t capacity, uint64_t *n_out);
+/* Same with one presence ratio PER QUERY — what AnnotatedDBG::get_labels passes: it rescales the caller's ratio by
+ * the k-mers of the sequence that are missing from the graph (common/annotated_dbg.cpp:104-113).  Batches of up to
+ * 2^14 indices in all take a direct form: one host->device copy, descent, one CTA per query that builds the
+ * histogram from the descent's chunks and writes the kept pairs into pinned host memory, one wait. */
+int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                                const double *presence_ratios, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                                uint64_t capacity, uint64_t *n_out);
 
 /* slice_rows: concatenation of get_row(R[t]) each followed by UINT64_MAX (SURVEY.md "Three facts" 1). */
 int ggq_slice_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, uint64_t **out, uint64_t *out_len);
@@ -297,6 +304,13 @@ int ggq_bv_get_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint8_t 
  *   to_words: the plain bits, (size + 63) / 64 LSB-first words         (to_vector / copy, bit_vector.cpp:36-46)
  *   call_ones_into: positions of the set bits, ascending               (call_ones, bit_vector.cpp:442-451, 767-790, 958-983);
  *               *n_ones is always set; GGQ_ERR_ARG if capacity < num_set_bits */
+/* AnnotatedDBG::graph_to_anno_index (common/annotated_dbg.cpp:142-156) for a batch: anno_idx[t] =
+ * annotation_mask.rank1(graph_idx[t]) - 1 where the mask bit is set.  Where it is not (the reference throws "trying
+ * to annotate k-mer that cannot be annotated") or the index is out of range, anno_idx[t] = UINT64_MAX — a value every
+ * row query answers with an empty row — and *n_unmapped (may be NULL) counts them.  The device variant chains into
+ * ggq_get_rows_device / ggq_count_labels_device on the same stream without a host round trip. */
+int ggq_map_rank1(const ggq_bv *mask, const uint64_t *graph_idx, uint64_t n, uint64_t *anno_idx, uint64_t *n_unmapped);
+int ggq_map_rank1_device(const ggq_bv *mask, const uint64_t *d_graph_idx, uint64_t n, uint64_t *d_anno_idx, void *stream);
 int ggq_bv_rank0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
 int ggq_bv_select0(const ggq_bv *v, const uint64_t *q, uint64_t n, uint64_t *out);
 int ggq_bv_rank0_device(const ggq_bv *v, const uint64_t *d_q, uint64_t n, uint64_t *d_out, void *stream);

@@ -148,3 +148,25 @@ def test_synthesized_matches_oracle_generator(ggq, orc, ref, kind, d):
     ks = rng.integers(1, rv.num_set_bits + 1, 20000).astype(np.uint64)
     assert np.array_equal(gv.select1(ks), rv.select1(ks))
     gv.close()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_map_rank1_is_graph_to_anno_index(ggq, ref, kind):
+    """ggq_map_rank1 = AnnotatedDBG::graph_to_anno_index over a batch (common/annotated_dbg.cpp:142-156):
+    annotation_mask.rank1(i) - 1 where the mask is set; unset / out-of-range indices come back as UINT64_MAX."""
+    n = 100_000
+    bits = (np.random.default_rng(3).random(n) < 0.4).astype(np.uint8)
+    words = pack(bits)
+    gv = ggq.GpuBitVector.build(kind, words, n)
+    rv = ref.RefBitVector.build(kind, words, n)
+    try:
+        q = np.concatenate([np.random.default_rng(4).integers(0, n, 20_000), [0, n - 1, n, n + 5, 2**50]]).astype(np.uint64)
+        got, bad = gv.map_rank1(q)
+        inside = q < n
+        set_ = np.zeros(q.size, bool)
+        set_[inside] = bits[q[inside].astype(np.int64)] == 1
+        exp = np.full(q.size, 2**64 - 1, dtype=np.uint64)
+        exp[set_] = rv.rank1(q[set_]) - np.uint64(1)
+        assert np.array_equal(got, exp) and bad == int((~set_).sum())
+    finally:
+        gv.close()

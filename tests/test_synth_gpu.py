@@ -164,27 +164,58 @@ def test_two_matrices_with_different_shapes_coexist(ggq):
     wide.close(); narrow.close()
 
 
-def test_labels_batch_equals_per_query_get_labels(ggq):
-    """ggq_get_labels_batch (cross-query batching, main.cpp:462-504) == ggq_get_labels per query: same columns,
-    same counts, same threshold (annotate_static.cpp:79-91), empty queries and duplicates included."""
-    n, m, d = 40_000, 150, 0.04
-    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=11, arity=3)
+def _expected_labels(orc, m, thr, seed, rows, n, ratio):
+    """StaticBinRelAnnotator::get_labels(indices, ratio) (annotate_static.cpp:71-94) restated on direct evaluation of
+    the implicit matrix (oracle): histogram over the multiset of rows, min = ratio == 0 ? 1 : ceil(|rows| * ratio)."""
+    h = np.zeros(m, np.int64)
+    for r in rows:
+        if r < n:
+            np.add.at(h, orc.synth_row(m, thr, seed, int(r)).astype(np.int64), 1)
+    need = 1 if ratio == 0 else int(np.ceil(len(rows) * ratio))
+    keep = np.nonzero((h != 0) & (h >= need))[0]
+    return keep.astype(np.uint64), h[keep].astype(np.uint64)
+
+
+@pytest.mark.parametrize("sizes", [[0, 1, 2, 300, 17, 0, 250, 299], "many", "large"])
+def test_labels_batch_against_oracle_histograms(ggq, orc, sizes):
+    """ggq_get_labels_batch / _ratios (cross-query batching, main.cpp:462-504): every query's kept labels and counts
+    against histograms of oracle-evaluated rows and the reference's threshold rule, with one ratio for all queries
+    and with a ratio per query (AnnotatedDBG::get_labels rescales it per sequence, annotated_dbg.cpp:104-113).
+    Covers the direct small-batch form (<= 2^14 indices), the general form, empty queries and duplicates."""
+    n, m, d, seed = 40_000, 150, 0.04, 11
+    thr = ggq.density_threshold(d)
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=seed, arity=3)
     try:
         rng = np.random.default_rng(5)
-        sizes = np.concatenate([[0, 1, 2], rng.integers(1, 400, 120), [0, 5000]])
+        if sizes == "many":
+            sizes = np.concatenate([[0, 1, 2], rng.integers(1, 200, 100), [0, 900]])       # ~11 K indices: direct form
+        elif sizes == "large":
+            sizes = np.concatenate([[0, 3], rng.integers(100, 400, 90), [0, 6000]])         # ~28 K indices: general form
+        sizes = np.asarray(sizes)
         qoff = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
         rows = rng.integers(0, n, int(qoff[-1])).astype(np.uint64)
-        rows[10:20] = rows[10]   # duplicates are counted
-        for ratio in (0.0, 0.05, 0.3, 1.0):
+        if rows.size > 20:
+            rows[10:20] = rows[10]   # duplicates are counted
+            rows[5] = np.uint64(n + 7)   # out of range: an empty row
+        per_query = rng.choice([0.0, 0.01, 0.05, 0.3, 1.0], size=sizes.size)
+        for ratio in (0.0, 0.05, 0.3, 1.0, per_query):
             loff, cols, cnt = gm.get_labels_batch(rows, qoff, ratio)
             assert loff[0] == 0 and loff[-1] == cols.size == cnt.size
             for q in range(sizes.size):
-                ec, ev = gm.get_labels(rows[int(qoff[q]):int(qoff[q + 1])], ratio)
+                rq = float(ratio[q]) if np.ndim(ratio) else ratio
+                ec, ev = _expected_labels(orc, m, thr, seed, rows[int(qoff[q]):int(qoff[q + 1])], n, rq)
                 a, b = int(loff[q]), int(loff[q + 1])
-                assert np.array_equal(cols[a:b], ec) and np.array_equal(cnt[a:b], ev), (ratio, q)
+                assert np.array_equal(cols[a:b], ec) and np.array_equal(cnt[a:b], ev), (rq, q)
+        # the single-query call agrees as well
+        for q in (3, sizes.size - 1):
+            sub = rows[int(qoff[q]):int(qoff[q + 1])]
+            lc, lv = gm.get_labels(sub, 0.05)
+            ec, ev = _expected_labels(orc, m, thr, seed, sub, n, 0.05)
+            assert np.array_equal(lc, ec) and np.array_equal(lv, ev)
         # capacity too small: error, offsets complete
-        with pytest.raises(ggq.GgqError):
-            gm.get_labels_batch(rows, qoff, 0.0, capacity=3)
+        if qoff[-1] > 100:
+            with pytest.raises(ggq.GgqError):
+                gm.get_labels_batch(rows, qoff, 0.0, capacity=3)
         # no queries
         loff, cols, cnt = gm.get_labels_batch(np.zeros(0, np.uint64), np.zeros(1, np.uint64), 0.5)
         assert loff.tolist() == [0] and cols.size == 0
@@ -370,7 +401,7 @@ def test_leaf_codes_give_the_same_rows(ggq, orc, n, m, d, arity, tmp_path):
         gi.close()
 
 
-@pytest.mark.parametrize("n,m,d", [(3_000_000, 2652, 0.003), (50_000, 300, 0.02), (5_000, 70_000, 0.0002)])
+@pytest.mark.parametrize("n,m,d", [(3_000_000, 2652, 0.003), (50_000, 300, 0.02), (5_000, 12_000, 0.001)])
 def test_compact_host_call_matches_get_rows_into(ggq, n, m, d):
     """ggq_get_rows_compact (u32 row ids in, u8 / u16 counts and u16 / u32 ids out) returns exactly the CSR of
     ggq_get_rows_into: counts = differences of its offsets, ids bit-identical, for batches below and above the
