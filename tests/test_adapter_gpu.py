@@ -32,3 +32,15 @@ def test_reference_annotator_instantiated_over_the_gpu_matrix():
     p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert p.returncode == 0, p.stdout[-3000:]
     assert "all checks passed" in p.stdout
+
+
+def test_label_batcher_hands_every_caller_its_own_answer():
+    """ggq::LabelBatcher (include/ggq/label_batcher.hpp): 8 threads x 200 query sequences through one batcher, every
+    answer equal to the caller's own ggq_get_labels call (tests/cpp/batcher_test.cpp; also prints the throughput)."""
+    exe = os.path.join(ROOT, "tests", "cpp", "bin", "batcher_test")
+    if not os.path.exists(exe):
+        pytest.skip("tests/cpp/bin/batcher_test not built (make -C genome_graph_annotation_b200/csrc)")
+    p = subprocess.run([exe, "300000", "400", "0.01", "8", "120", "300"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                       text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-3000:]
+    assert "all checks passed" in p.stdout
