@@ -77,6 +77,13 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bitvector", action="store_true", help="skip the rank1/select1/get block (C3)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--c5-rows", type=float, default=1e9)
+    ap.add_argument("--c5-cols", type=int, default=3173)
+    ap.add_argument("--c5-density", type=float, default=0.038)
+    ap.add_argument("--c5-batch", type=int, default=1 << 22, help="row ids per step (the same batch on every rank)")
+    ap.add_argument("--c5-spot-rows", type=int, default=1 << 14)
+    ap.add_argument("--c5-full", action="store_true", help="c5: every rank merges the whole batch instead of its slice")
+    ap.add_argument("--no-c5", action="store_true", help="multi-GPU default run: skip the column-sharded C5 block")
     ap.add_argument("--no-peer", action="store_true",
                     help="c5: exchange partial rows with NCCL instead of merging from peer memory over NVLink")
     return ap.parse_args()
@@ -542,6 +549,16 @@ def run_ours(args):
               "api": "ggq_count_labels (host row ids in, per-column counters out; row sets never leave the device)",
               "labels_counted_per_step": int(cnt.sum())}
 
+    # ---- C5 (BASELINE.json configs[4]): the column-sharded configuration, a collective over all ranks; needs the
+    # memory of the C4 replica, so everything that touches `gm` is read out first
+    device_image_gb = gm.device_bytes / 1e9
+    ws.close()
+    gm.close()
+    c5 = None
+    if dist is not None and world >= 2 and not args.no_c5:
+        torch.cuda.empty_cache()
+        c5 = c5_measure(args, dist, rank, world, local, max(3, min(K, 5)), 2)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -578,7 +595,7 @@ def run_ours(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic", "config": workload_config(args, world),
             "clocks": clk, "roofline": roof, "gpu_launches": launches,
-            "build_seconds": build_s, "device_image_gb": gm.device_bytes / 1e9, "leaf_codes": codes,
+            "build_seconds": build_s, "device_image_gb": device_image_gb, "leaf_codes": codes,
             "column_ids_per_row": ids / (B * K)}
     line["spot_check"] = spot
     if extra is not None:
@@ -599,8 +616,8 @@ def run_ours(args):
                 "sample": "%d random rows in %.1f s on a %d x %d d=%g sub-shape (same generator; the reference "
                           "builder cannot make the full shape); unmodified BRWT::get_row under omp parallel for" %
                           (cnt, secs, sub_n, args.cols, args.density)}
-    ws.close()
-    gm.close()
+    if c5 is not None:
+        line["c5"] = c5
     # ---- the metric's "rank/select ops/s" term (BASELINE.json configs[2]): independent vectors =>
     # replicas only, measured on rank 0
     if not args.no_bitvector:
@@ -615,26 +632,27 @@ def run_ours(args):
 # does not fit one GPU.  Every rank answers the SAME batch over its own subtrees; partial CSRs are exchanged with
 # NCCL (all-gather of offsets + grouped broadcasts of column ids) and merged in shard order on every rank.
 # --------------------------------------------------------------------------------------------
-def run_c5(args):
-    import torch
-    import torch.distributed as dist
-    import genome_graph_annotation_b200 as g
+def d2h_array(ptr, nbytes, dtype):
+    """Device pointer (int) -> numpy array (outside every timed region)."""
+    from cuda.bindings import runtime as rt
+    out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+    if nbytes:
+        (err,) = rt.cudaMemcpy(out.ctypes.data, ptr, nbytes, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+        if int(err) != 0:
+            raise RuntimeError("cudaMemcpy failed: %s" % err)
+    return out
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world < 2:
-        raise RuntimeError("--workload c5 is the column-sharded configuration: launch with torchrun, >= 2 ranks")
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+def c5_measure(args, dist, rank, world, local, K, W):
+    """C5 on an initialised process group: builds this rank's shard, times K collective steps, checks a sample of the
+    answers against direct evaluation.  Returns the result block on rank 0 (None elsewhere)."""
+    import torch
+    import genome_graph_annotation_b200 as g
     ids = [g.Comm.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     comm = g.Comm(ids[0], rank, world, local)
-    n = int(args.rows) if args.rows != 3.7e9 else int(1e9)
-    m = args.cols if args.cols != 2652 else 3173
-    d = args.density if args.density != 0.003 else 0.038
-    B = args.batch if args.batch != (1 << 24) else (1 << 22)
-    K, W = args.steps, args.warmup
+    n, m, d, B = int(args.c5_rows), args.c5_cols, args.c5_density, args.c5_batch
+    slice_mode = not args.c5_full
     t0 = time.time()
     gm = g.GpuMatrix.synthesize_brwt_shard(n, m, d, rank, world, seed=SEED, arity=args.arity, device=local)
     torch.cuda.synchronize()
@@ -652,13 +670,20 @@ def run_c5(args):
         dist.barrier()
         torch.cuda.synchronize()
 
+    def step(i):
+        """-> (first query, queries, d_offsets, d_cols, ids) of what this rank ends up holding"""
+        if slice_mode:
+            return ws.get_rows_sharded_slice_device(comm, batches[i % n_pool].data_ptr(), B, 8)
+        off, cols, total = ws.get_rows_sharded_device(comm, batches[i % n_pool].data_ptr(), B, 8)
+        return 0, B, off, cols, total
+
     if not args.no_peer:
         # merge straight from the peers' partial CSRs over NVLink (cudaIpc); capacity: this batch size, ids with slack
         comm.enable_peer(ws, B, int(B * m * d * 1.3 / world) + (1 << 20))
     clocks = ClockSampler(local)
     clocks.start()
     for i in range(W):
-        ws.get_rows_sharded_device(comm, batches[i % n_pool].data_ptr(), B, 8)
+        step(i)
     barrier()
     clocks.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -666,7 +691,7 @@ def run_c5(args):
     with torch.cuda.stream(stream):
         e0.record()
     for i in range(K):
-        _, _, total = ws.get_rows_sharded_device(comm, batches[(W + i) % n_pool].data_ptr(), B, 8)
+        total = step(W + i)[4]
         kern_ms.append(ws.stat("kernel_ms")); xch_ms.append(ws.stat("exchange_ms"))
         xch_bytes += int(ws.stat("exchange_bytes")); touches += int(ws.stat("touches"))
         launches += int(ws.stat("launches")); ids_total += total
@@ -674,44 +699,81 @@ def run_c5(args):
         e1.record()
     barrier()
     clk = clocks.stop()
+    # spot check (untimed): the first rows this rank holds of batch 0 against direct evaluation of the implicit matrix
+    q0, nq, d_off, d_cols, total = step(0)
+    torch.cuda.synchronize()
+    ns = min(nq, args.c5_spot_rows)
+    h_off = d2h_array(d_off, (ns + 1) * 8, np.uint64)
+    h_cols = d2h_array(d_cols, int(h_off[ns]) * 8, np.uint64)
+    sample = batches[0][q0:q0 + ns].cpu().numpy().view(np.uint64)
+    counts, cols = direct_rows(sample, m, d)
+    same = np.array_equal(np.diff(h_off.astype(np.int64)), counts.astype(np.int64)) and np.array_equal(h_cols, cols)
+    ok = torch.tensor([1.0 if same else 0.0], device="cuda", dtype=torch.float64)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if float(ok.item()) != 1.0:
+        raise RuntimeError("bench.py: C5 rows differ from direct evaluation")
     t = torch.tensor([e0.elapsed_time(e1), float(np.mean(kern_ms)), float(np.mean(xch_ms)), float(touches),
-                      float(gm.device_bytes)], device="cuda", dtype=torch.float64)
+                      float(gm.device_bytes), float(ids_total)], device="cuda", dtype=torch.float64)
     tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
     ms_step = float(tmax[0]) / K
     peer = comm.peer_active
+    block = None
     if rank == 0:
         peak, peak_src = peaks()
         k_ms = float(tmax[1])
+        ids_all = float(tsum[5]) if slice_mode else float(ids_total)   # ids of the whole batch over the K steps
         # the slowest rank's descent over ITS subtrees bounds the step: algorithmic bytes of all ranks / that time
-        alg = (16.0 * B * K * world + 8.0 * ids_total + 32.0 * float(tsum[3])) / K
-        line = {"metric": METRIC, "value": B / (ms_step / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "u64", "data": "synthetic",
-                "config": {"workload": "C5 RefSeq-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner, "
-                                       "column-sharded over %d GPUs; get_rows over %d uniformly random row ids per step "
-                                       "(same batch on every rank), %s, full CSR on every rank" %
-                                       (n, m, d, args.arity, world, B,
-                                        "merge kernels read the shards' partial rows from peer memory over NVLink (cudaIpc)"
-                                        if peer else "NCCL exchange + merge"),
-                           "rows": n, "cols": m, "density": d, "arity": args.arity, "batch_rows": B, "seed": SEED,
-                           "parallelism": "column shards x%d (cut frontier dealt in DFS runs), %s" %
-                                          (world, "peer-memory merge (P2P loads), 8-byte all-gathers as barriers" if peer
-                                           else "ncclAllGather + grouped ncclBroadcast"),
-                           "l2": "inputs larger than L2"},
-                "clocks": clk,
-                "roofline": {"bound": "hbm", "kernel": "brwt_rows_kernel", "achieved": alg / (k_ms / 1e3) / 1e9 / world,
-                             "peak": peak, "unit": "GB/s", "frac": alg / (k_ms / 1e3) / 1e9 / world / peak, "traffic": None,
-                             "peak_source": peak_src, "kernel_ms_max_over_ranks": k_ms,
-                             "note": "per-GPU average: algorithmic bytes of all shards / (ranks x slowest descent)"},
-                "exchange": {"mode": "peer (timed: fused transfer + merge)" if peer else "nccl (timed: transfer only)",
-                             "ms_max_over_ranks": float(tmax[2]), "bytes_per_step_per_rank": xch_bytes / K,
-                             "gb_per_s_per_rank": xch_bytes / K / (float(tmax[2]) / 1e3) / 1e9 if float(tmax[2]) > 0 else None},
-                "gpu_launches": launches, "build_seconds": build_s,
-                "device_image_gb_per_rank_max": float(tmax[4]) / 1e9, "device_image_gb_total": float(tsum[4]) / 1e9,
-                "column_ids_per_row": ids_total / (B * K)}
-        emit(line)
+        alg = (16.0 * B * K * world + 8.0 * ids_all + 32.0 * float(tsum[3])) / K
+        how = ("merge kernels read the shards' partial rows from peer memory over NVLink (cudaIpc)" if peer
+               else "NCCL exchange + merge")
+        block = {"value": B / (ms_step / 1e3), "unit": UNIT, "ms_per_step": ms_step, "steps": K, "warmup": W, "scaling": "strong",
+                 "config": {"workload": "C5 RefSeq-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner, "
+                                        "column-sharded over %d GPUs; get_rows over %d uniformly random row ids per step "
+                                        "(same batch on every rank), %s, %s" %
+                                        (n, m, d, args.arity, world, B, how,
+                                         "every rank merges its 1/%d slice of the batch" % world if slice_mode
+                                         else "full CSR on every rank"),
+                            "rows": n, "cols": m, "density": d, "arity": args.arity, "batch_rows": B, "seed": SEED,
+                            "result": "slice per rank" if slice_mode else "full CSR on every rank",
+                            "parallelism": "column shards x%d (cut frontier dealt in DFS runs), %s" %
+                                           (world, "peer-memory merge (P2P loads), 8-byte all-gathers as barriers" if peer
+                                            else "ncclAllGather + grouped ncclBroadcast"),
+                            "l2": "inputs larger than L2"},
+                 "clocks": clk,
+                 "roofline": {"bound": "hbm", "kernel": "brwt_rows_kernel", "achieved": alg / (k_ms / 1e3) / 1e9 / world,
+                              "peak": peak, "unit": "GB/s", "frac": alg / (k_ms / 1e3) / 1e9 / world / peak, "traffic": None,
+                              "peak_source": peak_src, "kernel_ms_max_over_ranks": k_ms,
+                              "note": "per-GPU average: algorithmic bytes of all shards / (ranks x slowest descent)"},
+                 "exchange": {"mode": "peer (timed: fused transfer + merge)" if peer else "nccl (timed: transfer only)",
+                              "ms_max_over_ranks": float(tmax[2]), "bytes_per_step_per_rank": xch_bytes / K,
+                              "gb_per_s_per_rank": xch_bytes / K / (float(tmax[2]) / 1e3) / 1e9 if float(tmax[2]) > 0 else None},
+                 "spot_check": {"rows_per_rank": int(ns), "identical": True,
+                                "against": "direct numpy evaluation of the implicit matrix, counts and ids in DFS order"},
+                 "gpu_launches": launches, "build_seconds": build_s,
+                 "device_image_gb_per_rank_max": float(tmax[4]) / 1e9, "device_image_gb_total": float(tsum[4]) / 1e9,
+                 "column_ids_per_row": ids_all / (B * K)}
     ws.close(); gm.close(); comm.close()
+    return block
+
+
+def run_c5(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world < 2:
+        raise RuntimeError("--workload c5 is the column-sharded configuration: launch with torchrun, >= 2 ranks")
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    block = c5_measure(args, dist, rank, world, local, args.steps, args.warmup)
+    if rank == 0:
+        line = {"metric": METRIC, "n_gpus": world, "higher_is_better": True, "vs_baseline": None, "dtype": "u64",
+                "data": "synthetic"}
+        line.update(block)
+        emit(line)
     dist.destroy_process_group()
 
 

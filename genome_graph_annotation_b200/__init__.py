@@ -66,6 +66,7 @@ def lib():
         "ggq_comm_enable_peer": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
         "ggq_comm_peer_active": (C.c_int, [vp]),
         "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
+        "ggq_get_rows_sharded_slice_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, u64p, u64p, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
         "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
         "ggq_num_rows": (C.c_uint64, [vp]),
@@ -539,6 +540,13 @@ class Workspace:
         _check(lib().ggq_get_rows_sharded_device(self.m._h, self._h, comm._h, C.c_void_p(d_rows_ptr), n, col_bytes,
                                                  C.byref(off), C.byref(cols), C.byref(total)))
         return off.value, cols.value, total.value
+
+    def get_rows_sharded_slice_device(self, comm, d_rows_ptr, n, col_bytes=4):
+        """Collective; this rank merges only its slice of the batch -> (first_query, n_queries, d_offsets, d_cols, n_cols)."""
+        off, cols, total, first, cnt = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+        _check(lib().ggq_get_rows_sharded_slice_device(self.m._h, self._h, comm._h, C.c_void_p(d_rows_ptr), n, col_bytes,
+                                                       C.byref(first), C.byref(cnt), C.byref(off), C.byref(cols), C.byref(total)))
+        return first.value, cnt.value, off.value, cols.value, total.value
 
     def merge_shards_device(self, n, d_offsets_ptrs, d_cols_ptrs, col_bytes=4):
         """Merge step alone on device pointers of every shard's partial CSR -> (d_offsets, d_cols, n_cols)."""

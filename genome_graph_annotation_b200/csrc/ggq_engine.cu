@@ -1186,19 +1186,33 @@ void ggq_comm_free(ggq_comm *c) {
     delete c;
 }
 
-int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
-                                uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
-                                uint64_t *n_cols) {
+static int rows_sharded_c(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows, uint64_t n,
+                          int col_bytes, bool slice, uint64_t *first, uint64_t *count, const uint64_t **d_offsets,
+                          const void **d_cols, uint64_t *n_cols) {
     GGQ_TRY
     if (!m || !ws || !comm || (!d_rows && n) || (col_bytes != 4 && col_bytes != 8)) return fail(GGQ_ERR_ARG, "bad argument");
     if (m->kind != Matrix::BRWT) return fail(GGQ_ERR_ARG, "not a BRWT");
-    u64 total = 0;
-    rows_sharded_device(m, ws, comm, reinterpret_cast<const u64 *>(d_rows), n, col_bytes, &total);
+    u64 total = 0, q0 = 0, nq = n;
+    rows_sharded_device(m, ws, comm, reinterpret_cast<const u64 *>(d_rows), n, col_bytes, &total, slice, &q0, &nq);
+    if (first) *first = q0;
+    if (count) *count = nq;
     if (d_offsets) *d_offsets = reinterpret_cast<const uint64_t *>(ws->m_off.p);
     if (d_cols) *d_cols = ws->m_out.p;
     if (n_cols) *n_cols = total;
     return GGQ_OK;
     GGQ_CATCH
+}
+
+int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
+                                uint64_t *n_cols) {
+    return rows_sharded_c(m, ws, comm, d_rows, n, col_bytes, false, nullptr, nullptr, d_offsets, d_cols, n_cols);
+}
+
+int ggq_get_rows_sharded_slice_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                      uint64_t n, int col_bytes, uint64_t *first_query, uint64_t *n_queries,
+                                      const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols) {
+    return rows_sharded_c(m, ws, comm, d_rows, n, col_bytes, true, first_query, n_queries, d_offsets, d_cols, n_cols);
 }
 
 // host rows -> device query -> host CSR in the workspace's pinned staging buffer

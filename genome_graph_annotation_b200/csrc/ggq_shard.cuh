@@ -151,9 +151,17 @@ inline void merge_shards(Workspace *ws, const ShardPtrs &p, u64 n, int col_bytes
 
 void rows_device(const Matrix *m, Workspace *ws, const u64 *d_rows, u64 n, int col_bytes, u64 *total_out);
 
-// steps 1-3; every rank ends with the complete CSR of the batch
+// steps 1-3.  slice == false: every rank ends with the complete CSR of the batch.  slice == true: rank k merges only
+// ITS slice of the batch, queries [n*k/R, n*(k+1)/R) — the consumer of a sharded query is itself spread over the
+// ranks, and merging everything everywhere makes the exchange (R-1)/R of the whole result per rank, which does not
+// shrink with R.  With the peer-memory exchange a slice reads 1/R of that over NVLink; the NCCL exchange still
+// gathers everything (correct, not faster).
 inline void rows_sharded_device(const Matrix *m, Workspace *ws, Comm *c, const u64 *d_rows, u64 n, int col_bytes,
-                                u64 *total_out) {
+                                u64 *total_out, bool slice = false, u64 *slice_first = nullptr, u64 *slice_n = nullptr) {
+    const u64 q0 = slice ? n * u64(c->rank) / u64(c->n_ranks) : 0;
+    const u64 q1 = slice ? n * u64(c->rank + 1) / u64(c->n_ranks) : n;
+    if (slice_first) *slice_first = q0;
+    if (slice_n) *slice_n = q1 - q0;
     if (c->n_ranks > kMaxShards) throw LimitError("too many shards");
     if (u32(c->n_ranks) != m->tree.n_shards || u32(c->rank) != m->tree.shard)
         throw std::runtime_error("communicator rank/size does not match the matrix shard");
@@ -181,16 +189,16 @@ inline void rows_sharded_device(const Matrix *m, Workspace *ws, Comm *c, const u
             ShardPtrs p;
             p.n = R;
             for (int r = 0; r < R; ++r) {
-                p.off[r] = r == c->rank ? ws->d_offsets.p : c->peer_off[r];
+                p.off[r] = (r == c->rank ? ws->d_offsets.p : c->peer_off[r]) + q0;   // (offsets are absolute: cols stay)
                 p.cols[r] = r == c->rank ? reinterpret_cast<const u32 *>(ws->d_out.p) : c->peer_cols[r];
             }
-            merge_shards(ws, p, n, col_bytes, total_out);
+            merge_shards(ws, p, q1 - q0, col_bytes, total_out);
             // nobody may overwrite its partial CSR (next query) before every peer has read it
             NCCL_CHECK(NcclApi::get().AllGather(ws->g_tot.p + kMaxShards, ws->g_tot.p, 1, ncclUint64, c->comm, st));
             CUDA_CHECK(cudaEventRecord(e1, st));
             ws->exchange_bytes = 0;
-            for (int r = 0; r < R; ++r)
-                if (r != c->rank) ws->exchange_bytes += (n + 1) * 8 * 2 + tot[r] * 4;   // offsets are read by both merge kernels
+            for (int r = 0; r < R; ++r)   // offsets are read by both merge kernels; ids of the merged queries once
+                if (r != c->rank) ws->exchange_bytes += (q1 - q0 + 1) * 8 * 2 + (slice ? tot[r] / u64(R) : tot[r]) * 4;
             ws->exchange_timed = true;
             ws->launches += 5;
             return;
@@ -211,8 +219,8 @@ inline void rows_sharded_device(const Matrix *m, Workspace *ws, Comm *c, const u
     // 3. merge in shard order
     ShardPtrs p;
     p.n = R;
-    for (int r = 0; r < R; ++r) { p.off[r] = ws->g_off.p + size_t(r) * (n + 1); p.cols[r] = ws->g_cols.p + col_off[r]; }
-    merge_shards(ws, p, n, col_bytes, total_out);
+    for (int r = 0; r < R; ++r) { p.off[r] = ws->g_off.p + size_t(r) * (n + 1) + q0; p.cols[r] = ws->g_cols.p + col_off[r]; }
+    merge_shards(ws, p, q1 - q0, col_bytes, total_out);
     ws->exchange_timed = true;
     ws->launches += 3 + R;
 }

@@ -246,6 +246,13 @@ int ggq_comm_peer_active(const ggq_comm *c);
 int ggq_get_rows_sharded_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
                                 uint64_t n, int col_bytes, const uint64_t **d_offsets, const void **d_cols,
                                 uint64_t *n_cols);
+/* Same collective, but rank k merges only ITS slice of the batch: queries [n*k/R, n*(k+1)/R) (returned in
+ * *first_query / *n_queries; d_offsets has *n_queries + 1 entries starting at 0).  Every rank still descends the
+ * whole batch over its own columns; what shrinks is the exchange — with the peer-memory merge a rank reads 1/R of the
+ * other shards' partial rows over NVLink instead of all of them. */
+int ggq_get_rows_sharded_slice_device(const ggq_matrix *m, ggq_workspace *ws, ggq_comm *comm, const uint64_t *d_rows,
+                                      uint64_t n, int col_bytes, uint64_t *first_query, uint64_t *n_queries,
+                                      const uint64_t **d_offsets, const void **d_cols, uint64_t *n_cols);
 
 /* count_labels across GPUs — collective.  Replicas: every rank passes ITS slice of the index list; column shards:
  * every rank passes the whole list (a shard counts its own columns, the others stay 0).  Either way one

@@ -40,9 +40,12 @@ class LabelBatcher {
         uint64_t queries = 0, batches = 0, indices = 0;
     };
 
+    // max_wait: longest a leader holds its batch open; idle_gap: it also submits as soon as nobody has joined for
+    // this long (with T blocking callers a batch can never grow beyond T: waiting out max_wait would be pure latency)
     explicit LabelBatcher(const ggq_matrix *matrix, size_t max_queries = 64,
-                          std::chrono::microseconds max_wait = std::chrono::microseconds(50))
-        : m_(matrix), max_queries_(max_queries ? max_queries : 1), max_wait_(max_wait) {
+                          std::chrono::microseconds max_wait = std::chrono::microseconds(50),
+                          std::chrono::microseconds idle_gap = std::chrono::microseconds(4))
+        : m_(matrix), max_queries_(max_queries ? max_queries : 1), max_wait_(max_wait), idle_gap_(idle_gap) {
         if (!matrix) throw std::invalid_argument("ggq::LabelBatcher: null matrix");
     }
     LabelBatcher(const LabelBatcher &) = delete;
@@ -69,6 +72,7 @@ class LabelBatcher {
         // results
         std::vector<uint64_t> label_offsets, cols, counts;
         std::atomic<bool> closed{false}, done{false};
+        std::atomic<uint32_t> joined{0};
         std::string error;
         std::condition_variable done_cv;
     };
@@ -77,7 +81,7 @@ class LabelBatcher {
 
     const ggq_matrix *m_;
     const size_t max_queries_;
-    const std::chrono::microseconds max_wait_;
+    const std::chrono::microseconds max_wait_, idle_gap_;
     mutable std::mutex mu_;
     std::shared_ptr<Batch> open_;   // the batch callers are currently joining (null: the next caller leads a new one)
     Stats stats_;
@@ -114,6 +118,7 @@ inline void LabelBatcher::get_labels(const uint64_t *indices, size_t n, double p
     b->rows.insert(b->rows.end(), indices, indices + n);
     b->offsets.push_back(b->rows.size());
     b->ratios.push_back(presence_ratio);
+    b->joined.fetch_add(1, std::memory_order_release);
     if (b->ratios.size() >= max_queries_) {   // full: nobody else may join; the leader sees the flag
         b->closed.store(true, std::memory_order_release);
         if (open_ == b) open_.reset();
@@ -123,8 +128,15 @@ inline void LabelBatcher::get_labels(const uint64_t *indices, size_t n, double p
         // sleeping on a condition variable.
         const auto deadline = std::chrono::steady_clock::now() + max_wait_;
         lk.unlock();
-        while (!b->closed.load(std::memory_order_acquire) && std::chrono::steady_clock::now() < deadline)
+        uint32_t seen = 1;
+        auto last_join = std::chrono::steady_clock::now();
+        while (!b->closed.load(std::memory_order_acquire)) {
+            const auto now = std::chrono::steady_clock::now();
+            const uint32_t j = b->joined.load(std::memory_order_acquire);
+            if (j != seen) { seen = j; last_join = now; }
+            if (now >= deadline || now - last_join >= idle_gap_) break;
             std::this_thread::yield();
+        }
         lk.lock();
         b->closed.store(true, std::memory_order_release);
         if (open_ == b) open_.reset();

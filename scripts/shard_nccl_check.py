@@ -38,16 +38,33 @@ def main():
         off, cols, total = ws.get_rows_sharded_device(comm, rows.data_ptr(), B, 8)
         h_off, h_cols = d2h(off, (B + 1) * 8, np.uint64), d2h(cols, total * 8, np.uint64)
         if rank == 0:
-            whole = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local)
-            eoff, ecols = whole.get_rows_csr(rows.cpu().numpy().view(np.uint64))
-            whole.close()
+            ref_m = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local)
+            eoff, ecols = ref_m.get_rows_csr(rows.cpu().numpy().view(np.uint64))
+            ref_m.close()
             assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), B
         print("rank %d B=%d total=%d exchange %.3f ms %.1f MB" % (rank, B, total, ws.stat("exchange_ms"),
                                                                   ws.stat("exchange_bytes") / 1e6), flush=True)
+    whole = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local)   # every rank checks its own slice
+
+    def check_slice(tag, B):
+        """ggq_get_rows_sharded_slice_device: this rank ends with queries [B*rank/world, B*(rank+1)/world) only."""
+        rows = torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen)
+        first, cnt, off, cols, total = ws.get_rows_sharded_slice_device(comm, rows.data_ptr(), B, 8)
+        assert (first, cnt) == (B * rank // world, B * (rank + 1) // world - B * rank // world), (tag, first, cnt)
+        h_off, h_cols = d2h(off, (cnt + 1) * 8, np.uint64), d2h(cols, total * 8, np.uint64)
+        eoff, ecols = whole.get_rows_csr(rows[first:first + cnt].cpu().numpy().view(np.uint64))
+        assert np.array_equal(h_off, eoff) and np.array_equal(h_cols, ecols), (tag, B)
+        print("rank %d slice %s B=%d -> queries [%d, %d) ids=%d exchange %.3f ms %.1f MB" %
+              (rank, tag, B, first, first + cnt, total, ws.stat("exchange_ms"), ws.stat("exchange_bytes") / 1e6), flush=True)
+
+    for B in (0, 1, 7, 1000, 300_001):
+        check_slice("nccl", B)
     # peer-memory exchange (ggq_comm_enable_peer): merge straight from the peers' buffers over NVLink; then a batch
     # beyond the pinned capacity, which must fall back to the NCCL exchange on every rank — same answers throughout
-    whole = g.GpuMatrix.synthesize_brwt(n, m, d, seed=42, arity=4, device=local) if rank == 0 else None
     comm.enable_peer(ws, 400_000, 400_000 * 8)
+    assert comm.peer_active
+    for B in (0, 1, 7, 1000, 300_001):
+        check_slice("peer", B)
     assert comm.peer_active
     for B, expect_peer in ((1, True), (1000, True), (300_000, True), (300_000, True), (0, True), (500_000, False), (1000, False)):
         rows = torch.randint(0, n, (B,), device="cuda", dtype=torch.int64, generator=gen)
