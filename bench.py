@@ -557,7 +557,7 @@ def run_ours(args):
     c5 = None
     if dist is not None and world >= 2 and not args.no_c5:
         torch.cuda.empty_cache()
-        c5 = c5_measure(args, dist, rank, world, local, max(3, min(K, 5)), 2)
+        c5 = c5_measure(args, dist, rank, world, local, 10, 2)
 
     if rank != 0:
         if dist is not None:
