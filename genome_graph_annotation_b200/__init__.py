@@ -67,6 +67,8 @@ def lib():
         "ggq_comm_peer_active": (C.c_int, [vp]),
         "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_get_rows_sharded_slice_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, u64p, u64p, C.POINTER(vp), C.POINTER(vp), u64p]),
+        "ggq_brwt_build_columns": (C.c_int, [u64p, C.c_uint64, C.c_uint64, C.c_int, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(vp)]),
+        "ggq_tree_shape": (C.c_int, [vp, u64p, C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), u64p, u64p, C.POINTER(C.c_uint32)]),
         "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
         "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
         "ggq_num_rows": (C.c_uint64, [vp]),
@@ -257,6 +259,32 @@ class GpuMatrix:
         m = cls(h.value, "brwt")
         m.consumed = used.value
         return m
+
+    @classmethod
+    def build_brwt(cls, col_words, n_rows, greedy=False, arity=2, relax=0, device=0):
+        """The reference's bottom-up construction on the device (ggq_brwt_build_columns): col_words[j] = column j as
+        ceil(n_rows / 64) LSB-first u64 words."""
+        cw = np.ascontiguousarray(col_words, dtype=np.uint64)
+        m = cw.shape[0] if cw.ndim == 2 else 0
+        if cw.size == 0:
+            cw = np.zeros(1, np.uint64)
+        h = C.c_void_p()
+        _check(lib().ggq_brwt_build_columns(cw.ctypes.data_as(u64p), n_rows, m, int(greedy), arity, relax, device, C.byref(h)))
+        return cls(h.value, "brwt")
+
+    def tree_shape(self):
+        """dict of per-node arrays in level order: parent, n_children, n_columns, size, ones, first_column."""
+        n = C.c_uint64()
+        _check(lib().ggq_tree_shape(self._h, C.byref(n), None, None, None, None, None, None))
+        k = n.value
+        out = {"parent": np.zeros(k, np.int64), "n_children": np.zeros(k, np.uint32), "n_columns": np.zeros(k, np.uint32),
+               "size": np.zeros(k, np.uint64), "ones": np.zeros(k, np.uint64), "first_column": np.zeros(k, np.uint32)}
+        _check(lib().ggq_tree_shape(self._h, C.byref(n), out["parent"].ctypes.data_as(C.POINTER(C.c_int64)),
+                                    out["n_children"].ctypes.data_as(C.POINTER(C.c_uint32)),
+                                    out["n_columns"].ctypes.data_as(C.POINTER(C.c_uint32)),
+                                    out["size"].ctypes.data_as(u64p), out["ones"].ctypes.data_as(u64p),
+                                    out["first_column"].ctypes.data_as(C.POINTER(C.c_uint32))))
+        return out
 
     @classmethod
     def load_image(cls, path, device=0):

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <new>
@@ -23,6 +24,7 @@
 #include "ggq_kernels.cuh"
 #include "ggq_engine.hpp"
 #include "ggq_builder.cuh"
+#include "ggq_build_greedy.cuh"
 #include "ggq_bv.cuh"
 #include "ggq_colmajor.cuh"
 #include "ggq_image.hpp"
@@ -465,8 +467,12 @@ void Matrix::upload_codes_tables() {
     refresh_img();
 }
 
-// host-parsed tree (plain bits per node) -> device image
-static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_shards = 1) {
+// Fills the concatenated plain bits of all present lanes on the device: d_plain (u32 words, zeroed),
+// lane_plain_off[li] = first word of lane li, which owns (size + 31) / 32 + 4 words.
+typedef std::function<void(const FlatTree &, u32 *, const std::vector<u64> &)> PlainFill;
+
+// tree with plain bits per node (host-parsed: FlatNode::bits; device-built: `fill`) -> device image
+static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_shards = 1, const PlainFill *fill = nullptr) {
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
     m->device = device;
@@ -487,16 +493,22 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     for (u32 li = 0; li < n_lanes; ++li) {
         if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
         lane_plain_off[li] = total_words;
-        total_words += t.nodes[t.lane_node[li]].bits.w.size();
+        const FlatNode &nd = t.nodes[t.lane_node[li]];
+        total_words += fill ? (nd.size + 31) / 32 + 4 : nd.bits.w.size();
     }
     {
         DeviceBuf<u32> d_plain;
         DeviceBuf<u64> d_off;
         d_plain.alloc(std::max<u64>(total_words, 1));
-        for (u32 li = 0; li < n_lanes; ++li) {
-            if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
-            const auto &w = t.nodes[t.lane_node[li]].bits.w;
-            CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+        if (fill) {
+            CUDA_CHECK(cudaMemset(d_plain.p, 0, d_plain.bytes()));
+            (*fill)(t, d_plain.p, lane_plain_off);
+        } else {
+            for (u32 li = 0; li < n_lanes; ++li) {
+                if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
+                const auto &w = t.nodes[t.lane_node[li]].bits.w;
+                CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+            }
         }
         upload_vec(d_off, lane_plain_off);
         std::vector<u32> chunk_lane, chunk_first, lane_chunk_off;
@@ -519,6 +531,155 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     m->build_leaf_codes();
     m->derive_stats();
     return m.release();
+}
+
+// BRWTBottomUpBuilder::build + BRWTOptimizer::relax on the device (ggq_build_greedy.cuh) from explicit columns:
+// col_words = n_cols columns of ceil(n_rows / 64) LSB-first u64 words each.  partitioner: 0 = basic(arity), 1 = greedy.
+static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, int partitioner, u32 arity,
+                                  u64 relax_arity, int device, std::vector<BuildNode> *shape_out = nullptr, int *root_out = nullptr) {
+    CUDA_CHECK(cudaSetDevice(device));
+    FlatTree t;
+    if (n_cols == 0) {   // BRWT(): a single empty node
+        t.nodes.emplace_back();
+        t.n_rows = 0; t.n_cols = 0;
+        return upload_brwt(std::move(t), device);
+    }
+    const u64 W = (n_rows + 63) / 64;
+    std::vector<BuildNode> N(n_cols);
+    std::vector<DeviceBuf<u64>> full(n_cols), sub_own;
+    std::vector<const u64 *> sub(n_cols, nullptr);
+    for (u32 j = 0; j < n_cols; ++j) {
+        N[j].cols = {j};
+        full[j].alloc(std::max<u64>(W, 1));
+        if (W) {
+            CUDA_CHECK(cudaMemcpy(full[j].p, col_words + size_t(j) * W, W * 8, cudaMemcpyHostToDevice));
+            if (n_rows & 63) {   // clear padding
+                const u64 last = col_words[size_t(j) * W + W - 1] & ((1ull << (n_rows & 63)) - 1ull);
+                CUDA_CHECK(cudaMemcpy(full[j].p + W - 1, &last, 8, cudaMemcpyHostToDevice));
+            }
+        }
+    }
+    // sampled rows for the similarity estimates (all rows when n_rows <= 10^6)
+    u64 Ws = W;
+    DeviceBuf<u64> d_idx;
+    bool sampled = false;
+    if (partitioner == 1 && n_rows > kBuildRowsSampled) {
+        const std::vector<u64> idx = build_row_sample(n_rows);
+        upload_vec(d_idx, idx);
+        Ws = (idx.size() + 63) / 64;
+        sampled = true;
+        sub_own.resize(n_cols);
+        for (u32 j = 0; j < n_cols; ++j) {
+            sub_own[j].alloc(Ws);
+            sample_rows_kernel<<<u32((Ws + 255) / 256), 256>>>(full[j].p, d_idx.p, idx.size(), sub_own[j].p);
+            sub[j] = sub_own[j].p;
+        }
+        CUDA_CHECK(cudaGetLastError());
+    } else {
+        for (u32 j = 0; j < n_cols; ++j) sub[j] = full[j].p;
+    }
+    std::vector<int> cur(n_cols);
+    for (u32 j = 0; j < n_cols; ++j) cur[j] = int(j);
+    DeviceBuf<u32> d_G;
+    DeviceBuf<const u64 *> d_ptrs;
+    while (cur.size() > 1) {
+        const u32 k_n = u32(cur.size());
+        std::vector<std::vector<u32>> part;
+        if (partitioner == 1) {
+            std::vector<const u64 *> ptrs(k_n);
+            for (u32 i = 0; i < k_n; ++i) ptrs[i] = sub[cur[i]];
+            d_ptrs.alloc(k_n);
+            CUDA_CHECK(cudaMemcpy(d_ptrs.p, ptrs.data(), size_t(k_n) * sizeof(const u64 *), cudaMemcpyHostToDevice));
+            d_G.alloc(size_t(k_n) * k_n);
+            const u32 tiles = (k_n + kGramTile - 1) / kGramTile;
+            gram_kernel<<<dim3(tiles, tiles), 256>>>(d_ptrs.p, k_n, Ws, d_G.p);
+            CUDA_CHECK(cudaGetLastError());
+            std::vector<u32> G(size_t(k_n) * k_n);
+            CUDA_CHECK(cudaMemcpy(G.data(), d_G.p, G.size() * 4, cudaMemcpyDeviceToHost));
+            part = greedy_partition(G, k_n);
+        } else {
+            part = basic_partition(k_n, std::max<u32>(arity, 2));
+        }
+        std::vector<int> next;
+        for (const std::vector<u32> &grp : part) {
+            if (grp.size() == 1) { next.push_back(cur[grp[0]]); continue; }   // passed through unchanged (BRWT_builders.cpp:74-76)
+            const int id = int(N.size());
+            N.emplace_back();
+            full.emplace_back();
+            full[id].alloc(std::max<u64>(W, 1));
+            CUDA_CHECK(cudaMemset(full[id].p, 0, std::max<u64>(W, 1) * 8));
+            if (sampled) { sub_own.emplace_back(); sub_own[id].alloc(Ws); CUDA_CHECK(cudaMemset(sub_own[id].p, 0, Ws * 8)); }
+            for (u32 g : grp) {
+                const int c = cur[g];
+                N[id].children.push_back(c);
+                N[id].cols.insert(N[id].cols.end(), N[c].cols.begin(), N[c].cols.end());
+                if (W) or_into_kernel<<<u32((W + 255) / 256), 256>>>(full[id].p, full[c].p, W);
+                if (sampled) or_into_kernel<<<u32((Ws + 255) / 256), 256>>>(sub_own[id].p, sub[c], Ws);
+            }
+            CUDA_CHECK(cudaGetLastError());
+            sub.push_back(sampled ? sub_own[id].p : full[id].p);
+            next.push_back(id);
+        }
+        cur.swap(next);
+    }
+    const int root = cur[0];
+    CUDA_CHECK(cudaDeviceSynchronize());
+    for (size_t id = 0; id < N.size(); ++id) N[id].ones = device_popcount(full[id].p, W);
+    if (relax_arity > 1) relax_tree(N, root, n_rows, relax_arity);
+    if (shape_out) *shape_out = N;
+    if (root_out) *root_out = root;
+    // BFS flattening; bn_of[flat id] = builder node
+    std::vector<int> bn_of;
+    {
+        struct Pending { int bn, parent, child_index; };
+        std::deque<Pending> q;
+        q.push_back({root, -1, 0});
+        while (!q.empty()) {
+            const Pending cu = q.front();
+            q.pop_front();
+            const int id = int(t.nodes.size());
+            t.nodes.emplace_back();
+            bn_of.push_back(cu.bn);
+            FlatNode &fn = t.nodes.back();
+            fn.parent = cu.parent;
+            fn.child_index = cu.child_index;
+            fn.depth = cu.parent < 0 ? 0 : t.nodes[cu.parent].depth + 1;
+            fn.cols = N[cu.bn].cols;
+            fn.ones = N[cu.bn].ones;
+            fn.size = cu.parent < 0 ? n_rows : t.nodes[cu.parent].ones;
+            if (cu.parent >= 0) t.nodes[cu.parent].children.push_back(id);
+            for (size_t i = 0; i < N[cu.bn].children.size(); ++i) q.push_back({N[cu.bn].children[i], id, int(i)});
+        }
+    }
+    t.n_rows = n_rows;
+    t.n_cols = n_cols;
+    // a child's stored vector = its index vector restricted to the ones of its parent's (generate_subindex)
+    PlainFill fill = [&](const FlatTree &ft, u32 *d_plain, const std::vector<u64> &lane_plain_off) {
+        DeviceBuf<u64> cnt, before;
+        DeviceBuf<unsigned char> tmp;
+        cnt.alloc(std::max<u64>(W, 1));
+        before.alloc(std::max<u64>(W, 1));
+        size_t need = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, need, cnt.p, before.p, W);
+        tmp.alloc(need + 16);
+        const u32 g = u32((W + 255) / 256);
+        for (size_t id = 0; id < ft.nodes.size() && W; ++id) {
+            const FlatNode &fn = ft.nodes[id];
+            const u32 li = fn.group * 4 + fn.lane;
+            if (fn.parent < 0) words64_to_32_kernel<<<g, 256>>>(full[bn_of[id]].p, W, d_plain + lane_plain_off[li]);
+            if (fn.children.empty()) continue;
+            const u64 *pv = full[bn_of[id]].p;
+            word_popc_kernel<<<g, 256>>>(pv, W, cnt.p);
+            cub::DeviceScan::ExclusiveSum(tmp.p, need, cnt.p, before.p, W);
+            for (int c : fn.children) {
+                const FlatNode &cn = ft.nodes[c];
+                pext_compact_kernel<<<g, 256>>>(full[bn_of[c]].p, pv, before.p, W, d_plain + lane_plain_off[cn.group * 4 + cn.lane]);
+            }
+            CUDA_CHECK(cudaGetLastError());
+        }
+        CUDA_CHECK(cudaDeviceSynchronize());
+    };
+    return upload_brwt(std::move(t), device, 0, 1, &fill);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -949,6 +1110,35 @@ int ggq_brwt_synthesize(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, ui
     *out = static_cast<ggq_matrix *>(synthesize_brwt(n_rows, u32(n_cols), threshold, seed, arity, device));
     return GGQ_OK;
     GGQ_CATCH
+}
+
+int ggq_brwt_build_columns(const uint64_t *col_words, uint64_t n_rows, uint64_t n_cols, int partitioner, uint32_t arity,
+                           uint64_t relax_arity, int device, ggq_matrix **out) {
+    GGQ_TRY
+    if (!out || (!col_words && n_rows && n_cols) || partitioner < 0 || partitioner > 1 || (partitioner == 0 && arity < 2))
+        return fail(GGQ_ERR_ARG, "bad argument");
+    if (n_rows >= kMaxRows || n_cols >= (u64(1) << 31)) return fail(GGQ_ERR_LIMIT, "matrix exceeds engine limits");
+    *out = static_cast<ggq_matrix *>(build_brwt_columns(reinterpret_cast<const u64 *>(col_words), n_rows, u32(n_cols),
+                                                        partitioner, arity, relax_arity, device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_tree_shape(const ggq_matrix *m, uint64_t *n_nodes, int64_t *parent, uint32_t *n_children, uint32_t *n_columns,
+                   uint64_t *size, uint64_t *ones, uint32_t *first_column) {
+    if (!m || !n_nodes) return fail(GGQ_ERR_ARG, "bad argument");
+    if (m->kind != Matrix::BRWT || m->tree.nodes.empty()) return fail(GGQ_ERR_ARG, "no host tree (column-major matrix or image file)");
+    const auto &N = m->tree.nodes;
+    *n_nodes = N.size();
+    for (size_t i = 0; i < N.size(); ++i) {
+        if (parent) parent[i] = N[i].parent;
+        if (n_children) n_children[i] = u32(N[i].children.size());
+        if (n_columns) n_columns[i] = u32(N[i].cols.size());
+        if (size) size[i] = N[i].size;
+        if (ones) ones[i] = N[i].ones;
+        if (first_column) first_column[i] = N[i].cols.empty() ? ~0u : N[i].cols[0];
+    }
+    return GGQ_OK;
 }
 
 int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t stats[8]) {

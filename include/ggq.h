@@ -83,6 +83,21 @@ int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, ui
  * serialized BRWT.  dfs_cols / depth: num_columns entries each, caller-allocated (may be NULL). */
 int ggq_brwt_inspect_columns(const uint8_t *buf, size_t len, uint32_t *dfs_cols, uint32_t *depth);
 
+/* The reference's BRWT construction on the device: BRWTBottomUpBuilder::build(columns, partitioner)
+ * (annotation/hierarchical_annotation/BRWT_builders.cpp:122-163) with partitioner 0 = get_basic_partitioner(arity)
+ * (:19-31) or 1 = parallel_binary_grouping_greedy (partitionings.cpp:146-196: pairs ranked by popcount(a & b) over
+ * up to 10^6 sampled rows), followed by BRWTOptimizer::relax(relax_arity) (BRWT_builders.cpp:166-380) when
+ * relax_arity > 1.  col_words: n_cols columns of ceil(n_rows / 64) LSB-first u64 words each.  Produces the SAME tree
+ * as the reference builder (nodes, child order, column arrangement): the Gram matrix, the ORs and the index
+ * restriction run on the GPU, the ranking and the space model decide as the reference does. */
+int ggq_brwt_build_columns(const uint64_t *col_words, uint64_t n_rows, uint64_t n_cols, int partitioner, uint32_t arity,
+                           uint64_t relax_arity, int device, ggq_matrix **out);
+/* Tree of a BRWT matrix, nodes in level (BFS) order, children in stored order: parent index (-1: root), number of
+ * children / columns, length and popcount of the node's vector, first column of its arrangement.  Arrays may be NULL;
+ * *n_nodes is always set.  Not available for matrices restored from an image file (GGQ_ERR_ARG). */
+int ggq_tree_shape(const ggq_matrix *m, uint64_t *n_nodes, int64_t *parent, uint32_t *n_children, uint32_t *n_columns,
+                   uint64_t *size, uint64_t *ones, uint32_t *first_column);
+
 /* BinaryMatrix::num_rows / num_columns / num_relations (common/binary_matrix.hpp:16-28) */
 uint64_t ggq_num_rows(const ggq_matrix *m);
 uint64_t ggq_num_columns(const ggq_matrix *m);

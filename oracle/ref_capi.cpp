@@ -366,5 +366,8 @@ void ggref_gen_implicit(uint64_t n, uint64_t m, uint64_t threshold, uint64_t see
 }
 
 int ggref_max_threads() { return omp_get_max_threads(); }
+// BRWTOptimizer's space model adds sizeof(bit_vector_rrr<>) * 8 bits per vector (BRWT_builders.cpp:293-300); the device
+// builder restates the model and carries the number as a constant — this pins it.
+uint64_t ggref_sizeof_bit_vector_rrr() { return sizeof(bit_vector_rrr<>); }
 
 }  // extern "C"

@@ -144,3 +144,14 @@ def test_reference_unit_tests_pass_on_oracle_build():
     tail = p.stdout[-2000:]
     assert p.returncode == 0, tail
     assert "PASSED" in tail and "FAILED" not in tail, tail
+
+
+def test_space_model_constant_of_the_device_builder(ref):
+    """ggq_build_greedy.cuh restates BRWTOptimizer's RRR space model with sizeof(bit_vector_rrr<>) as a constant."""
+    import ctypes
+    import re
+    f = ref.lib().ggref_sizeof_bit_vector_rrr
+    f.restype = ctypes.c_uint64
+    src = open(os.path.join(ROOT, "genome_graph_annotation_b200", "csrc", "ggq_build_greedy.cuh")).read()
+    k = re.search(r"kSizeofBitVectorRrrBits = (\d+) \* 8", src)
+    assert k and int(k.group(1)) == f()
