@@ -645,6 +645,8 @@ static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, 
             fn.child_index = cu.child_index;
             fn.depth = cu.parent < 0 ? 0 : t.nodes[cu.parent].depth + 1;
             fn.cols = N[cu.bn].cols;
+            if (cu.parent < 0)   // the root's local columns ARE the global ones (as flatten_parsed has it)
+                for (u32 c = 0; c < n_cols; ++c) fn.cols[c] = c;
             fn.ones = N[cu.bn].ones;
             fn.size = cu.parent < 0 ? n_rows : t.nodes[cu.parent].ones;
             if (cu.parent >= 0) t.nodes[cu.parent].children.push_back(id);

@@ -1,5 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-( time timeout 1500 python -m pytest tests/test_builder_gpu.py -m gpu -x -q 2>&1 | tail -30 ) 2>&1 | tail -36
-for T in 8 32; do tests/cpp/bin/batcher_test 500000000 2652 0.003 $T 400 300 2>&1 | tail -2 | head -1 | tee -a gpurun_out/r2g_batcher.txt; done
-tests/cpp/bin/batcher_test 1000000 100 0.01 16 400 100 2>&1 | tail -2 | head -1 | tee -a gpurun_out/r2g_batcher.txt
+( time timeout 1500 python -m pytest tests/test_builder_gpu.py -m gpu -q 2>&1 | tail -40 ) 2>&1 | tail -46
