@@ -19,6 +19,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace ggq {
@@ -199,30 +200,58 @@ inline void load_rrr63(Reader &in, PlainBits *out) {
     if (invert.bit_size < n_sb || btnrp.size() < n_sb) throw ParseError("rrr: bad superblock arrays");
     const Binomial63 &B = Binomial63::get();
     out->resize(m_size);
-    uint64_t pos = 0;
-    for (uint64_t b = 0; b < n_blocks; ++b) {
-        if (b % K == 0) {
-            const uint64_t p = btnrp.get(b / K);   // file-controlled: must not run backwards or past the offsets
-            if (p > btnr.bit_size || (b && p < pos)) throw ParseError("rrr: superblock pointer out of range");
-            pos = p;
+    // Superblocks (32 blocks = 2016 bits = 63 u32 words) are independent: each starts at its own offset pointer and
+    // on a word boundary of the output, so large vectors are decoded by several host threads.
+    auto decode_range = [&](uint64_t sb0, uint64_t sb1) {
+        uint64_t pos = 0;
+        const uint64_t b_end = std::min<uint64_t>(n_blocks, sb1 * K);
+        for (uint64_t b = sb0 * K; b < b_end; ++b) {
+            if (b % K == 0) {
+                const uint64_t p = btnrp.get(b / K);   // file-controlled: must not run backwards or past the offsets
+                if (p > btnr.bit_size || (b > sb0 * K && p < pos) || (b && p < btnrp.get(b / K - 1)))
+                    throw ParseError("rrr: superblock pointer out of range");
+                pos = p;
+            }
+            unsigned stored = unsigned(bt.get(b));
+            if (stored > BS) throw ParseError("rrr: block type out of range");
+            unsigned sp = B.space[stored];  // space[k] == space[63-k]
+            unsigned k = invert.bit(b / K) ? BS - stored : stored;
+            uint64_t start = b * BS;
+            unsigned len = unsigned(std::min<uint64_t>(BS, m_size - std::min(m_size, start)));
+            if (sp) {
+                if (pos > btnr.bit_size || sp > btnr.bit_size - pos) throw ParseError("rrr: btnr overrun");
+                uint64_t nr = btnr.get_bits(pos, sp);
+                uint64_t bits = B.decode(k, nr);
+                if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");
+                out->or_bits(start, bits, len);
+            } else if (k == BS) {
+                if (len < BS) throw ParseError("rrr: bits beyond the end");
+                out->or_bits(start, ~uint64_t(0), len);
+            }
+            pos += sp;
         }
-        unsigned stored = unsigned(bt.get(b));
-        if (stored > BS) throw ParseError("rrr: block type out of range");
-        unsigned sp = B.space[stored];  // space[k] == space[63-k]
-        unsigned k = invert.bit(b / K) ? BS - stored : stored;
-        uint64_t start = b * BS;
-        unsigned len = unsigned(std::min<uint64_t>(BS, m_size - std::min(m_size, start)));
-        if (sp) {
-            if (pos > btnr.bit_size || sp > btnr.bit_size - pos) throw ParseError("rrr: btnr overrun");
-            uint64_t nr = btnr.get_bits(pos, sp);
-            uint64_t bits = B.decode(k, nr);
-            if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");
-            out->or_bits(start, bits, len);
-        } else if (k == BS) {
-            if (len < BS) throw ParseError("rrr: bits beyond the end");
-            out->or_bits(start, ~uint64_t(0), len);
-        }
-        pos += sp;
+    };
+    unsigned n_thr = 1;
+    if (n_sb >= (uint64_t(1) << 12)) {
+        n_thr = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+        if (const char *e = std::getenv("GGQ_LOAD_THREADS")) n_thr = std::max(1, std::atoi(e));
+    }
+    if (n_thr <= 1) {
+        decode_range(0, n_sb);
+    } else {
+        std::vector<std::thread> pool;
+        std::vector<std::string> errors(n_thr);
+        for (unsigned t = 0; t < n_thr; ++t)
+            pool.emplace_back([&, t] {
+                try {
+                    decode_range(n_sb * t / n_thr, n_sb * (t + 1) / n_thr);
+                } catch (const std::exception &e) {
+                    errors[t] = e.what()[0] ? e.what() : "rrr: decode failed";
+                }
+            });
+        for (std::thread &th : pool) th.join();
+        for (const std::string &e : errors)
+            if (!e.empty()) throw ParseError(e);
     }
     out->count();
 }

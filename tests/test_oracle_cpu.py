@@ -155,3 +155,28 @@ def test_space_model_constant_of_the_device_builder(ref):
     src = open(os.path.join(ROOT, "genome_graph_annotation_b200", "csrc", "ggq_build_greedy.cuh")).read()
     k = re.search(r"kSizeofBitVectorRrrBits = (\d+) \* 8", src)
     assert k and int(k.group(1)) == f()
+
+
+def test_threaded_rrr_decode_of_large_vectors(ref, monkeypatch):
+    """Vectors of >= 2^12 superblocks are decoded by several host threads (ggq_format.hpp: load_rrr63); the parse of
+    a 9e6-row reference stream must give the reference's statistics with 1, 3 and many threads, and a stream whose
+    payload is damaged must still be rejected, not crash."""
+    import genome_graph_annotation_b200 as g
+    n = 9_000_000
+    cw = ref.gen_norepl(n, 3, 0.2, seed=3)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, threads=8)
+    data = rm.serialize()
+    for thr in ("1", "3", "16"):
+        monkeypatch.setenv("GGQ_LOAD_THREADS", thr)
+        info = g.inspect_brwt(data)
+        assert (info["num_rows"], info["num_columns"], info["num_relations"], info["num_nodes"], info["total_column_size"]) == \
+            (n, 3, rm.num_relations, rm.num_nodes, rm.total_column_size), thr
+        assert info["consumed"] == len(data)
+    bad = bytearray(data)
+    for i in range(len(bad) // 2, len(bad) // 2 + 4096):
+        bad[i] = 0xFF
+    try:
+        info = g.inspect_brwt(bytes(bad))   # flipped offsets may still decode to SOME vector; it must not crash
+        assert info["num_rows"] == n
+    except g.GgqError as e:
+        assert e.code == -1
