@@ -1484,7 +1484,7 @@ void ggq_rows_result_free(ggq_rows_result *r) {
 // rows per chunk of the pipelined host calls (GGQ_CHUNK_LOG2 overrides for experiments)
 static u64 pipeline_chunk() {
     const char *e = std::getenv("GGQ_CHUNK_LOG2");
-    const u64 l = e && *e ? std::strtoull(e, nullptr, 10) : 20;
+    const u64 l = e && *e ? std::strtoull(e, nullptr, 10) : 21;
     return u64(1) << std::min<u64>(std::max<u64>(l, 10), 30);
 }
 // count_labels returns only num_columns counters, so nothing but the first host->device copy is exposed: larger

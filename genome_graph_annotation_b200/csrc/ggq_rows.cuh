@@ -167,7 +167,7 @@ __device__ __forceinline__ void load_rec(const Img &img, u32 g, u32 half, u64 &b
 // (for the C4 tree: 3 levels, 22.9 of 33.4 probes per row) whenever a row has a single label under Z.
 __device__ __forceinline__ u32 ld_code(const unsigned char *p) {
     u32 v;
-    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(v) : "l"(p));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u8 %0, [%1];" : "=r"(v) : "l"(p));   // (a plain miss fetches 128 B)
     return v;
 }
 

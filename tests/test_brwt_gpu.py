@@ -151,11 +151,11 @@ def test_bad_stream_is_rejected(ggq, ref):
         assert e.value.code == -1  # GGQ_ERR_FORMAT  <->  BRWT::load() == false (BRWT.cpp:108-110)
 
 
-def test_config1_norepl_1e5(ggq, ref):
-    # experiments/main.cpp:216-217 generator (seed 42), reduced to 1e5 x 100 so the CPU build takes seconds
-    n, m = 100_000, 100
+def test_config1_norepl_1e6(ggq, ref):
+    # BASELINE config 1 at its full size: experiments/main.cpp:216-217 generator (seed 42), 1e6 x 100, brwt_greedy_relax_7
+    n, m = 1_000_000, 100
     cw = ref.gen_norepl(n, m, 0.01, seed=42)
-    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=7, threads=8)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=7, threads=16)
     gm = ggq.GpuMatrix.load_brwt(rm.serialize())
     rows = np.arange(n, dtype=np.uint64)
     off, cols = gm.get_rows_csr(rows)
@@ -172,13 +172,14 @@ def test_config1_norepl_1e5(ggq, ref):
 
 
 def test_config2_uniform_rows_multi_brwt(ggq, ref):
-    """BASELINE config 2 (SURVEY 8d "C2 concrete input"), reduced to 1e5 x 1000 so the CPU build takes seconds:
-    generate_random_rows(2e4 unique x 5, shuffled) seed 42 (experiments/main.cpp:232-247), Multi-BRWT = greedy
-    partitioner + relax(7); batched get_rows over all rows and over random ids at batch sizes 1 / 1e2 / 1e4 / all,
-    get_column for 10 random columns and a sweep of the others."""
-    n, m = 100_000, 1000
+    """BASELINE config 2 (SURVEY 8d "C2 concrete input") at its full size, 1e6 x 1000:
+    generate_random_rows(2e5 unique x 5, shuffled) seed 42 (experiments/main.cpp:232-247), Multi-BRWT = greedy
+    partitioner + relax(7) (the reference builder takes about a minute on the box's host threads); batched get_rows
+    over all rows and over random ids at batch sizes 1 / 1e2 / 1e4 / all, get_column for 10 random columns and a
+    sweep of the others."""
+    n, m = 1_000_000, 1000
     cw = ref.gen_uniform_rows(n, m, 0.01, n // 5, seed=42)
-    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=7, threads=8)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=7, threads=16)
     gm = ggq.GpuMatrix.load_brwt(rm.serialize())
     try:
         assert (gm.num_rows, gm.num_columns, gm.num_relations) == (n, m, rm.num_relations)

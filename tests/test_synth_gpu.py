@@ -447,3 +447,39 @@ def test_compact_host_call_matches_get_rows_into(ggq, n, m, d):
         assert tot == c.size and np.array_equal(cnt, np.diff(o.astype(np.int64)).astype(np.uint16)) and np.array_equal(ids[:tot], c.astype(np.uint16))
     finally:
         gd.close()
+
+
+def test_pipelined_calls_on_the_c4_column_geometry_against_direct_evaluation(ggq):
+    """A batch above 2^20 rows (the chunk pipeline of ggq_get_rows_into / ggq_get_rows_compact / ggq_count_labels) on
+    the benchmark's tile geometry (2652 columns: 83 bitmap words, 3 summary words per row, leaf codes in use), checked
+    against an expectation that owes nothing to the engine: direct evaluation of the implicit matrix
+    M[i][j] = mix64(seed*K + i*m + j) < T on a 1-in-23 sample of the batch, and the histogram of that evaluation."""
+    import bench
+    n, m, d = 4_000_000, 2652, 0.003
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=bench.SEED, arity=4)
+    try:
+        assert gm.leaf_codes["in_use"]
+        rows = np.random.default_rng(8).integers(0, n, (1 << 21) + 54_321).astype(np.uint64)
+        off = np.empty(rows.size + 1, np.uint64)
+        cols = np.empty(int(rows.size * m * d * 1.2) + 4096, np.uint32)
+        total = gm.get_rows_into(rows, off, cols)
+        pick = np.arange(0, rows.size, 23)
+        counts, ids = bench.direct_rows(rows[pick], m, d, threads=8)
+        assert np.array_equal(np.diff(off.astype(np.int64))[pick], counts.astype(np.int64))
+        starts = off[pick].astype(np.int64)
+        got = np.concatenate([cols[s:s + c] for s, c in zip(starts, counts.astype(np.int64))])
+        assert np.array_equal(got.astype(np.uint64), ids)
+        # the compact call on the same batch
+        cnt8 = np.empty(rows.size, np.uint8)
+        ids16 = np.empty(cols.size, np.uint16)
+        assert gm.get_rows_compact(rows.astype(np.uint32), cnt8, ids16) == total
+        assert np.array_equal(cnt8.astype(np.int64), np.diff(off.astype(np.int64)))
+        assert np.array_equal(ids16[:total], cols[:total].astype(np.uint16))
+        # count_labels over a batch above 2^22 rows (its own chunk pipeline): histogram of the direct evaluation,
+        # the sample taken four times
+        big = np.tile(rows[pick], 52)[: (1 << 22) + 1000]
+        reps = np.bincount(np.arange(big.size) % pick.size, minlength=pick.size)
+        hist = np.bincount(ids.astype(np.int64), weights=np.repeat(reps, counts.astype(np.int64)), minlength=m)
+        assert np.array_equal(gm.count_labels(big), hist.astype(np.uint64))
+    finally:
+        gm.close()
