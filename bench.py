@@ -100,7 +100,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 50 ms.  The sampler is started before the warm-up steps
+    """nvidia-smi clocks + throttle reasons sampled every 20 ms.  The sampler is started before the warm-up steps
     (nvidia-smi needs up to a second to come up on an 8-GPU box) and only the samples stamped inside the timed
     region are kept; if the region was too short to catch any, the samples of warm-up + timed region (the same
     load) are reported and `window` says so."""
@@ -120,7 +120,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
@@ -357,6 +357,10 @@ def run_ours(args):
     build_s = time.time() - t0
     ws = gm.workspace()
     stream = torch.cuda.ExternalStream(ws.stream, device=torch.device("cuda", local))
+    # nvidia-smi needs up to a second to come up: start it now, long before the timed region (the timed steps of the
+    # coded descent take ~0.1-0.2 s in all)
+    clocks = ClockSampler(local)
+    clocks.start()
 
     # distinct batches of row ids (seeded per rank); cycled if K + W exceeds the pool
     n_pool = min(K + W, 6)
@@ -388,8 +392,6 @@ def run_ours(args):
         gm.set_option("leaf_codes", 1)
 
     # ---- device-resident number ----------------------------------------------------------
-    clocks = ClockSampler(local)
-    clocks.start()
     for i in range(W):
         device_step(i)
     barrier()
@@ -661,6 +663,8 @@ def c5_measure(args, dist, rank, world, local, K, W):
     comm = g.Comm(ids[0], rank, world, local)
     n, m, d, B = int(args.c5_rows), args.c5_cols, args.c5_density, args.c5_batch
     slice_mode = not args.c5_full
+    clocks = ClockSampler(local)
+    clocks.start()   # (well before the timed region: nvidia-smi takes a while to come up)
     t0 = time.time()
     gm = g.GpuMatrix.synthesize_brwt_shard(n, m, d, rank, world, seed=SEED, arity=args.arity, device=local)
     torch.cuda.synchronize()
@@ -688,8 +692,6 @@ def c5_measure(args, dist, rank, world, local, K, W):
     if not args.no_peer:
         # merge straight from the peers' partial CSRs over NVLink (cudaIpc); capacity: this batch size, ids with slack
         comm.enable_peer(ws, B, int(B * m * d * 1.3 / world) + (1 << 20))
-    clocks = ClockSampler(local)
-    clocks.start()
     for i in range(W):
         step(i)
     barrier()
