@@ -690,6 +690,21 @@ static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, 
 Workspace::Workspace(const Matrix *m_) : m(m_) {
     CUDA_CHECK(cudaSetDevice(m->device));
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    if (const char *e = std::getenv("GGQ_L2_PERSIST")) {
+        // Experiment (north star: "node headers staged in ... the L2 persisting window"): pin the descent's group
+        // records in the persisting part of L2.  Measured on C4: no effect — the 22 KB table is hit
+        // every iteration by every warp and never leaves L1/L2 anyway — so it stays off by default.
+        if (*e && *e != '0' && m->kind == Matrix::BRWT && (m->group_rec16.p || m->group_rec.p)) {
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, size_t(4) << 20);
+            cudaStreamAttrValue attr{};
+            attr.accessPolicyWindow.base_ptr = m->compact_rec ? (void *)m->group_rec16.p : (void *)m->group_rec.p;
+            attr.accessPolicyWindow.num_bytes = m->compact_rec ? m->group_rec16.bytes() : m->group_rec.bytes();
+            attr.accessPolicyWindow.hitRatio = 1.0f;
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            CUDA_CHECK(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        }
+    }
     d_ctrl.alloc(8);
     d_err.alloc(1);
     CUDA_CHECK(cudaMallocHost(&h_ctrl, 32 * sizeof(u64)));
@@ -1784,42 +1799,27 @@ static u64 filter_labels_device(const ggq_matrix *m, Workspace *ws, u64 min_coun
     return kept;
 }
 
+static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                             const u64 *min_counts, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                             uint64_t capacity, uint64_t *n_out);
+
 static int labels_query(const ggq_matrix *m, const uint64_t *rows, uint64_t n, u64 min_count, bool top, u64 limit,
                         uint64_t *cols, uint64_t *counts, uint64_t *n_out) {
     if (!m || (!rows && n) || !n_out) return fail(GGQ_ERR_ARG, "bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
     Workspace *ws = m->acquire();
     try {
-        // one query sequence (<= 1024 indices), threshold only: descent, histogram, filter back to back on the stream,
-        // results written into pinned host memory by the filter kernel, ONE synchronisation
+        // one query sequence, threshold only: the direct form of the label batch with a single query — one
+        // host-to-device copy, the descent, one CTA that builds the histogram from the descent's chunks, thresholds it
+        // and writes the kept pairs into pinned host memory, ONE synchronisation
         const u64 nc_s = m->tree.n_cols;
-        if (m->kind == Matrix::BRWT && !top && n >= 1 && n <= u64(kSmallRows) && n < m->sort_min_n && nc_s >= 1 &&
-            nc_s <= (u64(1) << 16)) {
-            ws->reserve_rows(n);
-            ws->stage_reserve((2 + 2 * nc_s) * 8);
-            if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
-            if (ws->d_counts.n < nc_s) ws->d_counts.alloc(nc_s);
-            cudaStream_t st = ws->stream;
-            u64 *host = reinterpret_cast<u64 *>(ws->h_stage);
-            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
-            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
-            CUDA_CHECK(cudaMemsetAsync(ws->d_counts.p, 0, nc_s * 8, st));
-            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
-            col_hist_small_kernel<<<8, 512, 0, st>>>(ws->d_tmp.p, ws->d_ctrl.p, ws->d_tmp.n, ws->d_counts.p);
-            label_filter_small_kernel<<<1, 1024, 0, st>>>(ws->d_counts.p, u32(nc_s), min_count, ws->d_ctrl.p, ws->d_tmp.n, host);
-            CUDA_CHECK(cudaGetLastError());
-            CUDA_CHECK(cudaStreamSynchronize(st));
-            if (host[1] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
-            if (!(host[1] & 3)) {
-                const u64 kept = host[0];
-                if (kept && cols) std::memcpy(cols, host + 2, kept * 8);
-                if (kept && counts) std::memcpy(counts, host + 2 + nc_s, kept * 8);
-                *n_out = kept;
-                ws->launches = 3; ws->kernel_timed = false;
-                m->release(ws);
-                return GGQ_OK;
-            }
-            // the chunk arena has to grow: the general path does that
+        if (m->kind == Matrix::BRWT && !top && n >= 1 && n <= u64(kSmallRows) && nc_s >= 1 && nc_s <= (u64(1) << 15)) {
+            m->release(ws);   // (the batch call takes its own workspace)
+            const uint64_t qoff[2] = {0, n};
+            uint64_t loff[2] = {0, 0};
+            if (cols) return labels_batch_core(m, rows, qoff, 1, &min_count, loff, cols, counts, nc_s, n_out);
+            std::vector<uint64_t> tmp(nc_s);
+            return labels_batch_core(m, rows, qoff, 1, &min_count, loff, tmp.data(), counts, nc_s, n_out);
         }
         ws->reserve_rows(n);
         if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, ws->stream));
@@ -1866,13 +1866,12 @@ static u64 min_label_count(u64 n_indices, double ratio) {
 constexpr u64 kBatchSmallRows = u64(1) << 14;   // direct form of the label batch: indices of all queries together
 constexpr u64 kBatchSmallQueries = 1024;
 
-int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
-                                const double *presence_ratios, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
-                                uint64_t capacity, uint64_t *n_out) {
+// min_counts[q]: a label of query q is kept iff its count is non-zero and >= min_counts[q]
+static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                             const u64 *min_counts, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                             uint64_t capacity, uint64_t *n_out) {
     GGQ_TRY
-    if (!m || !query_offsets || !label_offsets || !n_out || (!presence_ratios && n_queries)) return fail(GGQ_ERR_ARG, "bad argument");
-    for (u64 q = 0; q < n_queries; ++q)
-        if (!(presence_ratios[q] >= 0.0 && presence_ratios[q] <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
+    if (!m || !query_offsets || !label_offsets || !n_out || (!min_counts && n_queries)) return fail(GGQ_ERR_ARG, "bad argument");
     if (query_offsets[0] != 0) return fail(GGQ_ERR_ARG, "query_offsets[0] must be 0");
     for (u64 q = 0; q < n_queries; ++q)
         if (query_offsets[q + 1] < query_offsets[q]) return fail(GGQ_ERR_ARG, "query_offsets must be non-decreasing");
@@ -1899,17 +1898,19 @@ int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const
         // straight from the caller's memory
         const u64 cap_pairs = u64(1) << 16;
         const bool direct = m->kind == Matrix::BRWT && n >= 1 && n <= kBatchSmallRows && n_queries <= kBatchSmallQueries;
+        // direct form: [query offsets | minimum counts | rows] in one pinned block and ONE host-to-device copy into
+        // d_qoff (the descent reads its rows from there)
         const size_t n_staged = direct ? size_t(n) : 0;
-        const size_t in_words = n_staged + (n_queries + 1) + n_queries;
+        const size_t in_words = (n_queries + 1) + n_queries + n_staged;
         ws->stage_reserve((in_words + 2 + 2 * n_queries + (direct ? cap_pairs : 0)) * 8);
+        if (direct && ws->d_qoff.n < in_words) ws->d_qoff.alloc(std::max<size_t>(in_words, 2 * kBatchSmallQueries + 2 + kBatchSmallRows));
         u64 *h_in = reinterpret_cast<u64 *>(ws->h_stage);
-        if (n_staged) std::memcpy(h_in, rows, n * 8);
-        std::memcpy(h_in + n_staged, query_offsets, (n_queries + 1) * 8);
-        for (u64 q = 0; q < n_queries; ++q)
-            h_in[n_staged + n_queries + 1 + q] = min_label_count(query_offsets[q + 1] - query_offsets[q], presence_ratios[q]);
-        // device: rows -> d_rows; offsets + minimum counts -> d_qoff (n_queries + 1 | n_queries)
-        if (n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, direct ? static_cast<const void *>(h_in) : static_cast<const void *>(rows), n * 8, cudaMemcpyHostToDevice, st));
-        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in + n_staged, (2 * n_queries + 1) * 8, cudaMemcpyHostToDevice, st));
+        std::memcpy(h_in, query_offsets, (n_queries + 1) * 8);
+        if (n_queries) std::memcpy(h_in + n_queries + 1, min_counts, n_queries * 8);
+        if (n_staged) std::memcpy(h_in + 2 * n_queries + 1, rows, n * 8);
+        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in, in_words * 8, cudaMemcpyHostToDevice, st));
+        const u64 *d_batch_rows = direct ? ws->d_qoff.p + 2 * n_queries + 1 : ws->d_rows.p;
+        if (n && !direct) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
         const u64 *d_minc = ws->d_qoff.p + n_queries + 1;
         bool done = false;
         if (direct) {
@@ -1918,7 +1919,7 @@ int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const
             host[0] = 0;
             if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
             CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
-            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
+            launch_rows_kernel(m, ws, d_batch_rows, nullptr, n);
             CUDA_CHECK(cudaFuncSetAttribute(query_labels_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
             query_labels_direct_kernel<<<u32(n_queries), 256, hist_smem, st>>>(
                 ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p, ws->d_qoff.p, d_minc, u32(nc),
@@ -1962,6 +1963,7 @@ int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const
         }
         if (!done) {
             u64 total = 0;
+            if (direct && n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, d_batch_rows, n * 8, cudaMemcpyDeviceToDevice, st));
             rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
             if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
             CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
@@ -2000,6 +2002,20 @@ int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const
     m->release(ws);
     return rc;
     GGQ_CATCH
+}
+
+int ggq_get_labels_batch_ratios(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
+                                const double *presence_ratios, uint64_t *label_offsets, uint64_t *cols, uint64_t *counts,
+                                uint64_t capacity, uint64_t *n_out) {
+    if (!query_offsets || (!presence_ratios && n_queries)) return fail(GGQ_ERR_ARG, "bad argument");
+    std::vector<u64> minc;
+    try { minc.resize(size_t(n_queries)); } catch (const std::bad_alloc &) { return fail(GGQ_ERR_OOM, "out of memory"); }
+    for (u64 q = 0; q < n_queries; ++q) {
+        if (!(presence_ratios[q] >= 0.0 && presence_ratios[q] <= 1.0)) return fail(GGQ_ERR_ARG, "presence_ratio must be in [0, 1]");
+        if (query_offsets[q + 1] < query_offsets[q]) return fail(GGQ_ERR_ARG, "query_offsets must be non-decreasing");
+        minc[q] = min_label_count(query_offsets[q + 1] - query_offsets[q], presence_ratios[q]);
+    }
+    return labels_batch_core(m, rows, query_offsets, n_queries, minc.data(), label_offsets, cols, counts, capacity, n_out);
 }
 
 int ggq_get_labels_batch(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
