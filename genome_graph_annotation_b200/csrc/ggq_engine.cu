@@ -494,7 +494,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
         if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
         lane_plain_off[li] = total_words;
         const FlatNode &nd = t.nodes[t.lane_node[li]];
-        total_words += fill ? (nd.size + 31) / 32 + 4 : nd.bits.w.size();
+        total_words += (fill || nd.lazy) ? (nd.size + 31) / 32 + 4 : nd.bits.w.size();
     }
     {
         DeviceBuf<u32> d_plain;
@@ -506,8 +506,17 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
         } else {
             for (u32 li = 0; li < n_lanes; ++li) {
                 if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
-                const auto &w = t.nodes[t.lane_node[li]].bits.w;
+                FlatNode &nd = t.nodes[t.lane_node[li]];
+                if (nd.lazy) {   // decode now, upload, forget: the host holds the plain bits of one node at a time
+                    decode_rrr63(nd.raw, &nd.bits);
+                    if (nd.bits.size != nd.size || (!nd.children.empty() && nd.bits.ones != nd.ones))
+                        throw ParseError("BRWT: child length differs from the parent's popcount");
+                    nd.ones = nd.bits.ones;
+                    nd.raw.clear();
+                }
+                const auto &w = nd.bits.w;
                 CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+                if (nd.lazy) { nd.bits.w.clear(); nd.bits.w.shrink_to_fit(); }
             }
         }
         upload_vec(d_off, lane_plain_off);
@@ -525,7 +534,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
         }
         CUDA_CHECK(cudaDeviceSynchronize());
     }
-    for (FlatNode &n : t.nodes) { n.bits.w.clear(); n.bits.w.shrink_to_fit(); }
+    for (FlatNode &n : t.nodes) { n.bits.w.clear(); n.bits.w.shrink_to_fit(); n.raw.clear(); }
     m->finalize_arena(t, true);
     m->refresh_img();
     m->build_leaf_codes();
@@ -1026,7 +1035,7 @@ static int brwt_load_reader(Reader &in, int device, ggq_matrix **out, u32 shard 
     GGQ_TRY
     if (!out) return fail(GGQ_ERR_ARG, "null out");
     ParsedNode root;
-    load_brwt_node(in, &root);
+    load_brwt_node(in, &root, /*lazy=*/true);   // vectors stay undecoded until their upload (upload_brwt)
     FlatTree t;
     flatten_parsed(std::move(root), &t);
     if (n_shards < 1 || shard >= n_shards) return fail(GGQ_ERR_ARG, "bad shard");
@@ -1879,8 +1888,12 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
     if (!rows && n) return fail(GGQ_ERR_ARG, "bad argument");
     if (n_queries >= (u64(1) << 31)) return fail(GGQ_ERR_LIMIT, "too many queries in one batch");
     CUDA_CHECK(cudaSetDevice(m->device));
-    int max_smem = 0;
-    CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+    static std::atomic<int> max_smem_cached{0};
+    int max_smem = max_smem_cached.load(std::memory_order_relaxed);
+    if (!max_smem) {
+        CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+        max_smem_cached.store(max_smem, std::memory_order_relaxed);
+    }
     const u64 nc = m->tree.n_cols;
     const size_t hist_smem = size_t(std::max<u64>(nc, 1)) * 4;
     if (hist_smem + 1024 > size_t(max_smem)) return fail(GGQ_ERR_LIMIT, "too many columns for the per-query shared-memory histogram");
@@ -1920,7 +1933,8 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
             if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
             CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
             launch_rows_kernel(m, ws, d_batch_rows, nullptr, n);
-            CUDA_CHECK(cudaFuncSetAttribute(query_labels_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
+            if (hist_smem > 48 * 1024)   // (a driver call that serialises concurrent callers: only when the opt-in is needed)
+                CUDA_CHECK(cudaFuncSetAttribute(query_labels_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
             query_labels_direct_kernel<<<u32(n_queries), 256, hist_smem, st>>>(
                 ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p, ws->d_qoff.p, d_minc, u32(nc),
                 u32(n_queries), host, cap_pairs);
@@ -1966,7 +1980,8 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
             if (direct && n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, d_batch_rows, n * 8, cudaMemcpyDeviceToDevice, st));
             rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
             if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
-            CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
+            if (hist_smem > 48 * 1024)
+                CUDA_CHECK(cudaFuncSetAttribute(query_labels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
             query_labels_kernel<<<u32(n_queries), 256, hist_smem, st>>>(ws->d_offsets.p, reinterpret_cast<const u32 *>(ws->d_out.p),
                                                                        ws->d_qoff.p, u32(nc), d_minc, ws->d_qstage_cols.p,
                                                                        ws->d_qstage_cnt.p, ws->d_qkept.p);

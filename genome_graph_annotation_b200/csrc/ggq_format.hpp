@@ -181,23 +181,39 @@ struct Binomial63 {
     }
 };
 
-inline void load_rrr63(Reader &in, PlainBits *out) {
+// The serialized arrays of one rrr_vector<63>, undecoded: about the size they have in the stream.  A BRWT keeps
+// these per node until the node is uploaded (lazy decode: the host never holds the plain bits of more than one node).
+struct RrrRaw {
+    uint64_t m_size = 0;
+    IntVector bt, btnr, btnrp, invert;
+    bool empty = true;   // default-constructed rrr_vector (empty matrix) / nothing read
+    void clear() { *this = RrrRaw(); }
+};
+
+inline void read_rrr63_raw(Reader &in, RrrRaw *r) {
     const unsigned BS = 63, K = 32;
-    uint64_t m_size = in.u64le();
-    IntVector bt, btnr, btnrp, rank, invert;
-    bt.load(in, true);
-    btnr.load(in, false, 1);
-    btnrp.load(in, true);
+    r->m_size = in.u64le();
+    IntVector rank;
+    r->bt.load(in, true);
+    r->btnr.load(in, false, 1);
+    r->btnrp.load(in, true);
     rank.load(in, true);
-    invert.load(in, false, 1);
-    if (m_size == 0 && bt.bit_size == 0) {  // default-constructed rrr_vector (empty matrix)
-        out->resize(0);
-        return;
-    }
-    uint64_t n_blocks = (m_size + BS) / BS;  // includes the trailing dummy/partial block
-    if (bt.width < 6 || bt.size() != n_blocks) throw ParseError("rrr: bad block-type array");
-    uint64_t n_sb = (n_blocks + K - 1) / K;
-    if (invert.bit_size < n_sb || btnrp.size() < n_sb) throw ParseError("rrr: bad superblock arrays");
+    r->invert.load(in, false, 1);
+    r->empty = r->m_size == 0 && r->bt.bit_size == 0;
+    if (r->empty) return;
+    const uint64_t n_blocks = (r->m_size + BS) / BS;  // includes the trailing dummy/partial block
+    if (r->bt.width < 6 || r->bt.size() != n_blocks) throw ParseError("rrr: bad block-type array");
+    const uint64_t n_sb = (n_blocks + K - 1) / K;
+    if (r->invert.bit_size < n_sb || r->btnrp.size() < n_sb) throw ParseError("rrr: bad superblock arrays");
+}
+
+inline void decode_rrr63(const RrrRaw &raw, PlainBits *out) {
+    const unsigned BS = 63, K = 32;
+    if (raw.empty) { out->resize(0); return; }
+    const uint64_t m_size = raw.m_size;
+    const IntVector &bt = raw.bt, &btnr = raw.btnr, &btnrp = raw.btnrp, &invert = raw.invert;
+    const uint64_t n_blocks = (m_size + BS) / BS;
+    const uint64_t n_sb = (n_blocks + K - 1) / K;
     const Binomial63 &B = Binomial63::get();
     out->resize(m_size);
     // Superblocks (32 blocks = 2016 bits = 63 u32 words) are independent: each starts at its own offset pointer and
@@ -254,6 +270,12 @@ inline void load_rrr63(Reader &in, PlainBits *out) {
             if (!e.empty()) throw ParseError(e);
     }
     out->count();
+}
+
+inline void load_rrr63(Reader &in, PlainBits *out) {
+    RrrRaw raw;
+    read_rrr63_raw(in, &raw);
+    decode_rrr63(raw, out);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -354,7 +376,8 @@ inline void load_stat(Reader &in, PlainBits *out) {
 struct ParsedNode {
     std::vector<std::vector<uint32_t>> partition;  // RangePartition::partition_
     uint64_t n_cols = 0;
-    PlainBits bits;                                // nonzero_rows_
+    PlainBits bits;                                // nonzero_rows_ (eager parse)
+    RrrRaw raw;                                    // ... or its serialized arrays (lazy parse: bits.size is set, w empty)
     std::vector<ParsedNode> children;
 };
 
@@ -382,15 +405,27 @@ inline void load_range_partition(Reader &in, ParsedNode *node) {
     node->n_cols = total;
 }
 
-inline void load_brwt_node(Reader &in, ParsedNode *node, int depth = 0) {
+// lazy: keep every node's vector undecoded (decode_rrr63 at upload time)
+inline void load_brwt_node(Reader &in, ParsedNode *node, bool lazy = false, int depth = 0) {
     if (depth > 4096) throw ParseError("BRWT: implausible depth");
     load_range_partition(in, node);
-    load_rrr63(in, &node->bits);
+    if (lazy) {
+        read_rrr63_raw(in, &node->raw);
+        if (node->raw.empty) node->bits.resize(0);   // nothing to decode: an ordinary (empty) vector
+        else node->bits.size = node->raw.m_size;
+    } else {
+        load_rrr63(in, &node->bits);
+    }
     uint64_t n_children = in.u64be();
     if (n_children && n_children != node->partition.size())
         throw ParseError("BRWT: children do not match the partition");  // BRWT.cpp:106-107
+    if (lazy && depth == 0 && n_children == 0 && !node->raw.empty) {
+        // a root that is a leaf (single column): its popcount sizes its own select samples, so decode it now
+        decode_rrr63(node->raw, &node->bits);
+        node->raw.clear();
+    }
     node->children.resize(n_children);
-    for (auto &c : node->children) load_brwt_node(in, &c, depth + 1);
+    for (auto &c : node->children) load_brwt_node(in, &c, lazy, depth + 1);
 }
 
 }  // namespace ggq

@@ -579,55 +579,6 @@ __global__ void publish_ctrl_kernel(const u64 *ctrl, u64 *host) {
     __threadfence_system();
 }
 
-// Small-batch form of the label queries (one query sequence = 10^2..10^3 indices): the histogram kernel learns the
-// number of ids from the descent's control words on the device, and the filter writes the kept pairs and a status
-// word straight into pinned host memory — no host round trip between descent, histogram and threshold.
-//   host[0] = kept pairs, host[1] = status (bit 0: stack overflow, bit 1: arena too small -> general path),
-//   host[2 .. 2+n_cols) = columns, host[2+n_cols .. 2+2 n_cols) = counts
-__global__ void __launch_bounds__(512)
-col_hist_small_kernel(const u32 *ids, const u64 *ctrl, u64 tmp_cap, u64 *counts) {
-    const u64 n_ids = ctrl[0] <= tmp_cap ? ctrl[0] : 0;   // (too small an arena: nothing was stored; flagged by the filter)
-    const u64 stride = u64(gridDim.x) * blockDim.x;
-    for (u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x; i < n_ids; i += stride) atomicAdd(counts + ids[i], 1ull);
-}
-
-__global__ void __launch_bounds__(1024)
-label_filter_small_kernel(const u64 *counts, u32 n_cols, u64 min_count, const u64 *ctrl, u64 tmp_cap, u64 *host) {
-    __shared__ u32 warp_cnt[32];
-    __shared__ u32 base_s;
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) base_s = 0;
-    __syncthreads();
-    u64 *out_cols = host + 2, *out_counts = host + 2 + n_cols;
-    for (u32 j0 = 0; j0 < n_cols; j0 += 1024) {
-        const u32 j = j0 + threadIdx.x;
-        const u64 c = j < n_cols ? counts[j] : 0;
-        const bool keep = c != 0 && c >= min_count;
-        const u32 bal = __ballot_sync(0xffffffffu, keep);
-        if (lane == 0) warp_cnt[warp] = __popc(bal);
-        __syncthreads();
-        u32 before = 0, total = 0;
-        for (u32 w = 0; w < 32; ++w) {
-            const u32 v = warp_cnt[w];
-            if (w < warp) before += v;
-            total += v;
-        }
-        const u32 base = base_s;
-        if (keep) {
-            const u32 o = base + before + __popc(bal & ((1u << lane) - 1u));
-            out_cols[o] = j;
-            out_counts[o] = c;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) base_s = base + total;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        host[0] = base_s;
-        host[1] = (ctrl[4] ? 1u : 0u) | (ctrl[0] > tmp_cap ? 2u : 0u);
-    }
-}
-
 // chunk-local CSR offsets -> global offsets (pipelined host API)
 __global__ void add_base_kernel(u64 *p, u64 n, u64 base) {
     u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;

@@ -30,6 +30,8 @@ struct FlatNode {
     uint32_t first_child_group = 0, n_child_groups = 0;
     uint32_t leaf_rank = 0;          // leaves: DFS rank of the first column
     PlainBits bits;                  // empty for synthetic trees
+    RrrRaw raw;                      // lazy load: the undecoded vector (bits.w empty until upload decodes it)
+    bool lazy = false;
 };
 
 struct FlatTree {
@@ -99,6 +101,9 @@ inline void flatten_parsed(ParsedNode &&root, FlatTree *t) {
         n.bits = std::move(p.bits);
         n.size = n.bits.size;
         n.ones = n.bits.ones;
+        n.lazy = !p.raw.empty || (n.bits.w.empty() && n.bits.size != 0);
+        n.raw = std::move(p.raw);
+        if (n.lazy && !p.children.empty()) n.ones = p.children[0].bits.size;   // popcount = length of every child (checked at decode)
         if (n.parent >= 0 && n.size != t->nodes[n.parent].ones)
             throw ParseError("BRWT: child length differs from the parent's popcount");
     }

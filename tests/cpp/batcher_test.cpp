@@ -70,10 +70,20 @@ int main(int argc, char **argv) {
                 for (int q = 0; q < Q; ++q) {
                     const Query &w = work[t][q];
                     if (batched) {
-                        lb->get_labels(w.idx, w.ratio, &c, &v);
+                        try {
+                            lb->get_labels(w.idx, w.ratio, &c, &v);
+                        } catch (const std::exception &e) {
+                            std::fprintf(stderr, "batcher_test: thread %d query %d: %s\n", t, q, e.what());
+                            ++wrong;
+                            continue;
+                        }
                     } else {
                         uint64_t k = 0;
-                        if (ggq_get_labels(mat, w.idx.data(), w.idx.size(), w.ratio, cb.data(), vb.data(), &k) != GGQ_OK) { ++wrong; continue; }
+                        if (ggq_get_labels(mat, w.idx.data(), w.idx.size(), w.ratio, cb.data(), vb.data(), &k) != GGQ_OK) {
+                            std::fprintf(stderr, "batcher_test: thread %d query %d: %s\n", t, q, ggq_last_error());
+                            ++wrong;
+                            continue;
+                        }
                         c.assign(cb.begin(), cb.begin() + k);
                         v.assign(vb.begin(), vb.begin() + k);
                     }
