@@ -1035,7 +1035,8 @@ static int brwt_load_reader(Reader &in, int device, ggq_matrix **out, u32 shard 
     GGQ_TRY
     if (!out) return fail(GGQ_ERR_ARG, "null out");
     ParsedNode root;
-    load_brwt_node(in, &root, /*lazy=*/true);   // vectors stay undecoded until their upload (upload_brwt)
+    const char *eager = std::getenv("GGQ_LOAD_EAGER");   // (A/B of the load path's host memory: scripts/load_probe.py)
+    load_brwt_node(in, &root, /*lazy=*/!(eager && *eager && *eager != '0'));   // vectors stay undecoded until their upload
     FlatTree t;
     flatten_parsed(std::move(root), &t);
     if (n_shards < 1 || shard >= n_shards) return fail(GGQ_ERR_ARG, "bad shard");
@@ -1904,9 +1905,8 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
     try {
         ws->reserve_rows(n);
         cudaStream_t st = ws->stream;
-        if (ws->d_qoff.n < 2 * n_queries + 2) {
-            ws->d_qoff.alloc(2 * n_queries + 2); ws->d_qlab_off.alloc(n_queries + 2); ws->d_qkept.alloc(n_queries + 2);
-        }
+        if (ws->d_qoff.n < 2 * n_queries + 2) ws->d_qoff.alloc(2 * n_queries + 2);
+        if (ws->d_qlab_off.n < n_queries + 2) { ws->d_qlab_off.alloc(n_queries + 2); ws->d_qkept.alloc(n_queries + 2); }
         // small batches: one pinned block [rows | query offsets | per-query minimum counts]; large ones copy the rows
         // straight from the caller's memory
         const u64 cap_pairs = u64(1) << 16;

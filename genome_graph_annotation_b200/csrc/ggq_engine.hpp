@@ -23,7 +23,8 @@ int fail(int code, const std::string &msg);
     do {                                                                                          \
         cudaError_t _e = (expr);                                                                  \
         if (_e != cudaSuccess) {                                                                  \
-            if (_e == cudaErrorMemoryAllocation) { cudaGetLastError(); throw std::bad_alloc(); }  \
+            cudaGetLastError(); /* clear the thread's last-error slot: a later launch check must not see this one */ \
+            if (_e == cudaErrorMemoryAllocation) throw std::bad_alloc();                          \
             throw ggq::CudaError(std::string(#expr) + ": " + cudaGetErrorString(_e));             \
         }                                                                                         \
     } while (0)
