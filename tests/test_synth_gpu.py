@@ -483,3 +483,24 @@ def test_pipelined_calls_on_the_c4_column_geometry_against_direct_evaluation(ggq
         assert np.array_equal(gm.count_labels(big), hist.astype(np.uint64))
     finally:
         gm.close()
+
+
+def test_label_batch_forms_alternate_on_one_matrix(ggq):
+    """The direct (<= 2^14 indices) and the general form of the label batch share a workspace's scratch: alternate
+    them on one matrix (a direct call first sized the shared input buffer and starved the general form's buffers
+    once) and compare every answer with the single-query call."""
+    n, m, d = 200_000, 300, 0.02
+    gm = ggq.GpuMatrix.synthesize_brwt(n, m, d, seed=3, arity=4)
+    try:
+        rng = np.random.default_rng(2)
+        for sizes in ([300] * 5, [300] * 80, [7, 300, 1], [250] * 100, [300] * 3):
+            qoff = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+            rows = rng.integers(0, n, int(qoff[-1])).astype(np.uint64)
+            ratios = rng.choice([0.0, 0.05, 0.5], size=len(sizes))
+            loff, cols, cnt = gm.get_labels_batch(rows, qoff, ratios)
+            for q in range(0, len(sizes), max(1, len(sizes) // 7)):
+                ec, ev = gm.get_labels(rows[int(qoff[q]):int(qoff[q + 1])], float(ratios[q]))
+                a, b = int(loff[q]), int(loff[q + 1])
+                assert np.array_equal(cols[a:b], ec) and np.array_equal(cnt[a:b], ev), (len(sizes), q)
+    finally:
+        gm.close()
