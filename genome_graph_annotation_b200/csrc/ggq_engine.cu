@@ -1542,7 +1542,7 @@ static int get_rows_into(const ggq_matrix *m, const void *rows_v, int row_bytes,
         for (u64 r = std::max<u64>(c / 8, u64(1) << 18); r < c; r *= 2) ramp.push_back(r);
         u64 ramp_sum = 0;
         for (u64 r : ramp) ramp_sum += r;
-        if (!ramp.empty() && n >= 2 * ramp_sum + c) {
+        if (!ramp.empty() && n >= 2 * ramp_sum + c && !std::getenv("GGQ_NO_RAMP")) {
             for (u64 r : ramp) start.push_back(start.back() + r);
             while (n - start.back() > ramp_sum + c) start.push_back(start.back() + c);
             const u64 rest = n - start.back() - ramp_sum;   // in (0, c]
@@ -1550,7 +1550,7 @@ static int get_rows_into(const ggq_matrix *m, const void *rows_v, int row_bytes,
             for (size_t i = ramp.size(); i-- > 1;) start.push_back(start.back() + ramp[i]);
             start.push_back(n);
         } else {
-            const u64 cs = std::min<u64>(c, u64(1) << 20);
+            const u64 cs = std::getenv("GGQ_NO_RAMP") ? c : std::min<u64>(c, u64(1) << 20);
             while (n - start.back() > cs) start.push_back(start.back() + cs);
             if (n > start.back() || start.size() == 1) start.push_back(n);
         }

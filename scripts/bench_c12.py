@@ -50,7 +50,17 @@ def run(name, n, m, d, gen, build_kw, args, g, R):
     line = {"config": name, "rows": n, "cols": m, "density": d, "builder": build_kw, "reference_build_s": build_s,
             "stream_bytes": len(data), "gpu_load_s": load_s, "device_image_bytes": int(gm.device_bytes),
             "num_nodes": int(gm.num_nodes), "avg_arity": float(rm.avg_arity),
-            "node_touches_per_row": float(gm.total_column_size) / n, "cpu_threads": threads}
+            "node_touches_per_row": float(gm.total_column_size) / n, "cpu_threads": threads,
+            "leaf_codes": gm.leaf_codes}
+    # the device builder on the same columns: same tree as the reference builder's, and how long it takes
+    t0 = time.time()
+    gd = g.GpuMatrix.build_brwt(cw, n, greedy=build_kw.get("greedy", False), arity=build_kw.get("arity", 2),
+                                relax=build_kw.get("relax", 0))
+    line["device_build_s"] = time.time() - t0
+    sa, sb = gd.tree_shape(), gm.tree_shape()
+    assert all(np.array_equal(sa[k], sb[k]) for k in sa), "device builder: tree differs from the reference builder's"
+    line["device_builder_same_tree"] = True
+    gd.close()
     # ---- get_rows over all rows in order (parity on every row) ---------------------------------------------
     all_rows = np.arange(n, dtype=np.uint64)
     eoff, ecols, cpu_s = rm.get_rows(all_rows, threads=threads)
@@ -67,11 +77,15 @@ def run(name, n, m, d, gen, build_kw, args, g, R):
     roff, rcols, _ = rm.get_rows(rnd, threads=threads)
     cpu_rnd_s = rm.time_get_rows(rnd, threads)[0]
     per_batch = {}
+    h_rcols = np.empty(max(int(roff[-1]), 1), np.uint32)
     for bs in (100, 10_000, n):
         nb = max(1, min(n // bs, 200))
         def go():
             for b in range(nb):
-                gm.get_rows_csr(rnd[b * bs:(b + 1) * bs])
+                if bs >= 10_000:   # caller-provided buffers, as a real bulk caller would use
+                    gm.get_rows_into(rnd[b * bs:(b + 1) * bs], h_off[:bs + 1], h_rcols)
+                else:
+                    gm.get_rows_csr(rnd[b * bs:(b + 1) * bs])
         o, c = gm.get_rows_csr(rnd[:bs])
         assert np.array_equal(o, roff[:bs + 1]) and np.array_equal(c, rcols[:int(roff[bs])]), "random batch differs"
         per_batch[str(bs)] = nb * bs / timed(go, reps=2)
