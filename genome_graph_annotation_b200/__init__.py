@@ -69,6 +69,9 @@ def lib():
         "ggq_get_rows_sharded_slice_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, u64p, u64p, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_brwt_build_columns": (C.c_int, [u64p, C.c_uint64, C.c_uint64, C.c_int, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(vp)]),
         "ggq_tree_shape": (C.c_int, [vp, u64p, C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), u64p, u64p, C.POINTER(C.c_uint32)]),
+        "ggq_brwt_serialize": (C.c_int, [vp, C.c_void_p, vp, u64p]),
+        "ggq_brwt_serialize_buffer": (C.c_int, [vp, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_size_t)]),
+        "ggq_rrr63_encode_buffer": (C.c_int, [u64p, C.c_uint64, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_size_t)]),
         "ggq_brwt_inspect_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p]),
         "ggq_brwt_inspect_columns": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
         "ggq_num_rows": (C.c_uint64, [vp]),
@@ -219,6 +222,19 @@ class Comm:
             self._h = None
 
 
+def rrr63_encode(words, n_bits):
+    """Host only: bytes of sdsl's rrr_vector<63>(bits).serialize() for the given plain bits."""
+    w = np.ascontiguousarray(words, dtype=np.uint64)
+    if w.size == 0:
+        w = np.zeros(1, np.uint64)
+    out = C.POINTER(C.c_uint8)()
+    n = C.c_size_t()
+    _check(lib().ggq_rrr63_encode_buffer(w.ctypes.data_as(u64p), n_bits, C.byref(out), C.byref(n)))
+    data = C.string_at(out, n.value)
+    lib().ggq_buffer_free(out)
+    return data
+
+
 def inspect_brwt(data):
     """Host-only parse + flatten of a serialized BRWT (no GPU needed) -> dict of stats."""
     stats = (C.c_uint64 * 8)()
@@ -271,6 +287,15 @@ class GpuMatrix:
         h = C.c_void_p()
         _check(lib().ggq_brwt_build_columns(cw.ctypes.data_as(u64p), n_rows, m, int(greedy), arity, relax, device, C.byref(h)))
         return cls(h.value, "brwt")
+
+    def serialize(self):
+        """BRWT::serialize from the device image (ggq_brwt_serialize_buffer) -> bytes."""
+        out = C.POINTER(C.c_uint8)()
+        n = C.c_size_t()
+        _check(lib().ggq_brwt_serialize_buffer(self._h, C.byref(out), C.byref(n)))
+        data = C.string_at(out, n.value)
+        lib().ggq_buffer_free(out)
+        return data
 
     def tree_shape(self):
         """dict of per-node arrays in level order: parent, n_children, n_columns, size, ones, first_column."""

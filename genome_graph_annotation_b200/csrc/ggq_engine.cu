@@ -20,6 +20,7 @@
 
 #include "../../include/ggq.h"
 #include "ggq_format.hpp"
+#include "ggq_rrr_write.hpp"
 #include "ggq_tree.hpp"
 #include "ggq_kernels.cuh"
 #include "ggq_engine.hpp"
@@ -693,6 +694,74 @@ static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, 
     return upload_brwt(std::move(t), device, 0, 1, &fill);
 }
 
+// BRWT::serialize (BRWT.cpp:113-128) from the device image: pre-order; per node its RangePartition (the stream's own
+// when the matrix was parsed from one, else derived from the column arrangements: group g = positions of child g's
+// columns among this node's), its vector read back from the slot arena and re-encoded as the reference's
+// rrr_vector<63> (ggq_rrr_write.hpp: byte-identical arrays), the child count, the children.
+static void serialize_brwt(const Matrix *m, ByteSink &sink) {
+    const FlatTree &t = m->tree;
+    if (m->kind != Matrix::BRWT || t.nodes.empty())
+        throw std::runtime_error("serialize needs the host tree (not kept for column-major matrices and image files)");
+    if (t.n_shards > 1) throw std::runtime_error("a column shard cannot serialize the whole matrix");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    if (t.n_cols == 0) {   // BRWT(): no groups, a default rrr_vector, no children
+        sink.u64be(0);
+        write_rrr63_default(sink);
+        sink.u64be(0);
+        return;
+    }
+    DeviceBuf<u32> d_plain;
+    std::vector<u64> words;
+    std::vector<u32> pos_of;   // column -> position in the current node's arrangement
+    struct Frame { u32 id; size_t next; };
+    std::vector<Frame> stack = {{0u, 0}};
+    while (!stack.empty()) {
+        Frame &f = stack.back();
+        const FlatNode &n = t.nodes[f.id];
+        if (f.next == 0) {
+            // RangePartition
+            if (!n.partition.empty()) {
+                sink.u64be(n.partition.size());
+                for (const auto &g : n.partition) write_u32_vector(sink, g);
+            } else if (n.children.empty()) {
+                sink.u64be(1);
+                std::vector<u32> ident(n.cols.size());
+                for (size_t i = 0; i < ident.size(); ++i) ident[i] = u32(i);
+                write_u32_vector(sink, ident);
+            } else {
+                pos_of.assign(t.n_cols, 0);
+                for (size_t i = 0; i < n.cols.size(); ++i) pos_of[n.cols[i]] = u32(i);
+                sink.u64be(n.children.size());
+                std::vector<u32> grp;
+                for (int c : n.children) {
+                    grp.clear();
+                    for (u32 col : t.nodes[c].cols) grp.push_back(pos_of[col]);
+                    write_u32_vector(sink, grp);
+                }
+            }
+            // nonzero_rows_
+            const u32 li = n.group * 4 + n.lane;
+            const u64 hot = t.group_hot[n.group], nb = t.group_nblocks[n.group];
+            const u64 n_words = (n.size + 63) / 64;
+            words.assign(std::max<u64>(n_words, (3 * nb + 1) / 2 + 1), 0);
+            if (nb) {
+                if (d_plain.n < 3 * nb) d_plain.alloc(3 * nb + 3 * nb / 8);
+                unpack_lane_kernel<<<u32((nb + 255) / 256), 256>>>(m->slots.p, hot, nb, li & 3, d_plain.p);
+                CUDA_CHECK(cudaGetLastError());
+                CUDA_CHECK(cudaMemcpy(words.data(), d_plain.p, size_t(3) * nb * 4, cudaMemcpyDeviceToHost));   // LE u32 pairs = u64
+            }
+            write_rrr63(sink, reinterpret_cast<const uint64_t *>(words.data()), n.size);
+            sink.u64be(n.children.size());
+        }
+        if (f.next < n.children.size()) {
+            const u32 c = u32(n.children[f.next++]);
+            stack.push_back({c, 0});
+        } else {
+            stack.pop_back();
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // Workspaces
 // ------------------------------------------------------------------------------------------
@@ -1166,6 +1235,60 @@ int ggq_tree_shape(const ggq_matrix *m, uint64_t *n_nodes, int64_t *parent, uint
         if (first_column) first_column[i] = N[i].cols.empty() ? ~0u : N[i].cols[0];
     }
     return GGQ_OK;
+}
+
+int ggq_brwt_serialize(const ggq_matrix *m, ggq_write_fn write, void *ctx, uint64_t *n_bytes) {
+    GGQ_TRY
+    if (!m || !write) return fail(GGQ_ERR_ARG, "bad argument");
+    ByteSink sink;
+    sink.write = write;
+    sink.ctx = ctx;
+    serialize_brwt(m, sink);
+    if (n_bytes) *n_bytes = sink.total;
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_brwt_serialize_buffer(const ggq_matrix *m, uint8_t **out, size_t *len) {
+    GGQ_TRY
+    if (!m || !out || !len) return fail(GGQ_ERR_ARG, "bad argument");
+    std::string bytes;
+    ByteSink sink;
+    sink.out = &bytes;
+    serialize_brwt(m, sink);
+    uint8_t *buf = static_cast<uint8_t *>(std::malloc(std::max<size_t>(bytes.size(), 1)));
+    if (!buf) throw std::bad_alloc();
+    std::memcpy(buf, bytes.data(), bytes.size());
+    *out = buf;
+    *len = bytes.size();
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+// Host only (no device needed): the bytes rrr_vector<63>(bits).serialize() writes — the building block of
+// ggq_brwt_serialize, exported so that the CPU tests can pin it against the reference byte for byte.
+int ggq_rrr63_encode_buffer(const uint64_t *words, uint64_t n_bits, uint8_t **out, size_t *len) {
+    GGQ_TRY
+    if (!out || !len || (!words && n_bits)) return fail(GGQ_ERR_ARG, "bad argument");
+    std::string bytes;
+    ByteSink sink;
+    sink.out = &bytes;
+    std::vector<u64> padded;   // clear the padding bits of the last word
+    const u64 n_words = (n_bits + 63) / 64;
+    const u64 *w = reinterpret_cast<const u64 *>(words);
+    if (n_bits & 63) {
+        padded.assign(w, w + n_words);
+        padded[n_words - 1] &= (u64(1) << (n_bits & 63)) - 1;
+        w = padded.data();
+    }
+    write_rrr63(sink, reinterpret_cast<const uint64_t *>(w), n_bits);
+    uint8_t *buf = static_cast<uint8_t *>(std::malloc(std::max<size_t>(bytes.size(), 1)));
+    if (!buf) throw std::bad_alloc();
+    std::memcpy(buf, bytes.data(), bytes.size());
+    *out = buf;
+    *len = bytes.size();
+    return GGQ_OK;
+    GGQ_CATCH
 }
 
 int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t stats[8]) {

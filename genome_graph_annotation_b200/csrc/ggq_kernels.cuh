@@ -614,6 +614,16 @@ __global__ void slice_rows_kernel(const u64 *offsets, const u32 *cols, u64 n, u6
     out[o] = ~0ull;
 }
 
+// One lane of the arena back to plain bits (3 data words per block): the inverse of pack_plain_kernel, used by
+// ggq_brwt_serialize.
+__global__ void unpack_lane_kernel(const uint4 *slots, u64 hot, u64 n_blocks, u32 lane, u32 *plain) {
+    const u64 b = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    const u32 sl = u32(hot >> kGhStrideShift) & 3u;
+    const uint4 s = slots[(hot & kGhBaseMask) + (b << sl) + lane];
+    plain[3 * b] = s.y; plain[3 * b + 1] = s.z; plain[3 * b + 2] = s.w;
+}
+
 // ------------------------------------------------------------------------------------------
 // Leaf codes (ggq_rows.cuh): for an internal node Z with first child group g0 and ones(Z) = n_pos positions in its
 // children's vectors, codes[p] = DFS index (relative to the subtree's first leaf, rank0) of the only leaf set below

@@ -32,6 +32,7 @@ struct FlatNode {
     PlainBits bits;                  // empty for synthetic trees
     RrrRaw raw;                      // lazy load: the undecoded vector (bits.w empty until upload decodes it)
     bool lazy = false;
+    std::vector<std::vector<uint32_t>> partition;   // parsed trees: the node's RangePartition as it was in the stream
 };
 
 struct FlatTree {
@@ -98,6 +99,7 @@ inline void flatten_parsed(ParsedNode &&root, FlatTree *t) {
             n.cols.resize(map.size());
             for (size_t c = 0; c < map.size(); ++c) n.cols[c] = par.cols[map[c]];
         }
+        n.partition = p.partition;   // (kept for ggq_brwt_serialize; src[id]->partition is still read by the children)
         n.bits = std::move(p.bits);
         n.size = n.bits.size;
         n.ones = n.bits.ones;

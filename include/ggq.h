@@ -41,6 +41,8 @@ typedef struct ggq_rows_result ggq_rows_result;  /* host-resident CSR result of 
 /* Pull reader used by the stream loaders: must copy exactly n bytes to dst and return n, or return
  * fewer on EOF/error.  Lets BinaryMatrix::load(std::istream&) consume exactly the matrix' bytes. */
 typedef size_t (*ggq_read_fn)(void *ctx, void *dst, size_t n);
+/* Output callback of ggq_brwt_serialize: takes n bytes, returns the number it took (fewer than n = failure). */
+typedef size_t (*ggq_write_fn)(void *ctx, const void *src, size_t n);
 
 const char *ggq_last_error(void);
 int ggq_device_count(int *count);
@@ -82,6 +84,18 @@ int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, ui
 /* Host-only: DFS (= get_row) order of the columns and the root-to-leaf depth of every column of a
  * serialized BRWT.  dfs_cols / depth: num_columns entries each, caller-allocated (may be NULL). */
 int ggq_brwt_inspect_columns(const uint8_t *buf, size_t len, uint32_t *dfs_cols, uint32_t *depth);
+
+/* BRWT::serialize (annotation/hierarchical_annotation/BRWT.cpp:113-128) FROM THE DEVICE IMAGE: every node's vector is
+ * read back from the arena and re-encoded as the reference's rrr_vector<63>, byte for byte what the reference writes
+ * for the same tree — so a matrix built on the device (ggq_brwt_build_columns) becomes a .brwt the reference loads, and
+ * a loaded matrix needs no host copy of its stream to be written back.  Needs the host tree: not available for
+ * column-major matrices, column shards and matrices restored from an image file (GGQ_ERR_INTERNAL with a message). */
+int ggq_brwt_serialize(const ggq_matrix *m, ggq_write_fn write, void *ctx, uint64_t *n_bytes);
+int ggq_brwt_serialize_buffer(const ggq_matrix *m, uint8_t **out, size_t *len);   /* *out: ggq_buffer_free */
+
+/* Host only: the bytes sdsl's rrr_vector<63>(bits).serialize() writes for the given plain bits (LSB-first words) —
+ * the building block of ggq_brwt_serialize.  *out is malloc'ed (ggq_buffer_free). */
+int ggq_rrr63_encode_buffer(const uint64_t *words, uint64_t n_bits, uint8_t **out, size_t *len);
 
 /* The reference's BRWT construction on the device: BRWTBottomUpBuilder::build(columns, partitioner)
  * (annotation/hierarchical_annotation/BRWT_builders.cpp:122-163) with partitioner 0 = get_basic_partitioner(arity)

@@ -132,8 +132,10 @@ class GpuMatrixBase : public BinaryMatrix {
     void serialize(std::ostream &out) const override {
         if (!out.good()) throw std::ofstream::failure("Error when dumping the matrix");
         if (have_stream_) { out.write(stream_.data(), std::streamsize(stream_.size())); return; }
-        if (stream_path_.empty())
-            throw std::ofstream::failure("ggq: serialize(): the matrix has neither a host copy of its stream nor a stream path");
+        if (stream_path_.empty()) {
+            serialize_from_device(out);   // BRWT: re-encoded from the device image; others throw
+            return;
+        }
         std::ifstream in(stream_path_, std::ios::binary);
         if (!in.good()) throw std::ofstream::failure("ggq: cannot read the serialized matrix at " + stream_path_);
         in.seekg(std::streamoff(stream_offset_));
@@ -146,6 +148,12 @@ class GpuMatrixBase : public BinaryMatrix {
             out.write(buf.data(), got);
             left -= uint64_t(got);
         }
+    }
+
+    // No host copy and no file: the engine writes the reference's stream format from the device image
+    // (ggq_brwt_serialize; BRWT matrices that still have their host tree — loaded from a stream or built on the device).
+    virtual void serialize_from_device(std::ostream &) const {
+        throw std::ofstream::failure("ggq: serialize(): the matrix has neither a host copy of its stream nor a stream path");
     }
 
     // Do not keep a host copy of the stream read by the next load() (serialize() then needs set_stream_path()).
@@ -234,7 +242,37 @@ class GpuBRWT final : public GpuMatrixBase {
     // the GPU-resident layout without parsing the stream again.  `stream_path` (optional) names the serialized
     // matrix the image was made from; it is read back only if serialize() is called.
     void save_image(const std::string &path) const { check(ggq_image_save(handle(), path.c_str())); }
-    // Without a stream_path serialize() throws (an image alone cannot reproduce the reference's stream).
+    void serialize_from_device(std::ostream &out) const override {
+        struct W {
+            static size_t put(void *ctx, const void *src, size_t n) {
+                std::ostream *o = static_cast<std::ostream *>(ctx);
+                o->write(static_cast<const char *>(src), std::streamsize(n));
+                return o->good() ? n : 0;
+            }
+        };
+        if (ggq_brwt_serialize(handle(), &W::put, &out, nullptr) != GGQ_OK)
+            throw std::ofstream::failure(std::string("ggq: serialize(): ") + ggq_last_error());
+    }
+    // Builds the matrix on the device from explicit columns (ggq_brwt_build_columns: the reference's bottom-up builder
+    // with the basic or the greedy partitioner + relax); serialize() then writes what the reference builder would.
+    bool build(const std::vector<std::vector<uint64_t>> &column_words, uint64_t n_rows, bool greedy, uint32_t arity = 2,
+               uint64_t relax_arity = 0) {
+        const uint64_t W = (n_rows + 63) / 64;
+        std::vector<uint64_t> flat(column_words.size() * W);
+        for (size_t j = 0; j < column_words.size(); ++j) {
+            if (column_words[j].size() < W) return false;
+            std::copy(column_words[j].begin(), column_words[j].begin() + W, flat.begin() + j * W);
+        }
+        ggq_matrix *m = nullptr;
+        if (ggq_brwt_build_columns(flat.data(), n_rows, column_words.size(), greedy ? 1 : 0, arity, relax_arity, device_, &m) != GGQ_OK)
+            return false;
+        h_.reset(m, [](ggq_matrix *p) { ggq_free(p); });
+        stream_.clear();
+        have_stream_ = false;
+        stream_path_.clear();
+        return true;
+    }
+    // Image without a stream_path: serialize() throws (the image does not carry the host tree).
     bool load_image(const std::string &path, const std::string &stream_path = std::string()) {
         ggq_matrix *m = nullptr;
         if (ggq_image_load(path.c_str(), device_, &m) != GGQ_OK) return false;

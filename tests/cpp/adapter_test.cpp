@@ -130,6 +130,20 @@ static void check_brwt(Columns &&cols, int arity, bool relax) {
     std::ostringstream sink;
     try { image_only.serialize(sink); } catch (const std::ios_base::failure &) { threw = true; }
     REQUIRE(threw && sink.str().empty());
+    // no host copy, no file: serialize() re-encodes the device image into the reference's stream format
+    {
+        ggq::GpuBRWT no_copy;
+        no_copy.keep_stream(false);
+        std::istringstream in2(stream);
+        REQUIRE(no_copy.load(in2));
+        std::ostringstream from_device;
+        no_copy.serialize(from_device);
+        REQUIRE(from_device.str() == stream);
+        BRWT back;   // ... which the reference loads
+        std::istringstream in3(from_device.str());
+        REQUIRE(back.load(in3));
+        REQUIRE(back.num_relations() == ref.num_relations());
+    }
     // load_file(): no host copy of the stream; serialize() re-reads the file
     ggq::GpuBRWT from_file;
     REQUIRE(from_file.load_file(ser));

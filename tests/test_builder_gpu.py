@@ -2,7 +2,8 @@
 partitioner + BRWTOptimizer::relax, SURVEY.md 8f-3) against the UNMODIFIED reference builder
 (annotation/hierarchical_annotation/BRWT_builders.cpp, partitionings.cpp behind oracle/_ref/libggref.so) on identical
 columns: the SAME TREE must come out — every node's parent, arity, column count, first column, vector length and
-popcount, in level order — and therefore the same answers, order included."""
+popcount, in level order — and therefore the same answers, order included, and the same SERIALIZED BYTES
+(ggq_brwt_serialize re-encodes the device image as the reference's RangePartition + rrr_vector<63> stream)."""
 import numpy as np
 import pytest
 
@@ -13,7 +14,8 @@ pytestmark = pytest.mark.gpu
 
 def compare(ggq, ref, cw, n, rows=None, **kw):
     rm = ref.RefMatrix.build_brwt(cw, n, threads=8, **kw)
-    g_ref = ggq.GpuMatrix.load_brwt(rm.serialize())
+    stream = rm.serialize()
+    g_ref = ggq.GpuMatrix.load_brwt(stream)
     g_dev = ggq.GpuMatrix.build_brwt(cw, n, greedy=kw.get("greedy", False), arity=kw.get("arity", 2), relax=kw.get("relax", 0))
     try:
         assert (g_dev.num_rows, g_dev.num_columns, g_dev.num_relations) == (g_ref.num_rows, g_ref.num_columns, g_ref.num_relations)
@@ -27,6 +29,10 @@ def compare(ggq, ref, cw, n, rows=None, **kw):
         eoff, ecols, _ = rm.get_rows(rows, threads=8)
         off, cols = g_dev.get_rows_csr(rows)
         assert np.array_equal(off, eoff) and np.array_equal(cols, ecols), kw
+        # BRWT::serialize from the device image: the loaded matrix writes back the stream it was loaded from, and the
+        # DEVICE-BUILT matrix writes byte for byte what the reference builder's matrix serializes to
+        assert g_ref.serialize() == stream, kw
+        assert g_dev.serialize() == stream, kw
         m = g_dev.num_columns
         for c in range(0, m, max(1, m // 7)):
             assert np.array_equal(g_dev.get_column(c), rm.get_column(c)), (c, kw)

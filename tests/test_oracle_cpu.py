@@ -180,3 +180,28 @@ def test_threaded_rrr_decode_of_large_vectors(ref, monkeypatch):
         assert info["num_rows"] == n
     except g.GgqError as e:
         assert e.code == -1
+
+
+def test_rrr_writer_is_byte_identical_to_sdsl(ref):
+    """ggq_rrr63_encode_buffer (host only; the building block of ggq_brwt_serialize) against the reference's
+    bit_vector_rrr<63>::serialize on the same bits: every array of sdsl's rrr_vector — block classes, offsets in
+    sdsl's numbering, superblock pointers, rank samples, inversion flags, widths and padding — byte for byte, over
+    the lengths where the construction rule has corners (multiples of 63 and of 2016, partial last blocks) and
+    densities on both sides of the inversion rule."""
+    import genome_graph_annotation_b200 as g
+    rng = np.random.default_rng(1)
+    for n in [0, 1, 5, 62, 63, 64, 125, 126, 127, 2015, 2016, 2017, 4031, 4032, 4033, 63 * 32 * 3, 100_003, 1 << 19]:
+        for d in [0.0, 0.001, 0.1, 0.5, 0.6, 0.9, 1.0]:
+            bits = (rng.random(n) < d).astype(np.uint8)
+            pad = np.zeros(((n + 63) // 64) * 64, np.uint8)
+            pad[:n] = bits
+            w = np.packbits(pad, bitorder="little").view(np.uint64).copy() if n else np.zeros(0, np.uint64)
+            assert g.rrr63_encode(w, n) == ref.RefBitVector.build("rrr", w, n).serialize(), (n, d)
+    # a run of dense superblocks followed by sparse ones: inversion switches inside the vector
+    bits = np.concatenate([np.ones(2016 * 3, np.uint8), (rng.random(2016 * 2 + 100) < 0.02).astype(np.uint8),
+                           (rng.random(5000) < 0.8).astype(np.uint8)])
+    n = bits.size
+    pad = np.zeros(((n + 63) // 64) * 64, np.uint8)
+    pad[:n] = bits
+    w = np.packbits(pad, bitorder="little").view(np.uint64).copy()
+    assert g.rrr63_encode(w, n) == ref.RefBitVector.build("rrr", w, n).serialize()
