@@ -704,9 +704,9 @@ static void serialize_brwt(const Matrix *m, ByteSink &sink) {
         throw std::runtime_error("serialize needs the host tree (not kept for column-major matrices and image files)");
     if (t.n_shards > 1) throw std::runtime_error("a column shard cannot serialize the whole matrix");
     CUDA_CHECK(cudaSetDevice(m->device));
-    if (t.n_cols == 0) {   // BRWT(): no groups, a default rrr_vector, no children
+    if (t.n_cols == 0) {   // BRWT(): no groups, the rrr_vector of an empty bit vector, no children
         sink.u64be(0);
-        write_rrr63_default(sink);
+        write_rrr63(sink, nullptr, 0);
         sink.u64be(0);
         return;
     }

@@ -173,17 +173,6 @@ inline void write_rrr63(ByteSink &s, const uint64_t *words, uint64_t n_bits) {
     invert.write(s, false);
 }
 
-// a default-constructed rrr_vector<63> (the single node of an empty BRWT, tests/test_BRWT.cpp:37-42): every member empty,
-// int_vector<> members with their default width 64
-inline void write_rrr63_default(ByteSink &s) {
-    s.u64le(0);
-    s.u64le(0); s.u8(64);   // m_bt
-    s.u64le(0);             // m_btnr
-    s.u64le(0); s.u8(64);   // m_btnrp
-    s.u64le(0); s.u8(64);   // m_rank
-    s.u64le(0);             // m_invert
-}
-
 // serialize_number_vector<uint32_t> (common/serialization.cpp:38-50): an sdsl::int_vector<> of width 32
 inline void write_u32_vector(ByteSink &s, const std::vector<uint32_t> &v) {
     PackedInts p(v.size(), 32);
