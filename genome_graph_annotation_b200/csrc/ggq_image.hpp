@@ -2,8 +2,10 @@
 // .brwt.annodbg it came from, so that a restart uploads the arrays as they are instead of re-parsing the
 // reference stream (RRR decode, BRWT.cpp:87-111), re-flattening it and rebuilding rank headers / select samples.
 //
-//   header   magic "GGQIMG02", endianness tag, layout constants, matrix shape, the BRWT stats the reference API reports
-//   tables   the host-side geometry (group records, lane tables, leaf order, column paths, shard plan) + FNV-1a
+//   header   magic "GGQIMG03", endianness tag, layout constants, matrix shape, the BRWT stats the reference API reports
+//   tables   the host-side geometry (group records, lane tables, leaf order, column paths, shard plan) and the host tree
+//            (every node's parent, children, column arrangement, vector length and popcount, RangePartition: what
+//            ggq_brwt_serialize / ggq_tree_shape need) + FNV-1a
 //   arrays   slots (16-byte slots with inline rank headers), select samples, superblock bases, lane totals, leaf codes
 //   trailer  end tag (a truncated file is rejected)
 //
@@ -16,7 +18,7 @@
 
 namespace ggq {
 
-static const char kImageMagic[8] = {'G', 'G', 'Q', 'I', 'M', 'G', '0', '2'};
+static const char kImageMagic[8] = {'G', 'G', 'Q', 'I', 'M', 'G', '0', '3'};
 static const u64 kImageEnd = 0x454e44474751494dull;
 static const u32 kImageEndian = 0x01020304u;
 
@@ -155,6 +157,66 @@ inline void image_check_tables(const FlatTree &t, const ImageHeader &h, const st
     }
 }
 
+// The host tree (FlatTree::nodes + lane_node), so that a matrix restored from an image is a full citizen: it can be
+// serialized back into the reference's stream format and inspected node by node.
+inline void image_put_nodes(ImageFile &io, const FlatTree &t) {
+    const u64 n = t.nodes.size();
+    io.put(&n, 8);
+    for (const FlatNode &nd : t.nodes) {
+        const int64_t fixed_i[1] = {nd.parent};
+        const u32 fixed_u[7] = {u32(nd.child_index), u32(nd.depth), nd.group, nd.lane, nd.first_child_group, nd.n_child_groups, nd.leaf_rank};
+        const u64 fixed_q[2] = {nd.size, nd.ones};
+        io.put(fixed_i, sizeof(fixed_i)); io.put(fixed_u, sizeof(fixed_u)); io.put(fixed_q, sizeof(fixed_q));
+        io.put_vec(nd.cols);
+        io.put_vec(nd.children);
+        const u64 ng = nd.partition.size();
+        io.put(&ng, 8);
+        for (const auto &g : nd.partition) io.put_vec(g);
+    }
+    io.put_vec(t.lane_node);
+}
+
+inline void image_get_nodes(ImageFile &io, FlatTree *t, u64 n_cols) {
+    u64 n = 0;
+    io.get(&n, 8);
+    if (n > u64(kMaxGroups) * 4 + 1) throw ParseError("image file: implausible node count");
+    t->nodes.assign(size_t(n), FlatNode());
+    const u64 G = t->group_hot.size();
+    for (u64 id = 0; id < n; ++id) {
+        FlatNode &nd = t->nodes[id];
+        int64_t fixed_i[1];
+        u32 fixed_u[7];
+        u64 fixed_q[2];
+        io.get(fixed_i, sizeof(fixed_i)); io.get(fixed_u, sizeof(fixed_u)); io.get(fixed_q, sizeof(fixed_q));
+        nd.parent = int(fixed_i[0]); nd.child_index = int(fixed_u[0]); nd.depth = int(fixed_u[1]);
+        nd.group = fixed_u[2]; nd.lane = fixed_u[3]; nd.first_child_group = fixed_u[4]; nd.n_child_groups = fixed_u[5];
+        nd.leaf_rank = fixed_u[6];
+        nd.size = fixed_q[0]; nd.ones = fixed_q[1];
+        io.get_vec(&nd.cols, n_cols);
+        io.get_vec(&nd.children, n);
+        u64 ng = 0;
+        io.get(&ng, 8);
+        if (ng > std::max<u64>(n_cols, 1)) throw ParseError("image file: implausible partition");
+        nd.partition.assign(size_t(ng), {});
+        for (auto &g : nd.partition) io.get_vec(&g, n_cols);
+        // sanity: a node refers to earlier parents, later children, existing columns and an existing lane
+        if ((id == 0) != (fixed_i[0] < 0) || fixed_i[0] >= int64_t(id) || nd.group >= G || nd.lane >= kGroupLanes ||
+            nd.ones > nd.size || nd.size >= kMaxRows)
+            throw ParseError("image file: host tree out of range");
+        for (int c : nd.children)
+            if (c <= int(id) || u64(c) >= n) throw ParseError("image file: host tree out of range");
+        for (u32 c : nd.cols)
+            if (c >= n_cols) throw ParseError("image file: host tree out of range");
+        for (const auto &g : nd.partition)
+            for (u32 c : g)
+                if (c >= std::max<u64>(nd.cols.size(), 1)) throw ParseError("image file: host tree out of range");
+    }
+    io.get_vec(&t->lane_node, u64(kMaxGroups) * 4);
+    if (n && t->lane_node.size() != 4 * G) throw ParseError("image file: inconsistent tables");
+    for (u32 v : t->lane_node)
+        if (v != ~0u && v >= n) throw ParseError("image file: host tree out of range");
+}
+
 inline void image_save(const Matrix *m, const char *path) {
     if (m->kind != Matrix::BRWT) throw std::runtime_error("only BRWT images can be saved");
     CUDA_CHECK(cudaSetDevice(m->device));
@@ -177,6 +239,7 @@ inline void image_save(const Matrix *m, const char *path) {
     io.put_vec(t.col_owned); io.put_vec(t.col_owner);
     io.put_vec(m->lane_size_h); io.put_vec(m->lane_ones_h);
     io.put_vec(t.lane_coded); io.put_vec(t.code_rec);
+    image_put_nodes(io, t);
     const u64 check = io.sum.h;
     if (std::fwrite(&check, 1, 8, io.f) != 8) throw std::runtime_error("image write failed");
     PinnedStage st;
@@ -210,6 +273,7 @@ inline Matrix *image_load(const char *path, int device) {
     io.get_vec(&t.col_owned, lim); io.get_vec(&t.col_owner, lim);
     io.get_vec(&m->lane_size_h, u64(kMaxGroups) * 4); io.get_vec(&m->lane_ones_h, u64(kMaxGroups) * 4);
     io.get_vec(&t.lane_coded, u64(kMaxGroups) * 4); io.get_vec(&t.code_rec, u64(kMaxGroups) * 16);
+    image_get_nodes(io, &t, h.n_cols);
     const u64 expect = io.sum.h;
     u64 check = 0;
     if (std::fread(&check, 1, 8, io.f) != 8 || check != expect) throw ParseError("image file: table checksum mismatch");
@@ -220,6 +284,7 @@ inline Matrix *image_load(const char *path, int device) {
         (!t.col_owned.empty() && t.col_owned.size() != t.n_cols))
         throw ParseError("image file: inconsistent tables");
     image_check_tables(t, h, m->lane_ones_h);
+    if (h.n_shards > 1) { t.nodes.clear(); t.lane_node.clear(); }   // (a shard's image does not carry which nodes it holds)
     t.total_slots = h.total_slots; t.total_sb = h.total_sb; t.total_sel = h.total_sel;
     t.max_depth = h.max_depth; t.multi_column_leaves = h.multi_leaf != 0;
     t.shard = h.shard; t.n_shards = h.n_shards; t.cut_depth = h.cut_depth;

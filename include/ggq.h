@@ -88,8 +88,8 @@ int ggq_brwt_inspect_columns(const uint8_t *buf, size_t len, uint32_t *dfs_cols,
 /* BRWT::serialize (annotation/hierarchical_annotation/BRWT.cpp:113-128) FROM THE DEVICE IMAGE: every node's vector is
  * read back from the arena and re-encoded as the reference's rrr_vector<63>, byte for byte what the reference writes
  * for the same tree — so a matrix built on the device (ggq_brwt_build_columns) becomes a .brwt the reference loads, and
- * a loaded matrix needs no host copy of its stream to be written back.  Needs the host tree: not available for
- * column-major matrices, column shards and matrices restored from an image file (GGQ_ERR_INTERNAL with a message). */
+ * a loaded matrix needs no host copy of its stream to be written back (matrices restored from an image file included:
+ * the image carries the host tree).  Not available for column-major matrices and column shards (GGQ_ERR_INTERNAL). */
 int ggq_brwt_serialize(const ggq_matrix *m, ggq_write_fn write, void *ctx, uint64_t *n_bytes);
 int ggq_brwt_serialize_buffer(const ggq_matrix *m, uint8_t **out, size_t *len);   /* *out: ggq_buffer_free */
 
@@ -108,7 +108,7 @@ int ggq_brwt_build_columns(const uint64_t *col_words, uint64_t n_rows, uint64_t 
                            uint64_t relax_arity, int device, ggq_matrix **out);
 /* Tree of a BRWT matrix, nodes in level (BFS) order, children in stored order: parent index (-1: root), number of
  * children / columns, length and popcount of the node's vector, first column of its arrangement.  Arrays may be NULL;
- * *n_nodes is always set.  Not available for matrices restored from an image file (GGQ_ERR_ARG). */
+ * *n_nodes is always set.  Not available for column-major matrices and images of column shards (GGQ_ERR_ARG). */
 int ggq_tree_shape(const ggq_matrix *m, uint64_t *n_nodes, int64_t *parent, uint32_t *n_children, uint32_t *n_columns,
                    uint64_t *size, uint64_t *ones, uint32_t *first_column);
 

@@ -122,14 +122,21 @@ static void check_brwt(Columns &&cols, int arity, bool relax) {
     REQUIRE(restored.num_nodes() == ref.num_nodes());
     compare(ref, restored, stream);
     REQUIRE(!restored.load_image(ser));   // not an image
-    // an image alone cannot reproduce the reference's stream: serialize() must throw, never write a truncated matrix
+    // an image alone (no stream path): the image carries the host tree, serialize() re-encodes the device image
     ggq::GpuBRWT image_only;
     REQUIRE(image_only.load_image(img));
     REQUIRE(image_only.get_column(0) == ref.get_column(0));
-    bool threw = false;
     std::ostringstream sink;
-    try { image_only.serialize(sink); } catch (const std::ios_base::failure &) { threw = true; }
-    REQUIRE(threw && sink.str().empty());
+    image_only.serialize(sink);
+    REQUIRE(sink.str() == stream);
+    // a column-major matrix without its stream has nothing to fall back to: serialize() throws, writes nothing
+    {
+        ggq::GpuColMajor cm;   // not loaded at all
+        bool threw = false;
+        std::ostringstream none;
+        try { cm.serialize(none); } catch (const std::exception &) { threw = true; }
+        REQUIRE(threw && none.str().empty());
+    }
     // no host copy, no file: serialize() re-encodes the device image into the reference's stream format
     {
         ggq::GpuBRWT no_copy;

@@ -74,6 +74,8 @@ def test_image_file_round_trip(ggq, path, tmp_path):
     gm.close()
     gi = ggq.GpuMatrix.load_image(img)
     try:
+        # the image carries the host tree: a restored matrix serializes back to the reference's stream byte for byte
+        assert gi.serialize() == g["stream"].tobytes()
         st = [int(x) for x in g["stats"]]
         assert (gi.num_rows, gi.num_columns, gi.num_relations, gi.num_nodes, gi.total_column_size) == tuple(st[:5])
         n, m = st[0], st[1]
@@ -152,6 +154,19 @@ def test_image_with_valid_checksum_but_insane_tables_is_rejected(ggq, tmp_path):
         cnt = struct.unpack_from("<Q", raw, pos)[0]
         starts.append((pos + 8, cnt, w))
         pos += 8 + cnt * w
+    # the host tree: node count, then per node 52 fixed bytes, cols, children, partition groups; then lane_node
+    def skip_vec(p, w):
+        return p + 8 + struct.unpack_from("<Q", raw, p)[0] * w
+    n_nodes = struct.unpack_from("<Q", raw, pos)[0]
+    pos += 8
+    for _ in range(n_nodes):
+        pos += 8 + 7 * 4 + 2 * 8
+        pos = skip_vec(skip_vec(pos, 4), 4)
+        ng = struct.unpack_from("<Q", raw, pos)[0]
+        pos += 8
+        for _ in range(ng):
+            pos = skip_vec(pos, 4)
+    pos = skip_vec(pos, 4)
     sum_at = pos
     assert struct.unpack_from("<Q", raw, sum_at)[0] == _fnv1a(raw[:sum_at])   # the walk matches the writer
 
