@@ -73,6 +73,9 @@ def parse_args():
     ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
                     help="c4: Kingsford-shaped, replicas (headline); c5: RefSeq-shaped 1e9 x 3173 d=3.8%%, column-sharded "
                          "over all ranks with the NCCL exchange (needs --gpus >= 2)")
+    ap.add_argument("--tree", default="basic", choices=["basic", "greedy_relax7"],
+                    help="basic: BRWTBottomUpBuilder with get_basic_partitioner(arity) (the headline, SURVEY.md 8d); "
+                         "greedy_relax7: the reference's Multi-BRWT recipe (greedy partitioner + relax(7)) on the same matrix")
     ap.add_argument("--spot-rows", type=int, default=1 << 20, help="rows of the full-scale parity sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bitvector", action="store_true", help="skip the rank1/select1/get block (C3)")
@@ -250,9 +253,11 @@ def run_reference(args):
 
 
 def workload_config(args, n_gpus):
-    c = {"workload": "C4 Kingsford-shaped synthetic BRWT %.3g x %d density %g, arity-%d basic partitioner; "
+    tree = ("arity-%d basic partitioner" % args.arity if args.tree == "basic"
+            else "greedy partitioner + relax(7) (the reference's Multi-BRWT recipe, built on the device)")
+    c = {"workload": "C4 Kingsford-shaped synthetic BRWT %.3g x %d density %g, %s; "
                      "get_rows over %d uniformly random row ids per GPU per step" %
-                     (args.rows, args.cols, args.density, args.arity, args.batch),
+                     (args.rows, args.cols, args.density, tree, args.batch),
          "rows": int(args.rows), "cols": args.cols, "density": args.density, "arity": args.arity,
          "batch_rows_per_gpu": args.batch, "seed": SEED,
          "parallelism": "replicas x%d, batch-sharded, no data-path collective" % n_gpus,
@@ -321,6 +326,15 @@ def spot_check(gm, rows, m, density, what="get_rows_csr"):
     t0 = time.time()
     s_off, s_cols = gm.get_rows_csr(rows)
     counts, cols = direct_rows(rows, m, density)
+    dfs = gm.dfs_columns().astype(np.int64)
+    if not np.array_equal(dfs, np.arange(m)):
+        # a tree whose DFS leaf order is not the column order (greedy partitioner): every row must list its columns by
+        # increasing DFS rank — re-order the expectation that way
+        rank = np.empty(m, np.int64)
+        rank[dfs] = np.arange(m)
+        row_of = np.repeat(np.arange(rows.size), counts.astype(np.int64))
+        order = np.lexsort((rank[cols.astype(np.int64)], row_of))
+        cols = cols[order]
     same = (np.array_equal(np.diff(s_off.astype(np.int64)), counts.astype(np.int64)) and
             np.array_equal(np.asarray(s_cols, dtype=np.uint64), cols))
     if not same:
@@ -352,7 +366,10 @@ def run_ours(args):
     B = args.batch
     K, W = args.steps, args.warmup
     t0 = time.time()
-    gm = g.GpuMatrix.synthesize_brwt(n, args.cols, args.density, seed=SEED, arity=args.arity, device=local)
+    if args.tree == "greedy_relax7":
+        gm = g.GpuMatrix.synthesize_brwt_greedy(n, args.cols, args.density, seed=SEED, relax=7, device=local)
+    else:
+        gm = g.GpuMatrix.synthesize_brwt(n, args.cols, args.density, seed=SEED, arity=args.arity, device=local)
     torch.cuda.synchronize()
     build_s = time.time() - t0
     ws = gm.workspace()

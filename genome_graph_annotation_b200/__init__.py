@@ -68,6 +68,8 @@ def lib():
         "ggq_get_rows_sharded_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_get_rows_sharded_slice_device": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_int, u64p, u64p, C.POINTER(vp), C.POINTER(vp), u64p]),
         "ggq_brwt_build_columns": (C.c_int, [u64p, C.c_uint64, C.c_uint64, C.c_int, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(vp)]),
+        "ggq_brwt_synthesize_greedy": (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(vp)]),
+        "ggq_tree_dfs_columns": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
         "ggq_tree_shape": (C.c_int, [vp, u64p, C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), u64p, u64p, C.POINTER(C.c_uint32)]),
         "ggq_brwt_serialize": (C.c_int, [vp, C.c_void_p, vp, u64p]),
         "ggq_brwt_serialize_buffer": (C.c_int, [vp, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_size_t)]),
@@ -296,6 +298,19 @@ class GpuMatrix:
         data = C.string_at(out, n.value)
         lib().ggq_buffer_free(out)
         return data
+
+    @classmethod
+    def synthesize_brwt_greedy(cls, n_rows, n_cols, density, seed=42, relax=7, device=0):
+        """The implicit matrix of synthesize_brwt under the reference's greedy partitioner + relax(relax)."""
+        h = C.c_void_p()
+        _check(lib().ggq_brwt_synthesize_greedy(n_rows, n_cols, density_threshold(density), seed, relax, device, C.byref(h)))
+        return cls(h.value, "brwt")
+
+    def dfs_columns(self):
+        """Columns in the order get_row lists them (DFS leaf order)."""
+        out = np.zeros(max(int(self.num_columns), 1), np.uint32)
+        _check(lib().ggq_tree_dfs_columns(self._h, out.ctypes.data_as(C.POINTER(C.c_uint32))))
+        return out[:int(self.num_columns)]
 
     def tree_shape(self):
         """dict of per-node arrays in level order: parent, n_children, n_columns, size, ones, first_column."""

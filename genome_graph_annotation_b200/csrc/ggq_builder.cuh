@@ -23,7 +23,7 @@ constexpr int kBuildWarps = 4;
 struct BuildInstr {
     u32 op_arity;   // bit 0: 1 = NODE; bits 8..: arity (NODE)
     u32 arg;        // LEAF: column; NODE: index of the first child in child_li[]
-    u32 node_idx;   // NODE: ordinal among internal nodes
+    u32 node_idx;   // NODE: ordinal among internal nodes; LEAF: ordinal among leaves
     u32 pad;
 };
 
@@ -32,6 +32,7 @@ struct BuildArgs {
     u32 n_instr;
     const u32 *child_li;     // lane (group*4+lane) of every child, in program order
     u32 n_internal;
+    u32 n_counters;          // counters per tile: n_internal, or n_internal + leaves when leaves are counted too
     u64 n_rows, n_cols, threshold, seed_mul;
     u64 n_tiles;
     unsigned short *tile_cnt;  // [tile][node_idx]   (pass 1 out)
@@ -45,9 +46,9 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
     extern __shared__ u32 s_cnt_all[];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 lt_mask = (1u << lane) - 1u;
-    u32 *s_cnt = s_cnt_all + size_t(warp) * a.n_internal;
+    u32 *s_cnt = s_cnt_all + size_t(warp) * a.n_counters;
     for (u64 tile = u64(blockIdx.x) * kBuildWarps + warp; tile < a.n_tiles; tile += u64(gridDim.x) * kBuildWarps) {
-        for (u32 i = lane; i < a.n_internal; i += 32) s_cnt[i] = 0;
+        for (u32 i = lane; i < a.n_counters; i += 32) s_cnt[i] = 0;
         __syncwarp();
         const u64 *prefix = FILL ? a.tile_prefix + tile * a.n_internal : nullptr;
         for (u32 step = 0; step < kTileRows / 32; ++step) {
@@ -63,6 +64,11 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
                     u64 bit = (row_ok && mix64(hbase + ins.arg) < a.threshold) ? 1ull : 0ull;
                     stack |= bit << sp;
                     ++sp;
+                    if (!FILL && a.n_counters > a.n_internal) {   // count pass of the shape search: column popcounts too
+                        const u32 c = __popc(__ballot_sync(0xffffffffu, bit != 0));
+                        if (lane == 0 && c) s_cnt[a.n_internal + ins.node_idx] += c;
+                        __syncwarp();
+                    }
                 } else {
                     const u32 ar = ins.op_arity >> 8;
                     sp -= ar;
@@ -123,8 +129,8 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
         }
         if (!FILL) {
             __syncwarp();
-            for (u32 i = lane; i < a.n_internal; i += 32)
-                a.tile_cnt[tile * a.n_internal + i] = (unsigned short)s_cnt[i];
+            for (u32 i = lane; i < a.n_counters; i += 32)
+                a.tile_cnt[tile * a.n_counters + i] = (unsigned short)s_cnt[i];
         }
         __syncwarp();
     }
@@ -144,14 +150,26 @@ __global__ void tile_scan_kernel(const unsigned short *tile_cnt, u64 *tile_prefi
     node_ones[i] = run;
 }
 
-inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, u32 arity, int device,
-                               u32 shard = 0, u32 n_shards = 1) {
+// totals per counter over all tiles (count-only pass)
+__global__ void tile_sum_kernel(const unsigned short *tile_cnt, u64 *totals, u64 n_tiles, u32 n_counters) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_counters) return;
+    u64 run = 0;
+    for (u64 t = 0; t < n_tiles; ++t) run += tile_cnt[t * n_counters + i];
+    totals[i] = run;
+}
+
+// `shape`: FlatTree::nodes (parent / children / cols / depth) of the tree to build.  count_only != null: only evaluate
+// the popcount of EVERY node's index vector (internal nodes and leaves) into (*count_only)[node id] and return null —
+// what BRWTOptimizer::relax needs before the final shape is known.
+inline Matrix *synthesize_brwt_shape(FlatTree &&shape, u64 n_rows, u32 n_cols, u64 threshold, u64 seed, int device,
+                                     u32 shard = 0, u32 n_shards = 1, std::vector<u64> *count_only = nullptr) {
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
     m->device = device;
     CUDA_CHECK(cudaSetDevice(device));
+    m->tree = std::move(shape);
     FlatTree &t = m->tree;
-    build_basic_shape(n_rows, n_cols, arity, &t);
     assign_groups(&t);
     plan_shards(&t, shard, n_shards);
     if (n_rows >= kMaxRows) throw LimitError("too many rows");
@@ -161,7 +179,7 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     std::vector<BuildInstr> prog;
     std::vector<u32> child_li;
     std::vector<int> internal_of(t.nodes.size(), -1);
-    std::vector<u32> internal_nodes;
+    std::vector<u32> internal_nodes, leaf_nodes;
     u32 max_sp = 0;
     if (n_cols) {
         struct Frame { int id; size_t next; };
@@ -172,7 +190,8 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
             Frame &f = st.back();
             const FlatNode &n = t.nodes[f.id];
             if (n.children.empty()) {
-                prog.push_back({0u, n.cols[0], 0u, 0u});
+                prog.push_back({0u, n.cols[0], u32(leaf_nodes.size()), 0u});
+                leaf_nodes.push_back(u32(f.id));
                 max_sp = std::max(max_sp, ++sp);
                 st.pop_back();
             } else if (f.next < n.children.size()) {
@@ -193,6 +212,7 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     }
     if (max_sp > 64) throw LimitError("tree too deep for the device builder");
     const u32 NI = u32(internal_nodes.size());
+    const u32 NC = count_only ? NI + u32(leaf_nodes.size()) : NI;   // counters per tile
     const u64 n_tiles = (n_rows + kTileRows - 1) / kTileRows;
 
     DeviceBuf<BuildInstr> d_prog;
@@ -203,18 +223,18 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     if (!prog.empty()) CUDA_CHECK(cudaMemcpy(d_prog.p, prog.data(), prog.size() * sizeof(BuildInstr), cudaMemcpyHostToDevice));
     d_child.alloc(std::max<size_t>(child_li.size(), 1));
     if (!child_li.empty()) CUDA_CHECK(cudaMemcpy(d_child.p, child_li.data(), child_li.size() * 4, cudaMemcpyHostToDevice));
-    d_cnt.alloc(std::max<u64>(n_tiles * NI, 1));
-    d_prefix.alloc(std::max<u64>(n_tiles * NI, 1));
-    d_ones.alloc(std::max<u32>(NI, 1));
+    d_cnt.alloc(std::max<u64>(n_tiles * NC, 1));
+    if (!count_only) d_prefix.alloc(std::max<u64>(n_tiles * NI, 1));
+    d_ones.alloc(std::max<u32>(NC, 1));
 
     BuildArgs a{};
-    a.prog = d_prog.p; a.n_instr = u32(prog.size()); a.child_li = d_child.p; a.n_internal = NI;
+    a.prog = d_prog.p; a.n_instr = u32(prog.size()); a.child_li = d_child.p; a.n_internal = NI; a.n_counters = NC;
     a.n_rows = n_rows; a.n_cols = n_cols; a.threshold = threshold;
     a.seed_mul = seed * 0x9E3779B97F4A7C15ULL;
     a.n_tiles = n_tiles; a.tile_cnt = d_cnt.p; a.tile_prefix = d_prefix.p;
     int sms = 148;
     CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-    size_t smem = size_t(kBuildWarps) * std::max<u32>(NI, 1) * 4;
+    size_t smem = size_t(kBuildWarps) * std::max<u32>(NC, 1) * 4;
     {
         int max_smem = 0;
         CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
@@ -227,6 +247,20 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     u32 grid = u32(std::min<u64>(u64(sms) * std::max(per_sm, 1), (n_tiles + kBuildWarps - 1) / kBuildWarps));
     if (grid == 0) grid = 1;
 
+    if (count_only) {
+        count_only->assign(t.nodes.size(), 0);
+        if (n_tiles && NC) {
+            brwt_build_kernel<false><<<grid, kBuildWarps * 32, smem>>>(a);
+            CUDA_CHECK(cudaGetLastError());
+            tile_sum_kernel<<<(NC + 127) / 128, 128>>>(d_cnt.p, d_ones.p, n_tiles, NC);
+            CUDA_CHECK(cudaGetLastError());
+            std::vector<u64> tot(NC);
+            CUDA_CHECK(cudaMemcpy(tot.data(), d_ones.p, size_t(NC) * 8, cudaMemcpyDeviceToHost));
+            for (u32 k = 0; k < NI; ++k) (*count_only)[internal_nodes[k]] = tot[k];
+            for (size_t k = 0; k < leaf_nodes.size(); ++k) (*count_only)[leaf_nodes[k]] = tot[NI + k];
+        }
+        return nullptr;
+    }
     std::vector<u64> ones(std::max<u32>(NI, 1), 0);
     if (n_tiles && NI) {
         brwt_build_kernel<false><<<grid, kBuildWarps * 32, smem>>>(a);
@@ -260,6 +294,13 @@ inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, 
     m->build_leaf_codes();
     m->derive_stats();
     return m.release();
+}
+
+inline Matrix *synthesize_brwt(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, u32 arity, int device,
+                               u32 shard = 0, u32 n_shards = 1) {
+    FlatTree t;
+    build_basic_shape(n_rows, n_cols, arity, &t);
+    return synthesize_brwt_shape(std::move(t), n_rows, n_cols, threshold, seed, device, shard, n_shards);
 }
 
 }  // namespace ggq

@@ -543,6 +543,35 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     return m.release();
 }
 
+// Builder tree -> FlatTree::nodes in level order (children in stored order); bn_of[flat id] = builder node.
+static void shape_to_flat(const std::vector<BuildNode> &N, int root, u64 n_rows, u32 n_cols, FlatTree *t, std::vector<int> *bn_of) {
+    struct Pending { int bn, parent, child_index; };
+    std::deque<Pending> q;
+    q.push_back({root, -1, 0});
+    t->nodes.clear();
+    bn_of->clear();
+    while (!q.empty()) {
+        const Pending cu = q.front();
+        q.pop_front();
+        const int id = int(t->nodes.size());
+        t->nodes.emplace_back();
+        bn_of->push_back(cu.bn);
+        FlatNode &fn = t->nodes.back();
+        fn.parent = cu.parent;
+        fn.child_index = cu.child_index;
+        fn.depth = cu.parent < 0 ? 0 : t->nodes[cu.parent].depth + 1;
+        fn.cols = N[cu.bn].cols;
+        if (cu.parent < 0)   // the root's local columns ARE the global ones (as flatten_parsed has it)
+            for (u32 c = 0; c < n_cols; ++c) fn.cols[c] = c;
+        fn.ones = N[cu.bn].ones;
+        fn.size = cu.parent < 0 ? n_rows : t->nodes[cu.parent].ones;
+        if (cu.parent >= 0) t->nodes[cu.parent].children.push_back(id);
+        for (size_t i = 0; i < N[cu.bn].children.size(); ++i) q.push_back({N[cu.bn].children[i], id, int(i)});
+    }
+    t->n_rows = n_rows;
+    t->n_cols = n_cols;
+}
+
 // BRWTBottomUpBuilder::build + BRWTOptimizer::relax on the device (ggq_build_greedy.cuh) from explicit columns:
 // col_words = n_cols columns of ceil(n_rows / 64) LSB-first u64 words each.  partitioner: 0 = basic(arity), 1 = greedy.
 static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, int partitioner, u32 arity,
@@ -640,31 +669,7 @@ static Matrix *build_brwt_columns(const u64 *col_words, u64 n_rows, u32 n_cols, 
     if (root_out) *root_out = root;
     // BFS flattening; bn_of[flat id] = builder node
     std::vector<int> bn_of;
-    {
-        struct Pending { int bn, parent, child_index; };
-        std::deque<Pending> q;
-        q.push_back({root, -1, 0});
-        while (!q.empty()) {
-            const Pending cu = q.front();
-            q.pop_front();
-            const int id = int(t.nodes.size());
-            t.nodes.emplace_back();
-            bn_of.push_back(cu.bn);
-            FlatNode &fn = t.nodes.back();
-            fn.parent = cu.parent;
-            fn.child_index = cu.child_index;
-            fn.depth = cu.parent < 0 ? 0 : t.nodes[cu.parent].depth + 1;
-            fn.cols = N[cu.bn].cols;
-            if (cu.parent < 0)   // the root's local columns ARE the global ones (as flatten_parsed has it)
-                for (u32 c = 0; c < n_cols; ++c) fn.cols[c] = c;
-            fn.ones = N[cu.bn].ones;
-            fn.size = cu.parent < 0 ? n_rows : t.nodes[cu.parent].ones;
-            if (cu.parent >= 0) t.nodes[cu.parent].children.push_back(id);
-            for (size_t i = 0; i < N[cu.bn].children.size(); ++i) q.push_back({N[cu.bn].children[i], id, int(i)});
-        }
-    }
-    t.n_rows = n_rows;
-    t.n_cols = n_cols;
+    shape_to_flat(N, root, n_rows, n_cols, &t, &bn_of);
     // a child's stored vector = its index vector restricted to the ones of its parent's (generate_subindex)
     PlainFill fill = [&](const FlatTree &ft, u32 *d_plain, const std::vector<u64> &lane_plain_off) {
         DeviceBuf<u64> cnt, before;
@@ -760,6 +765,92 @@ static void serialize_brwt(const Matrix *m, ByteSink &sink) {
             stack.pop_back();
         }
     }
+}
+
+// The same builder for the IMPLICIT matrix of the benchmark (SURVEY.md 8d generator), at sizes where the columns
+// cannot be materialised (C4: 1.2 TB): the greedy pairing only ever looks at the <= 10^6 sampled rows, so those are
+// generated on the device (sample_implicit_kernel); the popcounts relax needs come from a count-only pass of K6 over
+// ALL rows on the binary tree; the final shape is then built by K6 as usual.  Same tree as build_brwt_columns on the
+// materialised columns (tests/test_builder_gpu.py).
+__global__ void sample_implicit_kernel(const u64 *idx, u64 n_idx, u32 col, u64 n_cols, u64 seed_mul, u64 threshold, u64 *sub) {
+    const u64 w = u64(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (w * 64 >= n_idx) return;
+    u64 x = 0;
+    for (u32 b = 0; b < 64 && w * 64 + b < n_idx; ++b)
+        if (mix64(seed_mul + idx[w * 64 + b] * n_cols + col) < threshold) x |= 1ull << b;
+    sub[w] = x;
+}
+
+static Matrix *synthesize_brwt_greedy(u64 n_rows, u32 n_cols, u64 threshold, u64 seed, u64 relax_arity, int device) {
+    CUDA_CHECK(cudaSetDevice(device));
+    if (n_cols == 0 || n_rows == 0) return synthesize_brwt(n_rows, n_cols, threshold, seed, 2, device);
+    const u64 seed_mul = seed * 0x9E3779B97F4A7C15ULL;
+    // sampled rows (all of them up to 10^6), and every column restricted to them
+    std::vector<u64> idx = build_row_sample(n_rows);
+    DeviceBuf<u64> d_idx;
+    upload_vec(d_idx, idx);
+    const u64 Ws = (idx.size() + 63) / 64;
+    std::vector<BuildNode> N(n_cols);
+    std::vector<DeviceBuf<u64>> sub(n_cols);
+    for (u32 j = 0; j < n_cols; ++j) {
+        N[j].cols = {j};
+        sub[j].alloc(Ws);
+        sample_implicit_kernel<<<u32((Ws + 255) / 256), 256>>>(d_idx.p, idx.size(), j, n_cols, seed_mul, threshold, sub[j].p);
+    }
+    CUDA_CHECK(cudaGetLastError());
+    std::vector<int> cur(n_cols);
+    for (u32 j = 0; j < n_cols; ++j) cur[j] = int(j);
+    DeviceBuf<u32> d_G;
+    DeviceBuf<const u64 *> d_ptrs;
+    while (cur.size() > 1) {
+        const u32 k_n = u32(cur.size());
+        std::vector<const u64 *> ptrs(k_n);
+        for (u32 i = 0; i < k_n; ++i) ptrs[i] = sub[cur[i]].p;
+        d_ptrs.alloc(k_n);
+        CUDA_CHECK(cudaMemcpy(d_ptrs.p, ptrs.data(), size_t(k_n) * sizeof(const u64 *), cudaMemcpyHostToDevice));
+        d_G.alloc(size_t(k_n) * k_n);
+        const u32 tiles = (k_n + kGramTile - 1) / kGramTile;
+        gram_kernel<<<dim3(tiles, tiles), 256>>>(d_ptrs.p, k_n, Ws, d_G.p);
+        CUDA_CHECK(cudaGetLastError());
+        std::vector<u32> G(size_t(k_n) * k_n);
+        CUDA_CHECK(cudaMemcpy(G.data(), d_G.p, G.size() * 4, cudaMemcpyDeviceToHost));
+        std::vector<int> next;
+        for (const std::vector<u32> &grp : greedy_partition(G, k_n)) {
+            if (grp.size() == 1) { next.push_back(cur[grp[0]]); continue; }
+            const int id = int(N.size());
+            N.emplace_back();
+            sub.emplace_back();
+            sub[id].alloc(Ws);
+            CUDA_CHECK(cudaMemset(sub[id].p, 0, Ws * 8));
+            for (u32 g : grp) {
+                const int c = cur[g];
+                N[id].children.push_back(c);
+                N[id].cols.insert(N[id].cols.end(), N[c].cols.begin(), N[c].cols.end());
+                or_into_kernel<<<u32((Ws + 255) / 256), 256>>>(sub[id].p, sub[c].p, Ws);
+            }
+            CUDA_CHECK(cudaGetLastError());
+            next.push_back(id);
+        }
+        cur.swap(next);
+    }
+    const int root = cur[0];
+    CUDA_CHECK(cudaDeviceSynchronize());
+    sub.clear();
+    d_G.release();
+    std::vector<int> bn_of;
+    if (relax_arity > 1) {
+        // exact popcounts of every node's index vector over ALL rows: K6's count pass on the binary tree
+        FlatTree probe;
+        shape_to_flat(N, root, n_rows, n_cols, &probe, &bn_of);
+        std::vector<u64> ones;
+        synthesize_brwt_shape(std::move(probe), n_rows, n_cols, threshold, seed, device, 0, 1, &ones);
+        for (size_t id = 0; id < bn_of.size(); ++id) N[bn_of[id]].ones = ones[id];
+        relax_tree(N, root, n_rows, relax_arity);
+    }
+    FlatTree t;
+    shape_to_flat(N, root, n_rows, n_cols, &t, &bn_of);
+    for (FlatNode &fn : t.nodes) { fn.ones = 0; if (fn.parent >= 0) fn.size = 0; }   // K6 fills them in
+    return synthesize_brwt_shape(std::move(t), n_rows, n_cols, threshold, seed, device);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1218,6 +1309,23 @@ int ggq_brwt_build_columns(const uint64_t *col_words, uint64_t n_rows, uint64_t 
                                                         partitioner, arity, relax_arity, device));
     return GGQ_OK;
     GGQ_CATCH
+}
+
+int ggq_brwt_synthesize_greedy(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed, uint64_t relax_arity,
+                               int device, ggq_matrix **out) {
+    GGQ_TRY
+    if (!out) return fail(GGQ_ERR_ARG, "null out");
+    if (n_rows >= kMaxRows || n_cols >= (u64(1) << 31)) return fail(GGQ_ERR_LIMIT, "matrix exceeds engine limits");
+    *out = static_cast<ggq_matrix *>(synthesize_brwt_greedy(n_rows, u32(n_cols), threshold, seed, relax_arity, device));
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
+int ggq_tree_dfs_columns(const ggq_matrix *m, uint32_t *dfs_cols) {
+    if (!m || (!dfs_cols && m->tree.n_cols)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (m->kind != Matrix::BRWT) return fail(GGQ_ERR_ARG, "not a BRWT");
+    for (size_t i = 0; i < m->tree.leaf_col.size(); ++i) dfs_cols[i] = m->tree.leaf_col[i];
+    return GGQ_OK;
 }
 
 int ggq_tree_shape(const ggq_matrix *m, uint64_t *n_nodes, int64_t *parent, uint32_t *n_children, uint32_t *n_columns,

@@ -106,6 +106,15 @@ int ggq_rrr63_encode_buffer(const uint64_t *words, uint64_t n_bits, uint8_t **ou
  * restriction run on the GPU, the ranking and the space model decide as the reference does. */
 int ggq_brwt_build_columns(const uint64_t *col_words, uint64_t n_rows, uint64_t n_cols, int partitioner, uint32_t arity,
                            uint64_t relax_arity, int device, ggq_matrix **out);
+/* Benchmark harness: the same builder (greedy partitioner + relax(relax_arity)) for the IMPLICIT matrix of
+ * ggq_brwt_synthesize, at sizes where the columns cannot be materialised — the pairing looks at the sampled rows only
+ * (generated on the device), relax at popcounts counted over all rows; same tree as ggq_brwt_build_columns on the
+ * materialised columns. */
+int ggq_brwt_synthesize_greedy(uint64_t n_rows, uint64_t n_cols, uint64_t threshold, uint64_t seed, uint64_t relax_arity,
+                               int device, ggq_matrix **out);
+/* dfs_cols[k] = the column whose leaf is visited k-th by BRWT::get_row (DFS over child_nodes_, BRWT.cpp:45-50): the
+ * order in which every row lists its columns.  num_columns entries. */
+int ggq_tree_dfs_columns(const ggq_matrix *m, uint32_t *dfs_cols);
 /* Tree of a BRWT matrix, nodes in level (BFS) order, children in stored order: parent index (-1: root), number of
  * children / columns, length and popcount of the node's vector, first column of its arrangement.  Arrays may be NULL;
  * *n_nodes is always set.  Not available for column-major matrices and images of column shards (GGQ_ERR_ARG). */

@@ -95,3 +95,30 @@ def test_row_sampling_above_one_million_rows(ggq, ref, n):
     cw = ref.gen_uniform_rows(n, m, 0.05, n // 4, seed=7)
     rows = np.random.default_rng(1).integers(0, n, 200_000).astype(np.uint64)
     compare(ggq, ref, cw, n, rows=rows, greedy=True, relax=6)
+
+
+@pytest.mark.parametrize("n,m,d,relax", [(200_000, 300, 0.01, 7), (1_500_000, 60, 0.02, 5), (50_000, 97, 0.2, 0),
+                                         (2_300_000, 40, 0.004, 7)])
+def test_implicit_generator_variant_builds_the_same_tree(ggq, ref, n, m, d, relax):
+    """ggq_brwt_synthesize_greedy (the builder for the benchmark's implicit matrix: sampled rows generated on the
+    device, popcounts from K6's count pass over all rows) against the reference builder on the MATERIALISED columns
+    of the same generator: same tree, same rows, same serialized bytes — below and above the 10^6-row sampling limit."""
+    thr = ggq.density_threshold(d)
+    cw = ref.gen_implicit(n, m, thr, 42)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, greedy=True, relax=relax, threads=8)
+    stream = rm.serialize()
+    g_ref = ggq.GpuMatrix.load_brwt(stream)
+    g_imp = ggq.GpuMatrix.synthesize_brwt_greedy(n, m, d, seed=42, relax=relax)
+    try:
+        a, b = g_imp.tree_shape(), g_ref.tree_shape()
+        for key in a:
+            assert np.array_equal(a[key], b[key]), key
+        assert (g_imp.num_nodes, g_imp.total_column_size, g_imp.num_relations) == (rm.num_nodes, rm.total_column_size, rm.num_relations)
+        rows = np.random.default_rng(3).integers(0, n, 100_000).astype(np.uint64)
+        eoff, ecols, _ = rm.get_rows(rows, threads=8)
+        off, cols = g_imp.get_rows_csr(rows)
+        assert np.array_equal(off, eoff) and np.array_equal(cols, ecols)
+        assert g_imp.serialize() == stream
+    finally:
+        g_ref.close()
+        g_imp.close()
