@@ -13,7 +13,9 @@
 #include <algorithm>
 #include <cstdint>
 #include <stdexcept>
+#include <cstdlib>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ggq_format.hpp"
@@ -101,70 +103,96 @@ inline uint64_t rrr63_block_number(uint64_t bin, const Binomial63 &B) {
     return nr;
 }
 
-// rrr_vector<63>(bv).serialize(out): words = the plain bits, LSB first, (n_bits + 63) / 64 of them, zero-padded
+// Runs fn(t, n_threads) on n_threads host threads (1: inline).
+template <typename F>
+inline void rrr_parallel(unsigned n_threads, F fn) {
+    if (n_threads <= 1) { fn(0u, 1u); return; }
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < n_threads; ++t) pool.emplace_back([&, t] { fn(t, n_threads); });
+    for (std::thread &th : pool) th.join();
+}
+
+// rrr_vector<63>(bv).serialize(out): words = the plain bits, LSB first, (n_bits + 63) / 64 of them, zero-padded.
+// Three steps so that long vectors are encoded by several host threads: (1) every block's class, in parallel;
+// (2) one cheap sequential sweep over the superblocks in sdsl's order of events — inversion flag, offset pointer, rank
+// sample; (3) stored classes and offsets, in parallel (a superblock's 32 six-bit classes fill exactly three words; the
+// other arrays are written with atomic ORs into zeroed words).
 inline void write_rrr63(ByteSink &s, const uint64_t *words, uint64_t n_bits) {
     const unsigned BS = 63, K = 32;
     const Binomial63 &B = Binomial63::get();
     const uint64_t n_words = (n_bits + 63) / 64;
     const uint64_t n_blocks = (n_bits + BS) / BS;   // a dummy block at the end when n_bits % 63 == 0
+    const uint64_t n_real = (n_bits + BS - 1) / BS; // blocks that hold bits (the last one possibly partial)
     const uint64_t n_sb = (n_blocks + K - 1) / K;
+    unsigned n_thr = 1;
+    if (n_blocks >= (uint64_t(1) << 16)) {
+        n_thr = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+        if (const char *e = std::getenv("GGQ_LOAD_THREADS")) n_thr = unsigned(std::max(1, std::atoi(e)));
+    }
+    auto block_bits = [&](uint64_t b) {
+        const uint64_t pos = b * BS;
+        return plain_bits(words, n_words, pos, unsigned(std::min<uint64_t>(BS, n_bits - pos)));
+    };
+    // (1) classes
+    std::vector<uint8_t> cls(n_blocks, 0);
+    rrr_parallel(n_thr, [&](unsigned t, unsigned T) {
+        for (uint64_t b = n_real * t / T; b < n_real * (t + 1) / T; ++b) cls[b] = uint8_t(__builtin_popcountll(block_bits(b)));
+    });
+    // (2) per superblock: inverted?, first offset bit, ones before.  sdsl opens a superblock when it REACHES its first
+    // block, so a superblock that starts at the dummy block is never opened (its pointer and sample stay 0), and one
+    // that starts at the partial last block is opened without the inversion test.
+    std::vector<uint8_t> inv(n_sb, 0), opened(n_sb, 0);
+    std::vector<uint64_t> at(n_sb + 1, 0), before(n_sb + 1, 0);
+    uint64_t bit_at = 0, ones = 0;
+    for (uint64_t sb = 0; sb < n_sb; ++sb) {
+        const uint64_t b0 = sb * K, b1 = std::min<uint64_t>(b0 + K, n_blocks);
+        at[sb] = bit_at;
+        before[sb] = ones;
+        opened[sb] = b0 < n_real;
+        const bool starts_full = (b0 + 1) * BS <= n_bits;   // its first block is a full one
+        if (opened[sb] && starts_full && b0 + K <= n_blocks) {
+            unsigned dense = 0;
+            for (uint64_t b = b0; b < b1; ++b) dense += cls[b] > BS / 2;
+            inv[sb] = dense > K / 2;
+        }
+        for (uint64_t b = b0; b < b1 && b < n_real; ++b) { bit_at += B.space[cls[b]]; ones += cls[b]; }
+    }
+    at[n_sb] = bit_at;
+    before[n_sb] = ones;
     PackedInts bt(n_blocks, 6);
-    // (1) block classes, total offset bits, total ones
-    uint64_t pos = 0, i = 0, btnr_bits = 0, ones = 0;
-    while (pos + BS <= n_bits) {
-        const unsigned x = unsigned(__builtin_popcountll(plain_bits(words, n_words, pos, BS)));
-        bt.set(i++, x);
-        ones += x;
-        btnr_bits += B.space[x];
-        pos += BS;
-    }
-    if (pos < n_bits) {
-        const unsigned x = unsigned(__builtin_popcountll(plain_bits(words, n_words, pos, unsigned(n_bits - pos))));
-        bt.set(i++, x);
-        ones += x;
-        btnr_bits += B.space[x];
-    }
-    PackedInts btnr(std::max<uint64_t>(btnr_bits, 64), 1);
-    PackedInts btnrp(n_sb, uint8_t(hi_bit(btnr_bits) + 1));
+    PackedInts btnr(std::max<uint64_t>(bit_at, 64), 1);
+    PackedInts btnrp(n_sb, uint8_t(hi_bit(bit_at) + 1));
     PackedInts rank(n_sb + ((n_bits % (uint64_t(K) * BS)) > 0 ? 1 : 0), uint8_t(hi_bit(ones) + 1));
     PackedInts invert(n_sb, 1);
-    // (2) offsets, pointers, rank samples, inversion flags — in sdsl's order of events
-    pos = 0; i = 0;
-    uint64_t at = 0, sum = 0;
-    bool inv = false;
-    auto open_superblock = [&](bool may_invert) {
-        btnrp.set(i / K, at);
-        rank.set(i / K, sum);
-        inv = false;
-        if (may_invert && i + K <= n_blocks) {
-            unsigned dense = 0;
-            for (uint64_t j = i; j < i + K; ++j) dense += bt.get(j) > BS / 2;
-            if (dense > K / 2) {
-                invert.set(i / K, 1);
-                for (uint64_t j = i; j < i + K; ++j) { const uint64_t v = bt.get(j); bt.clear(j); bt.set(j, BS - v); }
-                inv = true;
+    auto or_bits = [](PackedInts &p, uint64_t bp, uint64_t v, unsigned len) {   // concurrent writers share words
+        if (!len || !v) return;
+        const uint64_t w = bp >> 6;
+        const unsigned o = bp & 63;
+        __atomic_fetch_or(&p.words[w], v << o, __ATOMIC_RELAXED);
+        if (o + len > 64) __atomic_fetch_or(&p.words[w + 1], v >> (64 - o), __ATOMIC_RELAXED);
+    };
+    // (3) stored classes, offsets, pointers, samples, flags
+    rrr_parallel(n_thr, [&](unsigned t, unsigned T) {
+        for (uint64_t sb = n_sb * t / T; sb < n_sb * (t + 1) / T; ++sb) {
+            const uint64_t b0 = sb * K, b1 = std::min<uint64_t>(b0 + K, n_blocks);
+            if (opened[sb]) {
+                or_bits(btnrp, sb * btnrp.width, at[sb], btnrp.width);
+                or_bits(rank, sb * rank.width, before[sb], rank.width);
+                if (inv[sb]) or_bits(invert, sb, 1, 1);
+            }
+            uint64_t p = at[sb];
+            for (uint64_t b = b0; b < b1; ++b) {
+                const unsigned stored = inv[sb] ? BS - cls[b] : cls[b];
+                or_bits(bt, b * 6, stored, 6);
+                if (b >= n_real) continue;
+                const unsigned sp = B.space[cls[b]];   // space[k] == space[63 - k]
+                if (sp) or_bits(btnr, p, rrr63_block_number(block_bits(b), B), sp);
+                p += sp;
             }
         }
-    };
-    while (pos + BS <= n_bits) {
-        if (i % K == 0) open_superblock(true);
-        const unsigned x = unsigned(bt.get(i++));
-        const unsigned sp = B.space[x];
-        sum += inv ? BS - x : x;
-        if (sp) btnr.put_bits(at, rrr63_block_number(plain_bits(words, n_words, pos, BS), B), sp);
-        at += sp;
-        pos += BS;
-    }
-    if (pos < n_bits) {   // the last, partial block (never starts an inverted superblock)
-        if (i % K == 0) open_superblock(false);
-        const unsigned x = unsigned(bt.get(i++));
-        const unsigned sp = B.space[x];
-        sum += inv ? BS - x : x;
-        if (sp) btnr.put_bits(at, rrr63_block_number(plain_bits(words, n_words, pos, unsigned(n_bits - pos)), B), sp);
-        at += sp;
-    }
+    });
     rank.clear(rank.count - 1);
-    rank.set(rank.count - 1, sum);   // "for technical reasons": the total closes the samples
+    rank.set(rank.count - 1, ones);   // "for technical reasons": the total closes the samples
     s.u64le(n_bits);
     bt.write(s, true);
     btnr.write(s, false);

@@ -182,7 +182,7 @@ def test_threaded_rrr_decode_of_large_vectors(ref, monkeypatch):
         assert e.code == -1
 
 
-def test_rrr_writer_is_byte_identical_to_sdsl(ref):
+def test_rrr_writer_is_byte_identical_to_sdsl(ref, monkeypatch):
     """ggq_rrr63_encode_buffer (host only; the building block of ggq_brwt_serialize) against the reference's
     bit_vector_rrr<63>::serialize on the same bits: every array of sdsl's rrr_vector — block classes, offsets in
     sdsl's numbering, superblock pointers, rank samples, inversion flags, widths and padding — byte for byte, over
@@ -205,3 +205,13 @@ def test_rrr_writer_is_byte_identical_to_sdsl(ref):
     pad[:n] = bits
     w = np.packbits(pad, bitorder="little").view(np.uint64).copy()
     assert g.rrr63_encode(w, n) == ref.RefBitVector.build("rrr", w, n).serialize()
+    # long vectors are encoded by several host threads (>= 2^16 blocks): dummy-block and partial-block endings, with
+    # dense and sparse stretches so that the inversion flag flips along the vector
+    monkeypatch.setenv("GGQ_LOAD_THREADS", "5")
+    for n in (63 * 65536, 63 * 65536 + 1, 2016 * 2100 + 62):
+        bits = (rng.random(n) < 0.02).astype(np.uint8)
+        bits[n // 3:n // 2] = (rng.random(n // 2 - n // 3) < 0.9).astype(np.uint8)
+        pad = np.zeros(((n + 63) // 64) * 64, np.uint8)
+        pad[:n] = bits
+        w = np.packbits(pad, bitorder="little").view(np.uint64).copy()
+        assert g.rrr63_encode(w, n) == ref.RefBitVector.build("rrr", w, n).serialize(), n
