@@ -89,6 +89,19 @@ def _rank_main(rank, world, port, path, q):
         exp = np.concatenate([ecols[eoff[r]:eoff[r + 1]] for r in rows]) if rows.size else np.zeros(0, np.uint64)
         exp_off = np.concatenate([[0], np.cumsum([eoff[r + 1] - eoff[r] for r in rows])]).astype(np.int64)
         ok = np.array_equal(out, exp) and np.array_equal(out_off, exp_off)
+        # slice mode (ggq_get_rows_sharded_slice_device): rank k merges only queries [n k / R, n (k + 1) / R); the
+        # slices of all ranks, concatenated in rank order, are the whole answer
+        q0, q1 = rows.size * rank // world, rows.size * (rank + 1) // world
+        mine = []
+        for t in range(q0, q1):
+            for r in range(world):
+                o = offs[r].numpy()
+                mine.append(cols[r].numpy()[o[t]:o[t + 1]])
+        mine = np.concatenate(mine).astype(np.int64) if mine else np.zeros(0, np.int64)
+        ok = ok and np.array_equal(mine.astype(np.uint64), exp[int(exp_off[q0]):int(exp_off[q1])])
+        sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([mine.size]))
+        ok = ok and sum(int(x) for x in sizes) == exp.size
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, bool(ok), ""))
