@@ -299,6 +299,7 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     }
     // root fast path + continuation groups (see RowsArgs)
     root_child = kNoRootFast;
+    root_all_ones = 0;
     any_more = 0;
     for (u64 h : tree.group_hot) any_more |= u32((h >> kGhMoreShift) & 1u);
     if (!tree.group_hot.empty()) {
@@ -310,6 +311,8 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
             root_sl = u32(h0 >> kGhStrideShift) & 3u;
             root_multi_sb = u32((h0 >> kGhSuperShift) & 1u);
             root_base = h0 & kGhBaseMask;
+            root_all_ones = !lane_ones_h.empty() && !lane_size_h.empty() && lane_size_h[0] > 0 && lane_ones_h[0] == lane_size_h[0] &&
+                            !env_u32("GGQ_NO_ROOT_ALL_ONES", 0);
         }
     }
     // query ordering (see K1): sort on the top `sort_bits` bits of the row id
@@ -1002,7 +1005,7 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     a.sum_words = rows_sum_words(m->bm_words); a.sum_magic = u32((u64(1) << 32) / a.sum_words) + 1u;
     a.err = reinterpret_cast<int *>(ws->d_ctrl.p + 4);
     a.root_child = m->root_child; a.root_sl = m->root_sl; a.root_multi_sb = m->root_multi_sb;
-    a.root_base = m->root_base; a.any_more = m->any_more;
+    a.root_base = m->root_base; a.any_more = m->any_more; a.root_all_ones = m->root_all_ones;
     u64 batches = (n + m->rb - 1) / m->rb;
     u32 grid = u32(std::min<u64>(std::min(full_grid, grid_cap), (batches + kRowsWarps - 1) / kRowsWarps));
     ws->ran_safe = safe;

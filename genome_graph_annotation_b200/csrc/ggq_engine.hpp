@@ -90,7 +90,7 @@ struct Matrix {
     // subtrees of the group tree, so this many can never be exceeded) and reruns the batch.
     u32 cap_safe = 0;
     mutable std::atomic<bool> stack_safe{false};
-    u32 root_child = 0xFFFFFFFFu, root_sl = 0, root_multi_sb = 0, any_more = 0;   // K1 root fast path (RowsArgs)
+    u32 root_child = 0xFFFFFFFFu, root_sl = 0, root_multi_sb = 0, any_more = 0, root_all_ones = 0;   // K1 root fast path (RowsArgs)
     u64 root_base = 0;
     size_t rows_smem = 0;
     // pipelined host calls: one CTA per SM fewer (shared-memory request padded so that no more fit), which leaves

@@ -55,6 +55,7 @@ struct RowsArgs {
     u32 root_child;           // first group of the root's children, or kNoRootFast
     u32 root_sl;              // stride_log2 of group 0
     u32 root_multi_sb;        // root vector spans several superblocks
+    u32 root_all_ones;        // the root vector has no zero: the seeding step needs no probe
     u64 root_base;            // slot base of group 0
     u32 any_more;             // some node has more than 4 children (continuation groups exist)
     int *err;
@@ -222,7 +223,12 @@ brwt_rows_kernel(Img img, RowsArgs a) {
         if (a.root_child != kNoRootFast) {
             bool push = false;
             u64 it = 0;
-            if (valid) {
+            if (valid && a.root_all_ones) {
+                // every row has a label (the usual case of a real annotation): rank1(r) - 1 = r, no probe at all
+                it = (r << kItemRShift) | (u64(lane) << kItemGroupBits) | a.root_child;
+                push = true;
+                touches += 1;
+            } else if (valid) {
                 u64 blk; u32 bit;
                 div96(r, blk, bit);
                 const uint4 s = ld_slot(img.slots + a.root_base + (blk << a.root_sl));
@@ -237,7 +243,7 @@ brwt_rows_kernel(Img img, RowsArgs a) {
             const u32 pm = __ballot_sync(0xffffffffu, push);
             if (push) sts64(stk + __popc(pm & lt_mask) * 8, it);
             top = __popc(pm);
-            probes += __popc(vmask);
+            if (!a.root_all_ones) probes += __popc(vmask);
         } else {
             if (valid) sts64(stk + __popc(vmask & lt_mask) * 8, (r << kItemRShift) | (u64(lane) << kItemGroupBits));
             top = __popc(vmask);

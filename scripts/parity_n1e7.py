@@ -89,11 +89,22 @@ def main():
     rec["device_builder_same_tree"] = bool(all(np.array_equal(ref_shape[k], dev_shape[k]) for k in ref_shape))
     off, cols = gd.get_rows_csr(rnd)
     rec["device_builder_same_rows"] = bool(np.array_equal(off, eoff) and np.array_equal(cols, ecols))
+    t0 = time.time()
+    rec["device_built_matrix_serializes_to_the_reference_stream"] = bool(gd.serialize() == data)
+    rec["serialize_from_device_s"] = time.time() - t0
     gd.close()
+    # the implicit-generator form (no materialised columns at all)
+    t0 = time.time()
+    gi = g.GpuMatrix.synthesize_brwt_greedy(n, m, a.density, seed=42, relax=a.relax)
+    rec["implicit_device_build_s"] = time.time() - t0
+    imp_shape = gi.tree_shape()
+    rec["implicit_builder_same_tree"] = bool(all(np.array_equal(ref_shape[k], imp_shape[k]) for k in ref_shape))
+    gi.close()
     print(json.dumps(rec))
     if a.out:
         json.dump(rec, open(a.out, "w"), indent=1)
-    if not (rec["device_builder_same_tree"] and rec["device_builder_same_rows"]):
+    if not (rec["device_builder_same_tree"] and rec["device_builder_same_rows"] and rec["implicit_builder_same_tree"] and
+            rec["device_built_matrix_serializes_to_the_reference_stream"]):
         raise SystemExit("device builder differs from the reference builder")
 
 
