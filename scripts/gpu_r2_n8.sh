@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round 2, 8 GPUs: 8-rank NCCL / peer / slice parity, then the default bench at N=8 (C4 replicas + the c5 block).
 mkdir -p gpurun_out
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29531 \
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29541 \
   scripts/shard_nccl_check.py > gpurun_out/r2_n8_nccl_check.log 2>&1; echo "nccl check rc=$?"; grep -c "slice peer" gpurun_out/r2_n8_nccl_check.log; tail -2 gpurun_out/r2_n8_nccl_check.log
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29532 \
   bench.py --gpus 8 --steps 5 --warmup 3 --no-bitvector > gpurun_out/r2_n8_bench.json 2> gpurun_out/r2_n8_bench.err
