@@ -82,6 +82,8 @@ def lib():
         "ggq_num_nodes": (C.c_uint64, [vp]),
         "ggq_total_column_size": (C.c_uint64, [vp]),
         "ggq_device_bytes": (C.c_uint64, [vp]),
+        "ggq_slot_bits": (C.c_uint32, [vp]),
+        "ggq_set_default_option": (C.c_int, [C.c_char_p, C.c_uint64]),
         "ggq_leaf_code_info": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "ggq_last_probe_count": (C.c_uint64, [vp]),
         "ggq_set_option": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
@@ -154,6 +156,12 @@ def _check(rc):
 def _u64(a):
     a = np.ascontiguousarray(a, dtype=np.uint64)
     return a, a.ctypes.data_as(u64p)
+
+
+def set_default_option(name, value):
+    """Process-wide default for matrices created afterwards (ggq_set_default_option): "wide_slots" = 1 selects the
+    capacity layout (32-byte slots of 224 positions)."""
+    _check(lib().ggq_set_default_option(name.encode(), int(value)))
 
 
 def device_count():
@@ -398,6 +406,7 @@ class GpuMatrix:
     num_nodes = property(lambda s: lib().ggq_num_nodes(s._h))
     total_column_size = property(lambda s: lib().ggq_total_column_size(s._h))
     device_bytes = property(lambda s: lib().ggq_device_bytes(s._h))
+    slot_bits = property(lambda s: lib().ggq_slot_bits(s._h))
 
     @property
     def leaf_codes(self):

@@ -39,6 +39,7 @@ struct BuildArgs {
     const u64 *tile_prefix;    // [tile][node_idx]   (pass 2 in)
     uint4 *slots;
     const u64 *group_hot;
+    u32 dw, quads;             // data words and 16-byte units per slot (3 / 1, or 7 / 2 in the capacity layout)
 };
 
 template <bool FILL>
@@ -97,14 +98,14 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
                                     if (li == ~0u) continue;
                                     const u64 hot = a.group_hot[li >> 2];
                                     const u32 sl = u32(hot >> kGhStrideShift) & 3u;
-                                    uint4 *base = a.slots + (hot & kGhBaseMask) + (li & 3);
+                                    uint4 *base = a.slots + (hot & kGhBaseMask) + (li & 3) * a.quads;
                                     if (va) {
-                                        u64 blk = wa / 3; u32 w = u32(wa - blk * 3);
+                                        u64 blk = a.dw == 3 ? wa / 3 : wa / 7; u32 w = u32(wa - blk * a.dw);
                                         atomicOr(reinterpret_cast<u32 *>(base + (blk << sl)) + 1 + w, va);
                                     }
                                     if (vb) {
                                         u64 wb = wa + 1;
-                                        u64 blk = wb / 3; u32 w = u32(wb - blk * 3);
+                                        u64 blk = a.dw == 3 ? wb / 3 : wb / 7; u32 w = u32(wb - blk * a.dw);
                                         atomicOr(reinterpret_cast<u32 *>(base + (blk << sl)) + 1 + w, vb);
                                     }
                                 }
@@ -121,9 +122,10 @@ __global__ void __launch_bounds__(kBuildWarps * 32) brwt_build_kernel(BuildArgs 
                 const u32 rootbits = __ballot_sync(0xffffffffu, (stack & 1ull) != 0);
                 if (lane == 0 && rootbits) {
                     const u64 hot = a.group_hot[0];
+                    const u32 sl = u32(hot >> kGhStrideShift) & 3u;
                     const u64 wr = (tile * kTileRows + step * 32) >> 5;
-                    const u64 blk = wr / 3; const u32 w = u32(wr - blk * 3);
-                    reinterpret_cast<u32 *>(a.slots + (hot & kGhBaseMask) + blk)[1 + w] = rootbits;
+                    const u64 blk = a.dw == 3 ? wr / 3 : wr / 7; const u32 w = u32(wr - blk * a.dw);
+                    reinterpret_cast<u32 *>(a.slots + (hot & kGhBaseMask) + (blk << sl))[1 + w] = rootbits;
                 }
             }
         }
@@ -170,6 +172,7 @@ inline Matrix *synthesize_brwt_shape(FlatTree &&shape, u64 n_rows, u32 n_cols, u
     CUDA_CHECK(cudaSetDevice(device));
     m->tree = std::move(shape);
     FlatTree &t = m->tree;
+    t.slot_bits = default_slot_bits();
     assign_groups(&t);
     plan_shards(&t, shard, n_shards);
     if (n_rows >= kMaxRows) throw LimitError("too many rows");
@@ -279,6 +282,8 @@ inline Matrix *synthesize_brwt_shape(FlatTree &&shape, u64 n_rows, u32 n_cols, u
     CUDA_CHECK(cudaMemset(m->slots.p, 0, m->slots.bytes()));
     a.slots = m->slots.p;
     a.group_hot = m->group_hot.p;
+    a.dw = slot_data_words(t.slot_bits);
+    a.quads = slot_quads(t.slot_bits);
     if (n_tiles && n_cols) {
         if (root_is_leaf) {
             // single column: the program is one LEAF; pass 2 only writes the root vector

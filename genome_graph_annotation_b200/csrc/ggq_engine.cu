@@ -40,6 +40,19 @@ int fail(int code, const std::string &msg) {
     return code;
 }
 
+// Slot layout of the BRWT matrices created from now on (ggq_set_default_option("wide_slots", v); GGQ_WIDE_SLOTS=1 in the
+// environment sets the initial value): 0 = 16-byte slots (default), 1 = the capacity layout (ggq_layout.hpp).
+static std::atomic<int> g_default_wide{-1};
+u32 default_slot_bits() {
+    int v = g_default_wide.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char *e = std::getenv("GGQ_WIDE_SLOTS");
+        v = (e && *e && *e != '0') ? 1 : 0;
+        g_default_wide.store(v, std::memory_order_relaxed);
+    }
+    return v ? kWideSlotBits : kSlotBits;
+}
+
 // ------------------------------------------------------------------------------------------
 // Image upload
 // ------------------------------------------------------------------------------------------
@@ -95,7 +108,8 @@ void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
     ChunkTable ct{d_cl.p, d_cf.p, d_lco.p, nch};
     u32 n_lanes = t.n_groups() * 4;
     if (nch) {
-        chunk_sum_kernel<<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_sum.p);
+        if (wide()) chunk_sum_kernel<true><<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_sum.p);
+        else chunk_sum_kernel<false><<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_sum.p);
         lane_scan_kernel<<<n_lanes, 256>>>(d_lco.p, d_sum.p, d_base.p, lane_ones.p, lane_sb_off.p, sb_base.p, n_lanes);
         CUDA_CHECK(cudaGetLastError());
     }
@@ -118,8 +132,10 @@ void Matrix::finalize_arena(const FlatTree &t, bool ones_known) {
         sel.alloc(std::max<u64>(sel_total, 1));
     }
     if (nch) {
-        header_kernel<<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_base.p,
-                                                        lane_info.p, lane_sel_off.p, sel.p, 1);
+        if (wide()) header_kernel<true><<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_base.p,
+                                                                          lane_info.p, lane_sel_off.p, sel.p, 1);
+        else header_kernel<false><<<chunk_grid(nch), kChunkBlocks>>>(slots.p, group_hot.p, group_nblocks.p, ct, d_base.p,
+                                                                    lane_info.p, lane_sel_off.p, sel.p, 1);
         CUDA_CHECK(cudaGetLastError());
     }
     CUDA_CHECK(cudaDeviceSynchronize());
@@ -210,13 +226,17 @@ void Matrix::refresh_img() {
 }
 
 // The instantiation of K1 for a tree: stack spill to global memory, leaves holding several columns.
-static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact) {
+template <bool WIDE>
+static const void *rows_kernel_fn_t(bool spill, bool multi_leaf, bool compact) {
     if (compact) {
-        if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, true> : (const void *)brwt_rows_kernel<true, false, true>;
-        return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true> : (const void *)brwt_rows_kernel<false, false, true>;
+        if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, true, WIDE> : (const void *)brwt_rows_kernel<true, false, true, WIDE>;
+        return multi_leaf ? (const void *)brwt_rows_kernel<false, true, true, WIDE> : (const void *)brwt_rows_kernel<false, false, true, WIDE>;
     }
-    if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, false> : (const void *)brwt_rows_kernel<true, false, false>;
-    return multi_leaf ? (const void *)brwt_rows_kernel<false, true, false> : (const void *)brwt_rows_kernel<false, false, false>;
+    if (spill) return multi_leaf ? (const void *)brwt_rows_kernel<true, true, false, WIDE> : (const void *)brwt_rows_kernel<true, false, false, WIDE>;
+    return multi_leaf ? (const void *)brwt_rows_kernel<false, true, false, WIDE> : (const void *)brwt_rows_kernel<false, false, false, WIDE>;
+}
+static const void *rows_kernel_fn(bool spill, bool multi_leaf, bool compact, bool wide) {
+    return wide ? rows_kernel_fn_t<true>(spill, multi_leaf, compact) : rows_kernel_fn_t<false>(spill, multi_leaf, compact);
 }
 
 // Descent kernel configuration: rows per warp batch, stack capacity, grid, query ordering.
@@ -248,9 +268,9 @@ void Matrix::configure_rows(u32 rb_request, u32 sort_request) {
     }
     if (rows_smem > size_t(max_smem)) throw LimitError("matrix has too many columns for the descent kernel's shared-memory bitmaps");
     int per_sm = 0;
-    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec);
+    const void *fn = rows_kernel_fn(cap_spill != 0, tree.multi_column_leaves != 0, compact_rec, wide());
     CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  // per function, shared by all matrices
-    CUDA_CHECK(cudaFuncSetAttribute(rows_kernel_fn(true, tree.multi_column_leaves != 0, compact_rec),
+    CUDA_CHECK(cudaFuncSetAttribute(rows_kernel_fn(true, tree.multi_column_leaves != 0, compact_rec, wide()),
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));   // the safe fallback below
     {   // provable stack bound: the items of one row that are pending at any time head disjoint subtrees of the group
         // tree (children groups + continuation group), and every such subtree contains a group without successors
@@ -401,8 +421,8 @@ void Matrix::build_leaf_codes() {
                 const u64 stride = std::max<u64>(1, n.ones / samples);
                 const u64 n_work = (n.ones + stride - 1) / stride;
                 CUDA_CHECK(cudaMemset(d_esc.p, 0, 8));
-                leaf_code_kernel<<<u32((n_work + 255) / 256), 256>>>(img, n.first_child_group, n.ones, first_rank[id], stride,
-                                                                    true, nullptr, d_esc.p);
+                if (wide()) leaf_code_kernel<true><<<u32((n_work + 255) / 256), 256>>>(img, n.first_child_group, n.ones, first_rank[id], stride, true, nullptr, d_esc.p);
+                else leaf_code_kernel<false><<<u32((n_work + 255) / 256), 256>>>(img, n.first_child_group, n.ones, first_rank[id], stride, true, nullptr, d_esc.p);
                 CUDA_CHECK(cudaGetLastError());
                 unsigned long long esc = 0;
                 CUDA_CHECK(cudaMemcpy(&esc, d_esc.p, 8, cudaMemcpyDeviceToHost));
@@ -443,7 +463,8 @@ void Matrix::build_leaf_codes() {
         const FlatNode &n = N[p.id];
         const u32 li = n.group * 4 + n.lane;
         const u32 grid = u32(std::min<u64>((n.ones + 255) / 256, u64(sms) * 32));
-        leaf_code_kernel<<<grid, 256>>>(img, n.first_child_group, n.ones, first_rank[p.id], 1, false, codes.p + at, nullptr);
+        if (wide()) leaf_code_kernel<true><<<grid, 256>>>(img, n.first_child_group, n.ones, first_rank[p.id], 1, false, codes.p + at, nullptr);
+        else leaf_code_kernel<false><<<grid, 256>>>(img, n.first_child_group, n.ones, first_rank[p.id], 1, false, codes.p + at, nullptr);
         CUDA_CHECK(cudaGetLastError());
         tree.lane_coded[li] = 1;
         tree.code_rec[4 * size_t(li) + 0] = u32(at);
@@ -483,6 +504,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     CUDA_CHECK(cudaSetDevice(device));
     m->tree = std::move(tree);
     FlatTree &t = m->tree;
+    t.slot_bits = default_slot_bits();
     assign_groups(&t);
     plan_shards(&t, shard, n_shards);
     assign_geometry(&t);
@@ -492,17 +514,18 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
     m->sel.alloc(std::max<u64>(t.total_sel, 1));
     // plain bits of all nodes, concatenated
     u32 n_lanes = t.n_groups() * 4;
-    std::vector<u64> lane_plain_off(n_lanes, 0);
+    std::vector<u64> lane_plain_off(n_lanes, 0), lane_plain_words(n_lanes, 0);
     u64 total_words = 0;
     for (u32 li = 0; li < n_lanes; ++li) {
         if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
         lane_plain_off[li] = total_words;
         const FlatNode &nd = t.nodes[t.lane_node[li]];
-        total_words += (fill || nd.lazy) ? (nd.size + 31) / 32 + 4 : nd.bits.w.size();
+        lane_plain_words[li] = (fill || nd.lazy) ? (nd.size + 31) / 32 + 4 : nd.bits.w.size();
+        total_words += lane_plain_words[li];
     }
     {
         DeviceBuf<u32> d_plain;
-        DeviceBuf<u64> d_off;
+        DeviceBuf<u64> d_off, d_have;
         d_plain.alloc(std::max<u64>(total_words, 1));
         if (fill) {
             CUDA_CHECK(cudaMemset(d_plain.p, 0, d_plain.bytes()));
@@ -524,6 +547,7 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
             }
         }
         upload_vec(d_off, lane_plain_off);
+        upload_vec(d_have, lane_plain_words);
         std::vector<u32> chunk_lane, chunk_first, lane_chunk_off;
         build_chunk_table(t, &chunk_lane, &chunk_first, &lane_chunk_off);
         DeviceBuf<u32> d_cl, d_cf, d_lco;
@@ -532,8 +556,12 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
         upload_vec(d_lco, lane_chunk_off);
         ChunkTable ct{d_cl.p, d_cf.p, d_lco.p, chunk_lane.size()};
         if (ct.n_chunks) {
-            pack_plain_kernel<<<chunk_grid(ct.n_chunks), kChunkBlocks>>>(m->slots.p, m->group_hot.p, m->group_nblocks.p,
-                                                                         ct, d_plain.p, d_off.p);
+            if (m->wide())
+                pack_plain_kernel<true><<<chunk_grid(ct.n_chunks), kChunkBlocks>>>(m->slots.p, m->group_hot.p, m->group_nblocks.p,
+                                                                                   ct, d_plain.p, d_off.p, d_have.p);
+            else
+                pack_plain_kernel<false><<<chunk_grid(ct.n_chunks), kChunkBlocks>>>(m->slots.p, m->group_hot.p, m->group_nblocks.p,
+                                                                                    ct, d_plain.p, d_off.p, d_have.p);
             CUDA_CHECK(cudaGetLastError());
         }
         CUDA_CHECK(cudaDeviceSynchronize());
@@ -751,12 +779,14 @@ static void serialize_brwt(const Matrix *m, ByteSink &sink) {
             const u32 li = n.group * 4 + n.lane;
             const u64 hot = t.group_hot[n.group], nb = t.group_nblocks[n.group];
             const u64 n_words = (n.size + 63) / 64;
-            words.assign(std::max<u64>(n_words, (3 * nb + 1) / 2 + 1), 0);
+            const u64 dw = slot_data_words(t.slot_bits);   // data words per block
+            words.assign(std::max<u64>(n_words, (dw * nb + 1) / 2 + 1), 0);
             if (nb) {
-                if (d_plain.n < 3 * nb) d_plain.alloc(3 * nb + 3 * nb / 8);
-                unpack_lane_kernel<<<u32((nb + 255) / 256), 256>>>(m->slots.p, hot, nb, li & 3, d_plain.p);
+                if (d_plain.n < dw * nb) d_plain.alloc(dw * nb + dw * nb / 8);
+                if (m->wide()) unpack_lane_kernel<true><<<u32((nb + 255) / 256), 256>>>(m->slots.p, hot, nb, li & 3, d_plain.p);
+                else unpack_lane_kernel<false><<<u32((nb + 255) / 256), 256>>>(m->slots.p, hot, nb, li & 3, d_plain.p);
                 CUDA_CHECK(cudaGetLastError());
-                CUDA_CHECK(cudaMemcpy(words.data(), d_plain.p, size_t(3) * nb * 4, cudaMemcpyDeviceToHost));   // LE u32 pairs = u64
+                CUDA_CHECK(cudaMemcpy(words.data(), d_plain.p, size_t(dw) * nb * 4, cudaMemcpyDeviceToHost));   // LE u32 pairs = u64
             }
             write_rrr63(sink, reinterpret_cast<const uint64_t *>(words.data()), n.size);
             sink.u64be(n.children.size());
@@ -1011,7 +1041,7 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     ws->ran_safe = safe;
     Img img = m->img;
     void *kargs[] = {&img, &a};
-    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr), dim3(grid),
+    CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->wide()), dim3(grid),
                                 dim3(kRowsWarps * 32), kargs, ws->pipelined ? m->rows_smem_p : m->rows_smem, ws->stream));
 }
 
@@ -1453,6 +1483,15 @@ uint64_t ggq_num_relations(const ggq_matrix *m) { return m->num_relations; }
 uint64_t ggq_num_nodes(const ggq_matrix *m) { return m->n_nodes; }
 uint64_t ggq_total_column_size(const ggq_matrix *m) { return m->total_column_size; }
 uint64_t ggq_device_bytes(const ggq_matrix *m) { return m->device_bytes; }
+uint32_t ggq_slot_bits(const ggq_matrix *m) { return m && m->kind == Matrix::BRWT ? m->tree.slot_bits : 0; }
+
+int ggq_set_default_option(const char *name, uint64_t value) {
+    GGQ_TRY
+    if (!name) return fail(GGQ_ERR_ARG, "bad argument");
+    if (std::string(name) == "wide_slots") { g_default_wide.store(value ? 1 : 0, std::memory_order_relaxed); return GGQ_OK; }
+    return fail(GGQ_ERR_ARG, "unknown option");
+    GGQ_CATCH
+}
 uint64_t ggq_last_probe_count(const ggq_matrix *m) { return m->last_probes; }
 int ggq_leaf_code_info(const ggq_matrix *m, uint64_t what[4]) {
     if (!m || !what) return fail(GGQ_ERR_ARG, "bad argument");
@@ -2362,7 +2401,8 @@ static int get_cells(const ggq_matrix *m, const uint64_t *rows, const uint64_t *
         }
         unsigned char *d_res = reinterpret_cast<unsigned char *>(ws->d_bytes8.p);
         if (m->kind == Matrix::BRWT)
-            brwt_get_kernel<<<u32((n + 255) / 256), 256, 0, st>>>(m->img, ws->d_rows.p, d_cols, fixed_col, n, d_res);
+            if (m->wide()) brwt_get_kernel<true><<<u32((n + 255) / 256), 256, 0, st>>>(m->img, ws->d_rows.p, d_cols, fixed_col, n, d_res);
+            else brwt_get_kernel<false><<<u32((n + 255) / 256), 256, 0, st>>>(m->img, ws->d_rows.p, d_cols, fixed_col, n, d_res);
         else
             colmajor_get_launch(m, ws->d_rows.p, d_cols, fixed_col, n, d_res, st);
         CUDA_CHECK(cudaGetLastError());
@@ -2407,11 +2447,13 @@ static void column_device(const ggq_matrix *m, Workspace *ws, uint64_t col, Devi
         if (d_res->n < std::max<u64>(cnt, 1)) d_res->alloc(std::max<u64>(cnt, 1));
         if (cnt) {
             u64 nb = t.group_nblocks[leaf_li >> 2];
-            lane_enumerate_kernel<<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res->p);
+            if (m->wide()) lane_enumerate_kernel<true><<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res->p);
+            else lane_enumerate_kernel<false><<<u32((nb + 255) / 256), 256, 0, st>>>(m->img, leaf_li, d_res->p);
             for (u32 p = p1 - 1; p-- > p0;) {
                 u32 li = t.col_path[p];
                 if (m->lane_ones_h[li] == m->lane_size_h[li]) continue;  // all ones: identity (BRWT.cpp:77-78)
-                lane_select_kernel<<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res->p, cnt);
+                if (m->wide()) lane_select_kernel<true><<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res->p, cnt);
+                else lane_select_kernel<false><<<u32((cnt + 255) / 256), 256, 0, st>>>(m->img, li, d_res->p, cnt);
             }
             CUDA_CHECK(cudaGetLastError());
         }

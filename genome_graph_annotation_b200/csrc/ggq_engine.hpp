@@ -18,6 +18,7 @@ struct LimitError : std::runtime_error { using std::runtime_error::runtime_error
 struct NcclError : std::runtime_error { using std::runtime_error::runtime_error; };
 
 int fail(int code, const std::string &msg);
+u32 default_slot_bits();   // slot layout of the matrices created from now on (ggq_set_default_option)
 
 #define CUDA_CHECK(expr)                                                                          \
     do {                                                                                          \
@@ -72,6 +73,7 @@ struct Matrix {
     DeviceBuf<unsigned char> codes;
     DeviceBuf<uint4> code_rec;
     bool use_codes = true;        // ggq_set_option("leaf_codes", 0/1)
+    bool wide() const { return tree.slot_bits == kWideSlotBits; }   // capacity layout (ggq_layout.hpp)
     u64 code_bytes = 0;
     u32 n_coded = 0;
     double code_escape_rate = 0;  // visit-weighted escape fraction of the coded nodes (sampled at build time)

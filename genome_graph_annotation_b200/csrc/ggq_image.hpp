@@ -31,7 +31,7 @@ struct ImageHeader {
     u64 code_bytes, n_coded, code_escape_ppm, reserved2;
 };
 // the kernel constants an image depends on: a file written with other values must not be indexed with these
-static const u32 kImageLayout = kSlotBits | (kSuperShift << 8) | (kSelectShift << 16) | (kGroupLanes << 24);
+inline u32 image_layout(u32 slot_bits) { return slot_bits | (kSuperShift << 8) | (kSelectShift << 16) | (kGroupLanes << 24); }
 
 struct Fnv {
     u64 h = 0xcbf29ce484222325ull;
@@ -106,7 +106,9 @@ struct PinnedStage {
 
 // The checksum proves the tables are the ones that were written, not that they are sane: a file from a damaged
 // writer (or a forged one) must come back as GGQ_ERR_FORMAT, never as an out-of-bounds index on the host or device.
-inline void image_check_tables(const FlatTree &t, const ImageHeader &h, const std::vector<u64> &lane_ones_h) {
+inline void image_check_tables(const FlatTree &t, const ImageHeader &h, const std::vector<u64> &lane_ones_h,
+                               const std::vector<u64> &lane_size_h) {
+    const u32 wide_shift = t.slot_bits == kWideSlotBits ? 1 : 0;   // stride_log2 counts 16-byte units
     const u64 G = t.group_hot.size();
     const u64 n_leaf_cols = t.leaf_col.size();
     auto bad = [](const char *what) { throw ParseError(std::string("image file: ") + what); };
@@ -116,13 +118,16 @@ inline void image_check_tables(const FlatTree &t, const ImageHeader &h, const st
         const u64 hot = t.group_hot[g];
         const u64 base = hot & kGhBaseMask, nb = t.group_nblocks[g];
         const u32 sl = u32(hot >> kGhStrideShift) & 3u, cnt = u32(hot >> kGhCntShift) & 7u;
-        if (cnt > kGroupLanes || (cnt > (1u << sl))) bad("group shape");
+        if (cnt > kGroupLanes || sl < wide_shift || (cnt > (1u << (sl - wide_shift)))) bad("group shape");
+        if (wide_shift && nb > (u64(1) << 25)) bad("vector too long for the capacity layout");
         if (nb > (u64(1) << 40) || base + (nb << sl) > h.total_slots) bad("group outside the slot arena");
         if (((hot >> kGhMoreShift) & 1u) && g + 1 >= G) bad("continuation group missing");
         const u64 n_sb = nb ? ((nb - 1) >> kSuperShift) + 1 : 1;
         for (u32 k = 0; k < cnt; ++k) {
             const u64 li = g * 4 + k;
             const u32 info = t.lane_info[li];
+            // every position of the vector lies inside the group's blocks
+            if (lane_size_h[li] && (lane_ones_h[li] > lane_size_h[li] || lane_size_h[li] / t.slot_bits + 1 > nb)) bad("vector longer than its blocks");
             if (info == kRemoteLane) continue;
             if (info & kLeafFlag) {
                 if (u64(info & ~kLeafFlag) + t.lane_aux[li] > n_leaf_cols) bad("leaf rank out of range");
@@ -230,7 +235,7 @@ inline void image_save(const Matrix *m, const char *path) {
     h.n_nodes = m->n_nodes; h.total_column_size = m->total_column_size; h.num_relations = m->num_relations;
     h.total_slots = m->slots.n; h.total_sb = m->sb_base.n; h.total_sel = m->sel.n;
     h.max_depth = t.max_depth; h.multi_leaf = t.multi_column_leaves; h.shard = t.shard; h.n_shards = t.n_shards;
-    h.cut_depth = t.cut_depth; h.layout = kImageLayout;
+    h.cut_depth = t.cut_depth; h.layout = image_layout(t.slot_bits);
     h.code_bytes = m->code_bytes; h.n_coded = m->n_coded; h.code_escape_ppm = u64(m->code_escape_rate * 1e6 + 0.5);
     io.put(&h, sizeof(h));
     io.put_vec(t.group_hot); io.put_vec(t.group_nblocks);
@@ -257,7 +262,8 @@ inline Matrix *image_load(const char *path, int device) {
     io.get(&h, sizeof(h));
     if (std::memcmp(h.magic, kImageMagic, 8) != 0) throw ParseError("not a ggq image file (or another version)");
     if (h.endian != kImageEndian || h.kind != 0) throw ParseError("image file of a foreign byte order / kind");
-    if (h.layout != kImageLayout) throw ParseError("image file written by a build with another slot layout");
+    if (h.layout != image_layout(kSlotBits) && h.layout != image_layout(kWideSlotBits))
+        throw ParseError("image file written by a build with another slot layout");
     if (h.n_rows >= kMaxRows || h.n_cols >= (u64(1) << 31)) throw LimitError("image exceeds engine limits");
     std::unique_ptr<Matrix> m(new Matrix());
     m->kind = Matrix::BRWT;
@@ -265,6 +271,7 @@ inline Matrix *image_load(const char *path, int device) {
     CUDA_CHECK(cudaSetDevice(device));
     FlatTree &t = m->tree;
     t.n_rows = h.n_rows; t.n_cols = h.n_cols;
+    t.slot_bits = h.layout & 0xffu;
     const u64 lim = u64(1) << 33;
     io.get_vec(&t.group_hot, kMaxGroups); io.get_vec(&t.group_nblocks, kMaxGroups);
     io.get_vec(&t.lane_info, u64(kMaxGroups) * 4); io.get_vec(&t.lane_aux, u64(kMaxGroups) * 4);
@@ -283,7 +290,7 @@ inline Matrix *image_load(const char *path, int device) {
         m->lane_ones_h.size() != 4 * G || t.col_path_off.size() != t.n_cols + 1 ||
         (!t.col_owned.empty() && t.col_owned.size() != t.n_cols))
         throw ParseError("image file: inconsistent tables");
-    image_check_tables(t, h, m->lane_ones_h);
+    image_check_tables(t, h, m->lane_ones_h, m->lane_size_h);
     if (h.n_shards > 1) { t.nodes.clear(); t.lane_node.clear(); }   // (a shard's image does not carry which nodes it holds)
     t.total_slots = h.total_slots; t.total_sb = h.total_sb; t.total_sel = h.total_sel;
     t.max_depth = h.max_depth; t.multi_column_leaves = h.multi_leaf != 0;

@@ -23,10 +23,13 @@ struct ChunkTable {
     u64 n_chunks;
 };
 
-// One CTA per chunk (kChunkBlocks threads): copy 96 plain bits per block into the slot data words.
+// One CTA per chunk (kChunkBlocks threads): copy the plain bits of one block (96, or 224 in the capacity layout) into
+// the slot's data words.  lane_plain_words[li] = words the lane owns in `plain`: reads beyond them are zeros.
+template <bool WIDE>
 __global__ void __launch_bounds__(kChunkBlocks)
 pack_plain_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, ChunkTable ct,
-                  const u32 *plain, const u64 *lane_plain_off) {
+                  const u32 *plain, const u64 *lane_plain_off, const u64 *lane_plain_words) {
+    constexpr u32 DW = SlotGeom<WIDE>::kWords;
     u64 chunk = blockIdx.x + u64(blockIdx.y) * gridDim.x;
     if (chunk >= ct.n_chunks) return;
     u32 li = ct.chunk_lane[chunk];
@@ -34,11 +37,12 @@ pack_plain_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, 
     u64 b = u64(ct.chunk_first[chunk]) + threadIdx.x;
     if (b >= group_nblocks[g]) return;
     u64 hot = group_hot[g];
-    u32 sl = u32(hot >> kGhStrideShift) & 3u;
-    const u32 *src = plain + lane_plain_off[li] + 3 * b;
-    uint4 s;
-    s.x = 0; s.y = src[0]; s.z = src[1]; s.w = src[2];
-    slots[(hot & kGhBaseMask) + (b << sl) + (li & 3)] = s;
+    const u32 *src = plain + lane_plain_off[li];
+    const u64 have = lane_plain_words[li];
+    u32 w[DW];
+    #pragma unroll
+    for (u32 i = 0; i < DW; ++i) w[i] = DW * b + i < have ? src[DW * b + i] : 0u;
+    SlotT<WIDE>::store_words(slots + slot_index_t<WIDE>(hot, b, li & 3), w);
 }
 
 __device__ __forceinline__ u32 block_reduce_sum_256(u32 v, u32 *sh) {
@@ -53,6 +57,7 @@ __device__ __forceinline__ u32 block_reduce_sum_256(u32 v, u32 *sh) {
 }
 
 // pass A: ones per chunk
+template <bool WIDE>
 __global__ void __launch_bounds__(kChunkBlocks)
 chunk_sum_kernel(const uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, ChunkTable ct,
                  u32 *chunk_sum) {
@@ -63,12 +68,8 @@ chunk_sum_kernel(const uint4 *slots, const u64 *group_hot, const u64 *group_nblo
     u32 g = li >> 2;
     u64 b = u64(ct.chunk_first[chunk]) + threadIdx.x;
     u64 hot = group_hot[g];
-    u32 sl = u32(hot >> kGhStrideShift) & 3u;
     u32 c = 0;
-    if (b < group_nblocks[g]) {
-        uint4 s = slots[(hot & kGhBaseMask) + (b << sl) + (li & 3)];
-        c = slot_popc(s);
-    }
+    if (b < group_nblocks[g]) c = SlotT<WIDE>::load_plain(slots + slot_index_t<WIDE>(hot, b, li & 3)).popc();
     u32 tot = block_reduce_sum_256(c, sh);
     if (threadIdx.x == 0) chunk_sum[chunk] = tot;
 }
@@ -111,6 +112,7 @@ lane_scan_kernel(const u32 *lane_chunk_off, const u32 *chunk_sum, u64 *chunk_bas
 }
 
 // pass C: rank headers (relative to the superblock base) and select samples
+template <bool WIDE>
 __global__ void __launch_bounds__(kChunkBlocks)
 header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, ChunkTable ct,
               const u64 *chunk_base, const u32 *lane_info, const u64 *lane_sel_off, u32 *sel,
@@ -123,11 +125,10 @@ header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, Chun
     u64 nb = group_nblocks[g];
     u64 b = u64(ct.chunk_first[chunk]) + threadIdx.x;
     u64 hot = group_hot[g];
-    u32 sl = u32(hot >> kGhStrideShift) & 3u;
-    uint4 *p = slots + (hot & kGhBaseMask) + (b << sl) + (li & 3);
-    uint4 s = make_uint4(0, 0, 0, 0);
+    uint4 *p = slots + slot_index_t<WIDE>(hot, b, li & 3);
+    SlotT<WIDE> s{};
     u32 c = 0;
-    if (b < nb) { s = *p; c = slot_popc(s); }
+    if (b < nb) { s = SlotT<WIDE>::load_plain(p); c = s.popc(); }
     sh[threadIdx.x] = c;
     __syncthreads();
     for (int o = 1; o < kChunkBlocks; o <<= 1) {
@@ -142,14 +143,13 @@ header_kernel(uint4 *slots, const u64 *group_hot, const u64 *group_nblocks, Chun
     const u32 chunks_per_sb = (1u << kSuperShift) / kChunkBlocks;
     u32 local = u32(chunk - ct.lane_chunk_off[li]);
     u64 sbb = chunk_base[chunk - (local % chunks_per_sb)];
-    s.x = u32(abs_before - sbb);
-    *p = s;
+    s.store_header(p, u32(abs_before - sbb));
     bool internal = !(lane_info[li] & kLeafFlag) || g == 0;
     if (want_select && internal) {
         u32 *my_sel = sel + lane_sel_off[li];
         u64 first = (abs_before + (1ull << kSelectShift) - 1) >> kSelectShift;
         if ((first << kSelectShift) < abs_before + c) my_sel[first] = u32(b);
-        // (a 96-bit block holds at most one multiple of 1024)
+        // (a block of 96 or 224 positions holds at most one multiple of 1024)
         if (b == nb - 1) {  // sentinel sample after the last real one
             u64 ones = abs_before + c;
             my_sel[(ones + (1ull << kSelectShift) - 1) >> kSelectShift] = u32(b);
@@ -614,14 +614,16 @@ __global__ void slice_rows_kernel(const u64 *offsets, const u32 *cols, u64 n, u6
     out[o] = ~0ull;
 }
 
-// One lane of the arena back to plain bits (3 data words per block): the inverse of pack_plain_kernel, used by
+// One lane of the arena back to plain bits (3 or 7 data words per block): the inverse of pack_plain_kernel, used by
 // ggq_brwt_serialize.
+template <bool WIDE>
 __global__ void unpack_lane_kernel(const uint4 *slots, u64 hot, u64 n_blocks, u32 lane, u32 *plain) {
+    constexpr u32 DW = SlotGeom<WIDE>::kWords;
     const u64 b = u64(blockIdx.x) * blockDim.x + threadIdx.x;
     if (b >= n_blocks) return;
-    const u32 sl = u32(hot >> kGhStrideShift) & 3u;
-    const uint4 s = slots[(hot & kGhBaseMask) + (b << sl) + lane];
-    plain[3 * b] = s.y; plain[3 * b + 1] = s.z; plain[3 * b + 2] = s.w;
+    const SlotT<WIDE> s = SlotT<WIDE>::load_plain(slots + slot_index_t<WIDE>(hot, b, lane));
+    #pragma unroll
+    for (u32 i = 0; i < DW; ++i) plain[DW * b + i] = s.word(i);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -634,6 +636,7 @@ __global__ void unpack_lane_kernel(const uint4 *slots, u64 hot, u64 n_blocks, u3
 // ------------------------------------------------------------------------------------------
 constexpr int kCodeStack = 64;   // pending groups of one walk; the engine codes only subtrees with fewer groups
 
+template <bool WIDE>
 __global__ void __launch_bounds__(256)
 leaf_code_kernel(Img img, u32 g0, u64 n_pos, u32 rank0, u64 stride, bool sample, unsigned char *codes, unsigned long long *escapes) {
     const u64 n_work = (n_pos + stride - 1) / stride;
@@ -652,20 +655,21 @@ leaf_code_kernel(Img img, u32 g0, u64 n_pos, u32 rank0, u64 stride, bool sample,
             const u64 hot = __ldg(img.group_hot + g);
             const u32 cnt = u32(hot >> kGhCntShift) & 7u;
             if (((hot >> kGhMoreShift) & 1u) && sp < kCodeStack) { st_g[sp] = g + 1; st_r[sp] = r; ++sp; }
-            const u64 blk = r / kSlotBits;
-            const u32 bit = u32(r - blk * kSlotBits);
+            u64 blk;
+            u32 bit;
+            SlotT<WIDE>::div(r, blk, bit);
             // children in reverse so that the walk is depth-first in child order (irrelevant to the result)
             for (int k = int(cnt) - 1; k >= 0; --k) {
                 const u32 li = g * 4 + u32(k);
-                const uint4 s = ld_slot_cached(slot_addr(img, hot, blk, u32(k)));
-                if (!slot_test(s, bit)) continue;
+                const SlotT<WIDE> s = SlotT<WIDE>::load_cached(slot_addr_t<WIDE>(img, hot, blk, u32(k)));
+                if (!s.test(bit)) continue;
                 const u32 info = __ldg(img.lane_info + li);
                 if (info & kLeafFlag) {
                     ++found;
                     code = (info & ~kLeafFlag) - rank0;
                 } else if (sp < kCodeStack) {
                     st_g[sp] = info;
-                    st_r[sp] = lane_rank_base(img, li, blk, s) + slot_rank_before(s, bit);
+                    st_r[sp] = lane_rank_base_h(img, li, blk, s.header()) + s.rank_before(bit);
                     ++sp;
                 } else {
                     found = 2;   // cannot happen for subtrees the engine selects; be safe: escape
@@ -685,6 +689,7 @@ leaf_code_kernel(Img img, u32 g0, u64 n_pos, u32 rank0, u64 stride, bool sample,
 // ------------------------------------------------------------------------------------------
 // K2: get(row, column).  One thread per query walks the column's root-to-leaf lane path.
 // ------------------------------------------------------------------------------------------
+template <bool WIDE>
 __global__ void brwt_get_kernel(Img img, const u64 *rows, const u64 *cols, u64 fixed_col, u64 n,
                                 unsigned char *out) {
     u64 t = u64(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -698,11 +703,17 @@ __global__ void brwt_get_kernel(Img img, const u64 *rows, const u64 *cols, u64 f
         for (u32 p = p0; p < p1; ++p) {
             u32 li = img.col_path[p];
             u64 hot = __ldg(img.group_hot + (li >> 2));
-            u64 blk = r / kSlotBits;
-            u32 bit = u32(r - blk * kSlotBits);
-            uint4 s = ld_slot(slot_addr(img, hot, blk, li & 3));
-            if (!slot_test(s, bit)) { res = false; break; }
-            if (p + 1 < p1) r = lane_rank_base(img, li, blk, s) + slot_rank_before(s, bit);
+            u64 blk;
+            u32 bit;
+            if (WIDE) {
+                SlotT<WIDE>::div(r, blk, bit);
+            } else {
+                blk = r / kSlotBits;
+                bit = u32(r - blk * kSlotBits);
+            }
+            const SlotT<WIDE> s = SlotT<WIDE>::load(slot_addr_t<WIDE>(img, hot, blk, li & 3));
+            if (!s.test(bit)) { res = false; break; }
+            if (p + 1 < p1) r = lane_rank_base_h(img, li, blk, s.header()) + s.rank_before(bit);
         }
     }
     out[t] = res;
@@ -712,24 +723,25 @@ __global__ void brwt_get_kernel(Img img, const u64 *rows, const u64 *cols, u64 f
 // K3: get_column
 // ------------------------------------------------------------------------------------------
 // a: positions of the ones of one lane, ascending (one thread per block; the rank header is the output index)
+template <bool WIDE>
 __global__ void lane_enumerate_kernel(Img img, u32 li, u64 *out) {
     u32 g = li >> 2;
     u64 nb = img.group_nblocks[g];
     u64 b = u64(blockIdx.x) * blockDim.x + threadIdx.x;
     if (b >= nb) return;
     u64 hot = img.group_hot[g];
-    uint4 s = ld_slot_cached(slot_addr(img, hot, b, li & 3));
-    u64 o = lane_rank_base(img, li, b, s);
-    u64 pos = b * kSlotBits;
-    u32 w = s.y;
-    while (w) { out[o++] = pos + __ffs(w) - 1; w &= w - 1; }
-    w = s.z;
-    while (w) { out[o++] = pos + 32 + __ffs(w) - 1; w &= w - 1; }
-    w = s.w;
-    while (w) { out[o++] = pos + 64 + __ffs(w) - 1; w &= w - 1; }
+    const SlotT<WIDE> s = SlotT<WIDE>::load_cached(slot_addr_t<WIDE>(img, hot, b, li & 3));
+    u64 o = lane_rank_base_h(img, li, b, s.header());
+    u64 pos = b * SlotGeom<WIDE>::kBits;
+    #pragma unroll
+    for (u32 i = 0; i < SlotGeom<WIDE>::kWords; ++i) {
+        u32 w = s.word(i);
+        while (w) { out[o++] = pos + 32 * i + __ffs(w) - 1; w &= w - 1; }
+    }
 }
 
 // select of the q-th (0-based) one of lane li
+template <bool WIDE>
 __device__ __forceinline__ u64 lane_select0(const Img &img, u32 li, u64 hot, u64 q) {
     const u32 *sel = img.sel + img.lane_sel_off[li];
     u64 si = q >> kSelectShift;
@@ -737,20 +749,21 @@ __device__ __forceinline__ u64 lane_select0(const Img &img, u32 li, u64 hot, u64
     // last block in [lo, hi] whose absolute header is <= q
     while (lo < hi) {
         u64 mid = (lo + hi + 1) >> 1;
-        uint4 s = ld_slot_cached(slot_addr(img, hot, mid, li & 3));
-        if (lane_rank_base(img, li, mid, s) <= q) lo = mid; else hi = mid - 1;
+        const u32 h = __ldg(reinterpret_cast<const u32 *>(slot_addr_t<WIDE>(img, hot, mid, li & 3)));   // the rank header
+        if (lane_rank_base_h(img, li, mid, h) <= q) lo = mid; else hi = mid - 1;
     }
-    uint4 s = ld_slot_cached(slot_addr(img, hot, lo, li & 3));
-    u64 before = lane_rank_base(img, li, lo, s);
-    return lo * kSlotBits + slot_select(s, u32(q - before));
+    const SlotT<WIDE> s = SlotT<WIDE>::load_cached(slot_addr_t<WIDE>(img, hot, lo, li & 3));
+    u64 before = lane_rank_base_h(img, li, lo, s.header());
+    return lo * SlotGeom<WIDE>::kBits + s.select(u32(q - before));
 }
 
 // b: rows[i] = select1(rows[i] + 1) in lane li  (BRWT.cpp:81-83)
+template <bool WIDE>
 __global__ void lane_select_kernel(Img img, u32 li, u64 *rows, u64 n) {
     u64 i = u64(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
     u64 hot = __ldg(img.group_hot + (li >> 2));
-    rows[i] = lane_select0(img, li, hot, rows[i]);
+    rows[i] = lane_select0<WIDE>(img, li, hot, rows[i]);
 }
 
 }  // namespace ggq

@@ -13,6 +13,18 @@
 namespace ggq {
 
 constexpr uint32_t kSlotBits = 96;          // positions per slot
+// Capacity layout ("wide slots"): a slot is 32 bytes = { u32 rank_before, u32 bits[7] } = 224
+// positions — one DRAM sector per child and probe, 14.3 % header overhead instead of 33.3 %.  Blocks of a group are
+// 32/64/128 bytes (the group's stride_log2 counts 16-byte units, so it is one more than in the default layout).
+// Vectors are limited to 2^32 positions in this layout (one superblock: ones fit the 32-bit header).
+constexpr uint32_t kWideSlotBits = 224;
+template <bool WIDE> struct SlotGeom {
+    static constexpr uint32_t kBits = WIDE ? kWideSlotBits : kSlotBits;   // positions per slot
+    static constexpr uint32_t kWords = WIDE ? 7u : 3u;                     // data words per slot
+    static constexpr uint32_t kQuads = WIDE ? 2u : 1u;                     // 16-byte units per slot
+};
+inline uint32_t slot_quads(uint32_t slot_bits) { return slot_bits == kWideSlotBits ? 2u : 1u; }
+inline uint32_t slot_data_words(uint32_t slot_bits) { return slot_bits == kWideSlotBits ? 7u : 3u; }
 constexpr uint32_t kGroupLanes = 4;         // sibling vectors interleaved per group
 constexpr uint32_t kSuperShift = 25;        // superblock = 2^25 blocks = 96 * 2^25 positions (< 2^32 ones)
 constexpr uint32_t kSelectShift = 10;       // one select sample per 1024 ones

@@ -172,7 +172,9 @@ __device__ __forceinline__ u32 ld_code(const unsigned char *p) {
     return v;
 }
 
-template <bool SPILL, bool MULTI_LEAF, bool COMPACT>
+// WIDE: the capacity layout (32-byte slots of 224 positions, ggq_layout.hpp): a lane reads one 32-byte sector per
+// child — twice the sectors of the default layout, where one sector holds two children.
+template <bool SPILL, bool MULTI_LEAF, bool COMPACT, bool WIDE = false>
 __global__ void __launch_bounds__(kRowsWarps * 32)
 brwt_rows_kernel(Img img, RowsArgs a) {
     typedef RecFmt<COMPACT> Fmt;
@@ -230,10 +232,10 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                 touches += 1;
             } else if (valid) {
                 u64 blk; u32 bit;
-                div96(r, blk, bit);
-                const uint4 s = ld_slot(img.slots + a.root_base + (blk << a.root_sl));
-                if (slot_test(s, bit)) {
-                    u64 ones = u64(s.x) + slot_rank_before(s, bit);
+                SlotT<WIDE>::div(r, blk, bit);
+                const SlotT<WIDE> s = SlotT<WIDE>::load(img.slots + a.root_base + (blk << a.root_sl));
+                if (s.test(bit)) {
+                    u64 ones = u64(s.header()) + s.rank_before(bit);
                     if (a.root_multi_sb) ones += img.sb_base[img.lane_sb_off[0] + (blk >> kSuperShift)];
                     it = (ones << kItemRShift) | (u64(lane) << kItemGroupBits) | a.root_child;
                     push = true;
@@ -271,7 +273,11 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                 if (half == 0) touches += cnt;
                 if (2 * half < cnt) {
                     u64 blk; u32 bit;
-                    if (short_rows) {
+                    if (WIDE) {
+                        const u32 r32 = u32(item >> kItemRShift), q = r32 / kWideSlotBits;   // (vectors < 2^32 positions)
+                        blk = q;
+                        bit = r32 - q * kWideSlotBits;
+                    } else if (short_rows) {
                         const u32 q = __umulhi(u32(item >> (kItemRShift + 5)), 0xAAAAAAABu) >> 1;
                         blk = q;
                         bit = u32(item >> kItemRShift) - q * kSlotBits;
@@ -280,25 +286,37 @@ brwt_rows_kernel(Img img, RowsArgs a) {
                         blk = rr / kSlotBits;
                         bit = u32(rr - blk * kSlotBits);
                     }
-                    const u64 si = gbase + (blk << sl) + 2 * half;   // slot of child 2*half
-                    uint4 s0, s1;
-                    ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
-                    if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
-                    const u32 wsel = bit >> 5, sh = bit & 31, below = (1u << sh) - 1u;
-                    const u32 w0 = wsel == 0 ? s0.y : (wsel == 1 ? s0.z : s0.w);
-                    const u32 w1 = wsel == 0 ? s1.y : (wsel == 1 ? s1.z : s1.w);
-                    const bool set0 = (w0 >> sh) & 1u;
-                    const bool set1 = (2 * half + 1 < cnt) && ((w1 >> sh) & 1u);
                     const bool leaf0 = child0 & Fmt::kLeaf, leaf1 = child1 & Fmt::kLeaf;
                     const u32 t = tq >> kItemGroupBits;
                     const u32 bm_row = bm + t * bm_row_bytes, sum_row = sum0 + t * sum_row_bytes;
+                    bool set0, set1;
+                    u64 ones0, ones1;   // r' = rank1(r) - 1 = ones strictly before r (BRWT.cpp:43-50)
+                    if (WIDE) {
+                        const uint4 *p0 = img.slots + gbase + (blk << sl) + 4 * half;   // child 2*half; two 16-byte units per child
+                        const bool has1 = 2 * half + 1 < cnt;
+                        const SlotT<true> a0 = SlotT<true>::load(p0);
+                        const SlotT<true> a1 = SlotT<true>::load(has1 ? p0 + 2 : p0);
+                        set0 = a0.test(bit);
+                        set1 = has1 && a1.test(bit);
+                        ones0 = a0.header() + a0.rank_before(bit);
+                        ones1 = a1.header() + a1.rank_before(bit);
+                    } else {
+                        const u64 si = gbase + (blk << sl) + 2 * half;   // slot of child 2*half
+                        uint4 s0, s1;
+                        ld_slot2(img.slots + (si & ~u64(1)), s0, s1);
+                        if (si & 1) s0 = s1;                            // stride-1 groups: odd blocks sit in the upper half
+                        const u32 wsel = bit >> 5, sh = bit & 31, below = (1u << sh) - 1u;
+                        const u32 w0 = wsel == 0 ? s0.y : (wsel == 1 ? s0.z : s0.w);
+                        const u32 w1 = wsel == 0 ? s1.y : (wsel == 1 ? s1.z : s1.w);
+                        set0 = (w0 >> sh) & 1u;
+                        set1 = (2 * half + 1 < cnt) && ((w1 >> sh) & 1u);
+                        ones0 = slot_ones_before(s0, w0, wsel, below);
+                        ones1 = slot_ones_before(s1, w1, wsel, below);
+                    }
                     if (set0 && leaf0 && child0 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child0 & (Fmt::kLeaf - 1u), g * 4 + 2 * half, bm_row, sum_row, cnt0 + t * 4);
                     if (set1 && leaf1 && child1 != Fmt::kRemote) mark_leaf<MULTI_LEAF>(img, child1 & (Fmt::kLeaf - 1u), g * 4 + 2 * half + 1, bm_row, sum_row, cnt0 + t * 4);
                     push0 = set0 && !leaf0;
                     push1 = set1 && !leaf1;
-                    // r' = rank1(r) - 1 = ones strictly before r (BRWT.cpp:43-50)
-                    u64 ones0 = slot_ones_before(s0, w0, wsel, below);
-                    u64 ones1 = slot_ones_before(s1, w1, wsel, below);
                     if ((flags >> 6) & 1u) {     // some lane of the group spans several superblocks
                         const u64 sb = blk >> kSuperShift;
                         if (push0) ones0 += img.sb_base[img.lane_sb_off[g * 4 + 2 * half] + sb];   // entry 0 of a lane is 0

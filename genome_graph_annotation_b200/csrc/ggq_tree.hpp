@@ -39,6 +39,7 @@ struct FlatTree {
     uint64_t n_rows = 0, n_cols = 0;
     std::vector<FlatNode> nodes;
     // geometry
+    uint32_t slot_bits = kSlotBits;       // kSlotBits (default) or kWideSlotBits (capacity layout), set before assign_groups
     std::vector<uint64_t> group_hot;      // see ggq_layout.hpp
     std::vector<uint64_t> group_nblocks;  // incl. sentinel
     std::vector<uint32_t> group_parent;   // node whose children the group holds (root group: ~0u)
@@ -171,7 +172,7 @@ inline void assign_groups(FlatTree *t) {
     t->group_hot.clear(); t->group_nblocks.clear(); t->group_parent.clear();
     t->lane_info.clear(); t->lane_aux.clear(); t->lane_node.clear();
     auto new_group = [&](uint32_t parent, uint32_t cnt, uint32_t more) {
-        uint32_t sl = cnt <= 1 ? 0 : (cnt == 2 ? 1 : 2);
+        uint32_t sl = (cnt <= 1 ? 0 : (cnt == 2 ? 1 : 2)) + (t->slot_bits == kWideSlotBits ? 1 : 0);   // in 16-byte units
         t->group_hot.push_back(pack_group_hot(0, sl, cnt, more));
         t->group_nblocks.push_back(0);
         t->group_parent.push_back(parent);
@@ -315,7 +316,9 @@ inline void assign_geometry(FlatTree *t) {
         const bool g_present = t->present(t->lane_node[g * 4]);
         uint64_t len = g_present ? N[t->lane_node[g * 4]].size : 0;
         if (len >= kMaxRows) throw ParseError("vector longer than the engine supports");
-        uint64_t nb = g_present ? len / kSlotBits + 1 : 0;  // + sentinel block
+        if (t->slot_bits == kWideSlotBits && len >= (uint64_t(1) << 32))
+            throw ParseError("vector longer than the capacity layout supports (2^32 positions)");
+        uint64_t nb = g_present ? len / t->slot_bits + 1 : 0;  // + sentinel block
         slot = (slot + 3) & ~uint64_t(3);   // 64-byte alignment of every group
         t->group_hot[g] = pack_group_hot(slot, sl, cnt, more) | (uint64_t(nb && ((nb - 1) >> kSuperShift) != 0) << kGhSuperShift);
         t->group_nblocks[g] = nb;

@@ -129,6 +129,14 @@ uint64_t ggq_num_relations(const ggq_matrix *m);
 uint64_t ggq_num_nodes(const ggq_matrix *m);
 uint64_t ggq_total_column_size(const ggq_matrix *m);
 uint64_t ggq_device_bytes(const ggq_matrix *m);
+/* Positions per slot of a BRWT image: 96 (default layout) or 224 (capacity layout, below); 0 for column-major. */
+uint32_t ggq_slot_bits(const ggq_matrix *m);
+/* Process-wide defaults for the matrices created AFTER the call (load, build, synthesize; an image file keeps the
+ * layout it was written with).  "wide_slots": 0 = 16-byte slots {rank, 96 bits} (default; fastest: one 32-byte sector
+ * answers two children), 1 = the capacity layout: 32-byte slots {rank, 224 bits} — 14 % instead of 33 % rank-header
+ * overhead (a matrix that does not fit in the default layout may fit in this one), one sector per child;
+ * vectors are limited to 2^32 positions.  Results are identical in both layouts.  Unknown name: GGQ_ERR_ARG. */
+int ggq_set_default_option(const char *name, uint64_t value);
 /* Leaf codes of a BRWT image: what[0] = coded nodes, what[1] = code bytes on the device,
  * what[2] = sampled escape rate x 1e6 (visit-weighted), what[3] = 1 if the descent currently uses them. */
 int ggq_leaf_code_info(const ggq_matrix *m, uint64_t what[4]);

@@ -238,6 +238,14 @@ class GpuBRWT final : public GpuMatrixBase {
     uint64_t num_nodes() const { return h_ ? ggq_num_nodes(h_.get()) : 0; }
     uint64_t total_column_size() const { return h_ ? ggq_total_column_size(h_.get()) : 0; }
 
+    // Capacity layout (ggq_set_default_option "wide_slots"): matrices loaded / built AFTER the call use 32-byte slots of
+    // 224 positions — 14 % instead of 33 % rank overhead, for matrices that do not fit a device otherwise; slower
+    // descent (one sector per child), identical answers.  Process-wide.
+    static void use_capacity_layout(bool on) {
+        if (ggq_set_default_option("wide_slots", on ? 1 : 0) != GGQ_OK) throw std::runtime_error(ggq_last_error());
+    }
+    uint32_t slot_bits() const { return h_ ? ggq_slot_bits(h_.get()) : 0; }
+
     // Flattened device image (ggq_image_save / ggq_image_load): written once next to the .brwt.annodbg, it restores
     // the GPU-resident layout without parsing the stream again.  `stream_path` (optional) names the serialized
     // matrix the image was made from; it is read back only if serialize() is called.

@@ -12,16 +12,25 @@ from conftest import ROOT
 pytestmark = pytest.mark.gpu
 
 
-def test_cpp_adapters_match_reference():
+def layout_env(wide):
+    """GGQ_WIDE_SLOTS=1: the process creates its matrices in the capacity layout — same answers."""
+    env = dict(os.environ)
+    env["GGQ_WIDE_SLOTS"] = "1" if wide else "0"
+    return env
+
+
+@pytest.mark.parametrize("wide", [False, True], ids=["default_layout", "capacity_layout"])
+def test_cpp_adapters_match_reference(wide):
     exe = os.path.join(ROOT, "oracle", "_ref", "adapter_test")
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref/adapter_test not built (needs /root/reference at build time)")
-    p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, env=layout_env(wide))
     assert p.returncode == 0, p.stdout[-3000:]
     assert "all checks passed" in p.stdout
 
 
-def test_reference_annotator_instantiated_over_the_gpu_matrix():
+@pytest.mark.parametrize("wide", [False, True], ids=["default_layout", "capacity_layout"])
+def test_reference_annotator_instantiated_over_the_gpu_matrix(wide):
     """annotate::StaticBinRelAnnotator<ggq::GpuBRWT, std::string> — the reference's own caller template over the GPU
     matrix (tests/cpp/annotator_test.cpp): loads the .brwt.annodbg the reference wrote, and answers the known-answer
     cases of the reference's tests/test_annotation_BRWT.cpp (get / has_labels / get_top_labels = Label2:4, Label8:3,
@@ -29,7 +38,7 @@ def test_reference_annotator_instantiated_over_the_gpu_matrix():
     exe = os.path.join(ROOT, "oracle", "_ref", "annotator_test")
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref/annotator_test not built (needs /root/reference at build time)")
-    p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    p = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, env=layout_env(wide))
     assert p.returncode == 0, p.stdout[-3000:]
     assert "all checks passed" in p.stdout
 
