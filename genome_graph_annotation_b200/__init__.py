@@ -83,6 +83,8 @@ def lib():
         "ggq_total_column_size": (C.c_uint64, [vp]),
         "ggq_device_bytes": (C.c_uint64, [vp]),
         "ggq_slot_bits": (C.c_uint32, [vp]),
+        "ggq_brwt_serialize_file": (C.c_int, [vp, C.c_char_p, u64p]),
+        "ggq_brwt_load_file": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
         "ggq_set_default_option": (C.c_int, [C.c_char_p, C.c_uint64]),
         "ggq_leaf_code_info": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "ggq_last_probe_count": (C.c_uint64, [vp]),
@@ -285,6 +287,19 @@ class GpuMatrix:
         m = cls(h.value, "brwt")
         m.consumed = used.value
         return m
+
+    @classmethod
+    def load_brwt_file(cls, path, device=0):
+        """BRWT::load from a file holding the matrix stream (ggq_brwt_load_file)."""
+        h = C.c_void_p()
+        _check(lib().ggq_brwt_load_file(os.fsencode(path), device, C.byref(h)))
+        return cls(h.value, "brwt")
+
+    def serialize_to_file(self, path):
+        """BRWT::serialize from the device image into a file (ggq_brwt_serialize_file) -> bytes written."""
+        n = C.c_uint64()
+        _check(lib().ggq_brwt_serialize_file(self._h, os.fsencode(path), C.byref(n)))
+        return n.value
 
     @classmethod
     def build_brwt(cls, col_words, n_rows, greedy=False, arity=2, relax=0, device=0):

@@ -531,19 +531,37 @@ static Matrix *upload_brwt(FlatTree &&tree, int device, u32 shard = 0, u32 n_sha
             CUDA_CHECK(cudaMemset(d_plain.p, 0, d_plain.bytes()));
             (*fill)(t, d_plain.p, lane_plain_off);
         } else {
-            for (u32 li = 0; li < n_lanes; ++li) {
-                if (t.lane_node[li] == ~0u || !t.present(t.lane_node[li])) continue;
-                FlatNode &nd = t.nodes[t.lane_node[li]];
-                if (nd.lazy) {   // decode now, upload, forget: the host holds the plain bits of one node at a time
-                    decode_rrr63(nd.raw, &nd.bits);
-                    if (nd.bits.size != nd.size || (!nd.children.empty() && nd.bits.ones != nd.ones))
-                        throw ParseError("BRWT: child length differs from the parent's popcount");
-                    nd.ones = nd.bits.ones;
-                    nd.raw.clear();
+            // Lazily parsed vectors are decoded in batches of at most 2^33 plain bits (1 GiB; a longer vector is a batch
+            // of its own) on the host's threads, uploaded, and forgotten: the host never holds more plain bits than that.
+            const u64 kBatchBits = u64(1) << 33;
+            std::vector<u32> lanes;
+            for (u32 li = 0; li < n_lanes; ++li)
+                if (t.lane_node[li] != ~0u && t.present(t.lane_node[li])) lanes.push_back(li);
+            for (size_t i = 0; i < lanes.size();) {
+                size_t j = i;
+                u64 bits = 0;
+                std::vector<FlatNode *> batch;
+                for (; j < lanes.size(); ++j) {
+                    FlatNode &nd = t.nodes[t.lane_node[lanes[j]]];
+                    if (!nd.lazy) continue;
+                    if (!batch.empty() && bits + nd.size > kBatchBits) break;
+                    batch.push_back(&nd);
+                    bits += nd.size;
                 }
-                const auto &w = nd.bits.w;
-                CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
-                if (nd.lazy) { nd.bits.w.clear(); nd.bits.w.shrink_to_fit(); }
+                decode_nodes_parallel(batch);
+                for (; i < j; ++i) {
+                    const u32 li = lanes[i];
+                    FlatNode &nd = t.nodes[t.lane_node[li]];
+                    if (nd.lazy) {
+                        if (nd.bits.size != nd.size || (!nd.children.empty() && nd.bits.ones != nd.ones))
+                            throw ParseError("BRWT: child length differs from the parent's popcount");
+                        nd.ones = nd.bits.ones;
+                        nd.raw.clear();
+                    }
+                    const auto &w = nd.bits.w;
+                    CUDA_CHECK(cudaMemcpy(d_plain.p + lane_plain_off[li], w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+                    if (nd.lazy) { nd.bits.w.clear(); nd.bits.w.shrink_to_fit(); }
+                }
             }
         }
         upload_vec(d_off, lane_plain_off);
@@ -1404,6 +1422,43 @@ int ggq_brwt_serialize_buffer(const ggq_matrix *m, uint8_t **out, size_t *len) {
     *len = bytes.size();
     return GGQ_OK;
     GGQ_CATCH
+}
+
+// Files: the .brwt.annodbg matrix part as the reference reads / writes it, through buffered stdio — no copy of the
+// stream in host memory on either side.
+int ggq_brwt_serialize_file(const ggq_matrix *m, const char *path, uint64_t *n_bytes) {
+    GGQ_TRY
+    if (!m || !path) return fail(GGQ_ERR_ARG, "bad argument");
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(GGQ_ERR_ARG, std::string("cannot create ") + path);
+    std::vector<char> buf(size_t(8) << 20);
+    std::setvbuf(f, buf.data(), _IOFBF, buf.size());
+    ByteSink sink;
+    sink.write = [](void *ctx, const void *src, size_t n) -> size_t { return std::fwrite(src, 1, n, static_cast<FILE *>(ctx)); };
+    sink.ctx = f;
+    int rc = GGQ_OK;
+    try {
+        serialize_brwt(m, sink);
+    } catch (...) {
+        std::fclose(f);
+        throw;
+    }
+    if (std::fclose(f) != 0) rc = fail(GGQ_ERR_INTERNAL, std::string("write failed: ") + path);
+    if (n_bytes) *n_bytes = sink.total;
+    return rc;
+    GGQ_CATCH
+}
+
+int ggq_brwt_load_file(const char *path, int device, ggq_matrix **out) {
+    if (!path || !out) return fail(GGQ_ERR_ARG, "bad argument");
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return fail(GGQ_ERR_FORMAT, std::string("cannot open ") + path);
+    std::vector<char> buf(size_t(8) << 20);
+    std::setvbuf(f, buf.data(), _IOFBF, buf.size());
+    Reader in([](void *ctx, void *dst, size_t n) -> size_t { return std::fread(dst, 1, n, static_cast<FILE *>(ctx)); }, f);
+    const int rc = brwt_load_reader(in, device, out);
+    std::fclose(f);
+    return rc;
 }
 
 // Host only (no device needed): the bytes rrr_vector<63>(bits).serialize() writes — the building block of

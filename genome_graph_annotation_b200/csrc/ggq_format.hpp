@@ -207,7 +207,9 @@ inline void read_rrr63_raw(Reader &in, RrrRaw *r) {
     if (r->invert.bit_size < n_sb || r->btnrp.size() < n_sb) throw ParseError("rrr: bad superblock arrays");
 }
 
-inline void decode_rrr63(const RrrRaw &raw, PlainBits *out) {
+// max_threads: 0 = as many as the vector's length warrants (below); 1 = the calling thread only (the caller runs
+// several decodes side by side: decode_nodes_parallel, ggq_tree.hpp)
+inline void decode_rrr63(const RrrRaw &raw, PlainBits *out, unsigned max_threads = 0) {
     const unsigned BS = 63, K = 32;
     if (raw.empty) { out->resize(0); return; }
     const uint64_t m_size = raw.m_size;
@@ -222,6 +224,10 @@ inline void decode_rrr63(const RrrRaw &raw, PlainBits *out) {
         uint64_t pos = 0;
         const uint64_t b_end = std::min<uint64_t>(n_blocks, sb1 * K);
         for (uint64_t b = sb0 * K; b < b_end; ++b) {
+            // The dummy block sdsl appends when m_size is a multiple of 63 holds nothing — and when it opens a superblock
+            // (m_size a multiple of 2016) that superblock was never "reached" by the construction loop: its pointer and
+            // rank sample are 0 (rrr_vector.hpp:196-238), which is not a pointer running backwards.
+            if (b * BS >= m_size) break;
             if (b % K == 0) {
                 const uint64_t p = btnrp.get(b / K);   // file-controlled: must not run backwards or past the offsets
                 if (p > btnr.bit_size || (b > sb0 * K && p < pos) || (b && p < btnrp.get(b / K - 1)))
@@ -252,6 +258,7 @@ inline void decode_rrr63(const RrrRaw &raw, PlainBits *out) {
         n_thr = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
         if (const char *e = std::getenv("GGQ_LOAD_THREADS")) n_thr = std::max(1, std::atoi(e));
     }
+    if (max_threads) n_thr = std::min(n_thr, max_threads);
     if (n_thr <= 1) {
         decode_range(0, n_sb);
     } else {

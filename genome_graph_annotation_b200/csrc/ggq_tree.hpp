@@ -7,6 +7,8 @@
 // (BRWT.cpp:49), the DFS (= get_row) rank of every leaf column, the root-to-leaf path of every
 // column (assignments_.group()/rank(), BRWT.cpp:21-23,73-74), and the slot arena geometry.
 #pragma once
+#include <atomic>
+#include <thread>
 
 #include <algorithm>
 #include <cstdint>
@@ -64,6 +66,44 @@ struct FlatTree {
 
     uint32_t n_groups() const { return uint32_t(group_hot.size()); }
 };
+
+// Decodes the lazily parsed vectors of a batch of nodes on the host's threads.  Long vectors (>= 2^12 superblocks) are
+// decoded one after the other, each by several threads (decode_rrr63); the others side by side, one vector per thread —
+// a tree of thousands of medium vectors loads at the host's aggregate decode rate, not at one core's.
+inline void decode_nodes_parallel(const std::vector<FlatNode *> &batch) {
+    if (batch.empty()) return;
+    Binomial63::get();   // (built once, before any thread needs it)
+    std::vector<FlatNode *> small;
+    for (FlatNode *n : batch) {
+        const uint64_t n_sb = ((n->raw.m_size + 63) / 63 + 31) / 32;
+        if (n_sb >= (uint64_t(1) << 12) || batch.size() == 1) decode_rrr63(n->raw, &n->bits);
+        else small.push_back(n);
+    }
+    if (small.empty()) return;
+    unsigned n_thr = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+    if (const char *e = std::getenv("GGQ_LOAD_THREADS")) n_thr = unsigned(std::max(1, std::atoi(e)));
+    n_thr = unsigned(std::min<size_t>(n_thr, small.size()));
+    if (n_thr <= 1) {
+        for (FlatNode *n : small) decode_rrr63(n->raw, &n->bits, 1);
+        return;
+    }
+    std::atomic<size_t> next{0};
+    std::vector<std::string> errors(n_thr);
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < n_thr; ++t)
+        pool.emplace_back([&, t] {
+            try {
+                for (size_t i = next.fetch_add(1); i < small.size(); i = next.fetch_add(1))
+                    decode_rrr63(small[i]->raw, &small[i]->bits, 1);
+            } catch (const std::exception &e) {
+                errors[t] = e.what()[0] ? e.what() : "rrr: decode failed";
+                next.store(small.size());   // the others stop at their next vector
+            }
+        });
+    for (std::thread &th : pool) th.join();
+    for (const std::string &e : errors)
+        if (!e.empty()) throw ParseError(e);
+}
 
 // ---- step 1a: parsed pre-order tree -> BFS nodes ------------------------------------------
 inline void flatten_parsed(ParsedNode &&root, FlatTree *t) {

@@ -54,6 +54,9 @@ int ggq_device_count(int *count);
  * flattens it into level-order sibling-interleaved arrays and uploads it once to `device`. */
 int ggq_brwt_load(ggq_read_fn read, void *ctx, int device, ggq_matrix **out);
 int ggq_brwt_load_buffer(const uint8_t *buf, size_t len, size_t *consumed, int device, ggq_matrix **out);
+/* BRWT::load from a file holding the matrix stream (buffered stdio; a missing file: GGQ_ERR_FORMAT, as load() == false).
+ * Host memory during the load: the compressed vectors (about the file size) + at most 1 GiB of decoded bits. */
+int ggq_brwt_load_file(const char *path, int device, ggq_matrix **out);
 
 /* ColMajorCompressed::load (annotation/column_compressed/column_major.cpp:58-79): BE u64 column
  * count + bit_vector_sd streams. */
@@ -92,6 +95,9 @@ int ggq_brwt_inspect_columns(const uint8_t *buf, size_t len, uint32_t *dfs_cols,
  * the image carries the host tree).  Not available for column-major matrices and column shards (GGQ_ERR_INTERNAL). */
 int ggq_brwt_serialize(const ggq_matrix *m, ggq_write_fn write, void *ctx, uint64_t *n_bytes);
 int ggq_brwt_serialize_buffer(const ggq_matrix *m, uint8_t **out, size_t *len);   /* *out: ggq_buffer_free */
+/* The same through buffered stdio, for streams of many gigabytes: no copy of the stream in host memory.  A file that
+ * cannot be created: GGQ_ERR_ARG; a failed write: GGQ_ERR_INTERNAL. */
+int ggq_brwt_serialize_file(const ggq_matrix *m, const char *path, uint64_t *n_bytes);
 
 /* Host only: the bytes sdsl's rrr_vector<63>(bits).serialize() writes for the given plain bits (LSB-first words) —
  * the building block of ggq_brwt_serialize.  *out is malloc'ed (ggq_buffer_free). */

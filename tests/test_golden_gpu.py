@@ -194,3 +194,30 @@ def test_image_with_valid_checksum_but_insane_tables_is_rejected(ggq, tmp_path):
     off, cols = gi.get_rows_csr(np.arange(0, n, 7, dtype=np.uint64))
     assert np.array_equal(off, exp[0]) and np.array_equal(cols, exp[1])
     gi.close()
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "brwt_*.npz"))))
+def test_stream_files(ggq, path, tmp_path):
+    """ggq_brwt_serialize_file / ggq_brwt_load_file (buffered stdio, no copy of the stream in memory): the file is the
+    reference's stream byte for byte, and a matrix loaded from it answers like the reference."""
+    g = np.load(path)
+    data = g["stream"].tobytes()
+    gm = ggq.GpuMatrix.load_brwt(data)
+    f = str(tmp_path / "m.brwt")
+    try:
+        assert gm.serialize_to_file(f) == len(data)
+    finally:
+        gm.close()
+    assert open(f, "rb").read() == data
+    gf = ggq.GpuMatrix.load_brwt_file(f)
+    try:
+        n = int(g["stats"][0])
+        off, cols = gf.get_rows_csr(np.arange(n, dtype=np.uint64))
+        assert np.array_equal(off, g["row_offsets"]) and np.array_equal(cols, g["row_cols"])
+    finally:
+        gf.close()
+    with pytest.raises(ggq.GgqError):
+        ggq.GpuMatrix.load_brwt_file(str(tmp_path / "missing.brwt"))
+    open(f, "wb").write(data[: max(len(data) // 2, 1)])   # truncated: load() == false
+    with pytest.raises(ggq.GgqError):
+        ggq.GpuMatrix.load_brwt_file(f)

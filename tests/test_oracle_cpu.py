@@ -182,6 +182,25 @@ def test_threaded_rrr_decode_of_large_vectors(ref, monkeypatch):
         assert e.code == -1
 
 
+@pytest.mark.parametrize("n", [63, 126, 2015, 2016, 2017, 4032, 2016 * 5, 2016 * 100, 2016 * 4096, 2016 * 4096 + 63])
+@pytest.mark.parametrize("lazy", [True, False])
+def test_vector_lengths_at_the_rrr_block_boundaries(ref, monkeypatch, n, lazy):
+    """sdsl appends an empty dummy block when the length is a multiple of 63; when that block opens a superblock (length
+    a multiple of 2016 = 32 x 63) the superblock's offset pointer and rank sample are 0.  Such a stream is valid and must
+    parse to the reference's statistics (found by the 7e8-row load probe: its root vector is 2016 x 347222 long)."""
+    import genome_graph_annotation_b200 as g
+    if not lazy:
+        monkeypatch.setenv("GGQ_LOAD_EAGER", "1")
+    dense = random_dense(n, 3, 0.3, n % 1000) if n < 10 ** 6 else None
+    cw = ref.pack_columns(dense) if dense is not None else ref.gen_norepl(n, 3, 0.3, seed=5)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=2, threads=4)
+    data = rm.serialize()
+    info = g.inspect_brwt(data)
+    assert (info["num_rows"], info["num_relations"], info["num_nodes"], info["total_column_size"]) == \
+        (n, rm.num_relations, rm.num_nodes, rm.total_column_size)
+    assert info["consumed"] == len(data)
+
+
 def test_rrr_writer_is_byte_identical_to_sdsl(ref, monkeypatch):
     """ggq_rrr63_encode_buffer (host only; the building block of ggq_brwt_serialize) against the reference's
     bit_vector_rrr<63>::serialize on the same bits: every array of sdsl's rrr_vector — block classes, offsets in
