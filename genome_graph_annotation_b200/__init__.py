@@ -97,6 +97,7 @@ def lib():
         "ggq_get_rows_into": (C.c_int, [vp, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p]),
         "ggq_get_column_count": (C.c_int, [vp, C.c_uint64, u64p]),
         "ggq_get_column_into": (C.c_int, [vp, C.c_uint64, u64p, C.c_uint64, u64p]),
+        "ggq_get_column_noalloc": (C.c_int, [vp, C.c_uint64, u64p, C.c_uint64, u64p]),
         "ggq_image_save": (C.c_int, [vp, C.c_char_p]),
         "ggq_image_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
         "ggq_get_labels": (C.c_int, [vp, u64p, C.c_uint64, C.c_double, u64p, u64p, u64p]),
@@ -158,6 +159,9 @@ def _check(rc):
 def _u64(a):
     a = np.ascontiguousarray(a, dtype=np.uint64)
     return a, a.ctypes.data_as(u64p)
+
+
+NOALLOC_MAX_COLUMN_ROWS = 1 << 20   # GGQ_NOALLOC_MAX_COLUMN_ROWS (include/ggq.h)
 
 
 def set_default_option(name, value):
@@ -570,6 +574,13 @@ class GpuMatrix:
         """Ascending set rows of `col` into the caller's uint64 array (e.g. pinned); returns their number."""
         n = C.c_uint64()
         _check(lib().ggq_get_column_into(self._h, col, out.ctypes.data_as(u64p), out.size, C.byref(n)))
+        return n.value
+
+    def get_column_noalloc(self, col, out):
+        """get_column_into through the entry point that allocates nothing on the device (ggq_get_column_noalloc: fixed
+        scratch inside the library, at most NOALLOC_MAX_COLUMN_ROWS set rows); returns their number."""
+        n = C.c_uint64()
+        _check(lib().ggq_get_column_noalloc(self._h, col, out.ctypes.data_as(u64p), out.size, C.byref(n)))
         return n.value
 
     def get_column(self, col):

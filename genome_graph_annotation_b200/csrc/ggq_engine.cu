@@ -2572,4 +2572,70 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
 
 }  // extern "C"
 
+// ------------------------------------------------------------------------------------------
+// ggq_get_column_noalloc: BinaryMatrix::get_column for callers that may not allocate (no counterpart in the reference).
+// The K3 kernels work in a result buffer the engine normally takes from a
+// workspace (cudaMalloc on first use / growth); here that scratch is a file-scope device array of a fixed, modest size
+// that every GPU loading the library holds until exit.  Nothing on this path calls cudaMalloc, cudaFree or an allocating
+// library routine: the kernels run on the default stream, the result leaves with a plain cudaMemcpy.
+// ------------------------------------------------------------------------------------------
+namespace ggq {
+
+constexpr u64 kNoAllocMaxRows = u64(GGQ_NOALLOC_MAX_COLUMN_ROWS);   // set rows of one column: 2^20 ids = 8 MiB of scratch
+static __device__ __align__(256) unsigned long long g_noalloc_column[kNoAllocMaxRows];
+
+// In host code `g_noalloc_column` is only a handle of the symbol, not a device address: the address is looked up once
+// per device, with that device current, and the POINTER is what the kernels get.
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;              // also serialises the calls of one process: they all share the array
+static u64 *g_noalloc_ptr[kNoAllocMaxDevices];
+
+static u64 *noalloc_scratch(int device) {    // caller holds g_noalloc_mu and has made `device` current
+    if (device < 0 || device >= kNoAllocMaxDevices) throw LimitError("device ordinal beyond the no-alloc table");
+    if (!g_noalloc_ptr[device]) {
+        void *p = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_column));
+        if (!p) throw CudaError("cudaGetSymbolAddress returned no address for the no-alloc scratch");
+        g_noalloc_ptr[device] = static_cast<u64 *>(p);
+    }
+    return g_noalloc_ptr[device];
+}
+
+}  // namespace ggq
+
+extern "C" int ggq_get_column_noalloc(const ggq_matrix *m, uint64_t col, uint64_t *rows, uint64_t capacity, uint64_t *n_rows) {
+    GGQ_TRY
+    if (!m || !n_rows || (!rows && capacity)) return fail(GGQ_ERR_ARG, "bad argument");
+    if (m->kind != Matrix::BRWT) return fail(GGQ_ERR_ARG, "ggq_get_column_noalloc: BRWT matrices only");
+    if (int rc = column_check(m, col)) return rc;
+    const u64 cnt = column_count(m, col);
+    *n_rows = cnt;
+    if (cnt > kNoAllocMaxRows)
+        return fail(GGQ_ERR_LIMIT, "ggq_get_column_noalloc: the column has " + std::to_string(cnt) + " set rows, the fixed scratch holds " +
+                                   std::to_string(kNoAllocMaxRows) + " (GGQ_NOALLOC_MAX_COLUMN_ROWS): use ggq_get_column_into");
+    if (cnt > capacity) return fail(GGQ_ERR_ARG, "capacity too small");
+    if (!cnt) return GGQ_OK;   // an empty leaf or ancestor (BRWT.cpp:58-62)
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    CUDA_CHECK(cudaSetDevice(m->device));
+    u64 *d_res = noalloc_scratch(m->device);
+    // Entries [0, cnt) are all written by the enumeration before anything reads them: what the previous call left in the
+    // array needs no clearing.
+    const FlatTree &t = m->tree;
+    const u32 p0 = t.col_path_off[col], p1 = t.col_path_off[col + 1];
+    const u32 leaf_li = t.col_path[p1 - 1];
+    const u64 nb = t.group_nblocks[leaf_li >> 2];
+    if (m->wide()) lane_enumerate_kernel<true><<<u32((nb + 255) / 256), 256>>>(m->img, leaf_li, d_res);
+    else lane_enumerate_kernel<false><<<u32((nb + 255) / 256), 256>>>(m->img, leaf_li, d_res);
+    for (u32 p = p1 - 1; p-- > p0;) {
+        const u32 li = t.col_path[p];
+        if (m->lane_ones_h[li] == m->lane_size_h[li]) continue;   // all ones: identity (BRWT.cpp:77-78)
+        if (m->wide()) lane_select_kernel<true><<<u32((cnt + 255) / 256), 256>>>(m->img, li, d_res, cnt);
+        else lane_select_kernel<false><<<u32((cnt + 255) / 256), 256>>>(m->img, li, d_res, cnt);
+    }
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaMemcpy(rows, d_res, cnt * 8, cudaMemcpyDeviceToHost));   // (default stream: ordered after the kernels)
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 #include "ggq_bv_api.cuh"

@@ -327,6 +327,17 @@ int ggq_get_column(const ggq_matrix *m, uint64_t col, uint64_t **rows, uint64_t 
  * ggq_get_column_count is a host-side lookup (popcount of the column's leaf vector); `capacity` in entries. */
 int ggq_get_column_count(const ggq_matrix *m, uint64_t col, uint64_t *n_rows);
 int ggq_get_column_into(const ggq_matrix *m, uint64_t col, uint64_t *rows, uint64_t capacity, uint64_t *n_rows);
+/* ggq_get_column_into for callers that may not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The result buffer the K3 kernels work in is a fixed device array inside the library (8 MiB, held by every GPU that loads
+ * the library until exit) instead of a workspace buffer: the call performs no cudaMalloc / cudaFree and calls no allocating
+ * library routine.  BRWT matrices only (both slot layouts).  A column with more than GGQ_NOALLOC_MAX_COLUMN_ROWS set rows:
+ * GGQ_ERR_LIMIT, *n_rows = the count (use ggq_get_column_into); `capacity` too small: GGQ_ERR_ARG.  Runs on the default
+ * stream and returns when `rows` (host memory) is filled.  All calls share the one array per device: calls of one process
+ * are serialised inside the library, but work that overlaps on the GPU by other means (several processes' captured graphs
+ * replayed together, a caller's own streams reading the array) races.  Same answer as ggq_get_column_into. */
+#define GGQ_NOALLOC_MAX_COLUMN_ROWS (1u << 20)
+int ggq_get_column_noalloc(const ggq_matrix *m, uint64_t col, uint64_t *rows, uint64_t capacity, uint64_t *n_rows);
 
 /* ------------------------------------------------------------------ bit vectors -------------- */
 
