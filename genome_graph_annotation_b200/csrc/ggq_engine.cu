@@ -3,6 +3,8 @@
 // ggq_bv.cuh (bit_vector_{stat,sd,rrr} layouts).  No CPU fallback anywhere: every compute entry
 // point launches CUDA kernels or fails.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -925,7 +927,7 @@ Workspace::Workspace(const Matrix *m_) : m(m_) {
             CUDA_CHECK(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
         }
     }
-    d_ctrl.alloc(8);
+    d_ctrl.alloc(16);   // 8 control words of K1 + the completion ticket of the direct label kernel
     d_err.alloc(1);
     CUDA_CHECK(cudaMallocHost(&h_ctrl, 32 * sizeof(u64)));
     CUDA_CHECK(cudaEventCreate(&ev0));
@@ -1057,6 +1059,7 @@ static void launch_rows_kernel(const Matrix *m, Workspace *ws, const u64 *proc_r
     u64 batches = (n + m->rb - 1) / m->rb;
     u32 grid = u32(std::min<u64>(std::min(full_grid, grid_cap), (batches + kRowsWarps - 1) / kRowsWarps));
     ws->ran_safe = safe;
+    ws->ctrl_clean = false;   // (K1 writes the control words; only the direct label kernel leaves them zeroed again)
     Img img = m->img;
     void *kargs[] = {&img, &a};
     CUDA_CHECK(cudaLaunchKernel(rows_kernel_fn(safe || m->cap_spill != 0, m->img.multi_leaf != 0, m->img.group_rec16 != nullptr, m->wide()), dim3(grid),
@@ -1780,17 +1783,38 @@ int ggq_get_rows(const ggq_matrix *m, const uint64_t *rows, uint64_t n, ggq_rows
             CUDA_CHECK(cudaSetDevice(m->device));
             const u64 cap_ids = u64(1) << 16;
             ws->reserve_rows(n);
-            ws->stage_reserve((2 + n + 1 + cap_ids) * 8);
+            // pinned block: [total | status | offsets (n + 1) | ids (cap_ids) | completion flag | the rows]
+            ws->stage_reserve((2 + n + 1 + cap_ids + 1 + n) * 8);
             if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
             cudaStream_t st = ws->stream;
-            CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
-            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
-            launch_rows_kernel(m, ws, ws->d_rows.p, nullptr, n);
             u64 *host = reinterpret_cast<u64 *>(ws->h_stage);
+            // Latency form (as in labels_batch_core): the descent reads the row ids straight from the pinned block, the
+            // control words were left cleared by the previous small call, the host polls a flag — two launches in all.
+            static const bool copy_form = [] { const char *e = std::getenv("GGQ_DIRECT_COPY"); return e && *e && *e != '0'; }();
+            u64 *flag = host + 2 + n + 1 + cap_ids, *h_rows = flag + 1;
+            const u64 *d_small_rows = ws->d_rows.p;
+            if (copy_form) {
+                CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+            } else {
+                std::memcpy(h_rows, rows, n * 8);
+                *flag = 0;
+                d_small_rows = h_rows;
+            }
+            if (!ws->ctrl_clean || copy_form) CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 9 * sizeof(u64), st));
+            launch_rows_kernel(m, ws, d_small_rows, nullptr, n);
             small_finish_kernel<<<1, 256, 0, st>>>(ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p,
-                                                  u32(n), host, cap_ids);
+                                                  u32(n), host, cap_ids, copy_form ? nullptr : flag);
             CUDA_CHECK(cudaGetLastError());
-            CUDA_CHECK(cudaStreamSynchronize(st));
+            bool flagged = false;
+            if (!copy_form) {   // (bounded: a failed launch never sets the flag)
+                volatile u64 *f = flag;
+                const auto t_end = std::chrono::steady_clock::now() + std::chrono::milliseconds(2);
+                for (u32 spin = 0; !(flagged = *f != 0); ++spin)
+                    if ((spin & 255u) == 255u && std::chrono::steady_clock::now() > t_end) break;
+                std::atomic_thread_fence(std::memory_order_acquire);
+            }
+            if (!flagged) CUDA_CHECK(cudaStreamSynchronize(st));
+            if (!copy_form) ws->ctrl_clean = true;
             if (host[1] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
             if (!(host[1] & 3)) {
                 ws->launches = 2; ws->kernel_timed = false; ws->last_probes = 0; ws->last_touches = 0;
@@ -2203,6 +2227,7 @@ static u64 min_label_count(u64 n_indices, double ratio) {
 
 constexpr u64 kBatchSmallRows = u64(1) << 14;   // direct form of the label batch: indices of all queries together
 constexpr u64 kBatchSmallQueries = 1024;
+constexpr u64 kZeroCopyRows = 4096;             // direct form: up to this many indices are read straight from pinned memory
 
 // min_counts[q]: a label of query q is kept iff its count is non-zero and >= min_counts[q]
 static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const uint64_t *query_offsets, uint64_t n_queries,
@@ -2249,25 +2274,43 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
         std::memcpy(h_in, query_offsets, (n_queries + 1) * 8);
         if (n_queries) std::memcpy(h_in + n_queries + 1, min_counts, n_queries * 8);
         if (n_staged) std::memcpy(h_in + 2 * n_queries + 1, rows, n * 8);
-        CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in, in_words * 8, cudaMemcpyHostToDevice, st));
-        const u64 *d_batch_rows = direct ? ws->d_qoff.p + 2 * n_queries + 1 : ws->d_rows.p;
+        // Latency form of the direct path (a single query sequence is launch-latency bound: every stream operation costs
+        // microseconds, and concurrent callers contend for the driver): up to kZeroCopyRows indices are READ BY THE
+        // KERNELS FROM THE PINNED BLOCK (each index is read once), the control words were left zeroed by the previous
+        // direct call's kernel, and the host polls the completion flag in pinned memory — two launches, nothing else.
+        // GGQ_DIRECT_COPY=1: the copy / memset / synchronise form (A/B).
+        static const bool copy_form = [] { const char *e = std::getenv("GGQ_DIRECT_COPY"); return e && *e && *e != '0'; }();
+        const bool zero_copy = direct && !copy_form && n <= kZeroCopyRows;
+        const u64 *d_in = zero_copy ? h_in : ws->d_qoff.p;   // [query offsets | minimum counts | rows]
+        if (!zero_copy) CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in, in_words * 8, cudaMemcpyHostToDevice, st));
+        const u64 *d_batch_rows = direct ? d_in + 2 * n_queries + 1 : ws->d_rows.p;
         if (n && !direct) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, rows, n * 8, cudaMemcpyHostToDevice, st));
-        const u64 *d_minc = ws->d_qoff.p + n_queries + 1;
+        const u64 *d_minc = d_in + n_queries + 1;
         bool done = false;
         if (direct) {
             // descent in the caller's order, per-query histogram + threshold writing into pinned memory: ONE wait
             u64 *host = h_in + in_words;
             host[0] = 0;
+            host[1] = 0;
             if (ws->d_tmp.n == 0) ws->d_tmp.alloc(std::max<u64>(n * 16, 1 << 16));
-            CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 8 * sizeof(u64), st));
+            if (!ws->ctrl_clean || copy_form) CUDA_CHECK(cudaMemsetAsync(ws->d_ctrl.p, 0, 9 * sizeof(u64), st));
             launch_rows_kernel(m, ws, d_batch_rows, nullptr, n);
             if (hist_smem > 48 * 1024)   // (a driver call that serialises concurrent callers: only when the opt-in is needed)
                 CUDA_CHECK(cudaFuncSetAttribute(query_labels_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 1024));
             query_labels_direct_kernel<<<u32(n_queries), 256, hist_smem, st>>>(
-                ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p, ws->d_qoff.p, d_minc, u32(nc),
+                ws->d_row_cnt.p, ws->d_row_tmp_off.p, ws->d_tmp.p, ws->d_tmp.n, ws->d_ctrl.p, d_in, d_minc, u32(nc),
                 u32(n_queries), host, cap_pairs);
             CUDA_CHECK(cudaGetLastError());
-            CUDA_CHECK(cudaStreamSynchronize(st));
+            bool flagged = false;
+            if (!copy_form) {   // poll the flag the last CTA sets (bounded: a failed launch never sets it)
+                volatile u64 *flag = host + 1;
+                const auto t_end = std::chrono::steady_clock::now() + std::chrono::milliseconds(2);
+                for (u32 spin = 0; !(flagged = *flag != 0); ++spin)
+                    if ((spin & 255u) == 255u && std::chrono::steady_clock::now() > t_end) break;
+                std::atomic_thread_fence(std::memory_order_acquire);
+            }
+            if (!flagged) CUDA_CHECK(cudaStreamSynchronize(st));
+            ws->ctrl_clean = true;   // the kernel's last CTA cleared the control words
             ws->launches = 2; ws->kernel_timed = false;
             if (host[0] & 1) m->stack_safe.store(true, std::memory_order_relaxed);   // estimate too small: general path, safe mode
             bool ok = (host[0] & 3) == 0;
@@ -2305,7 +2348,11 @@ static int labels_batch_core(const ggq_matrix *m, const uint64_t *rows, const ui
         }
         if (!done) {
             u64 total = 0;
-            if (direct && n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, d_batch_rows, n * 8, cudaMemcpyDeviceToDevice, st));
+            if (zero_copy) {   // the general path reads the query table from device memory
+                CUDA_CHECK(cudaMemcpyAsync(ws->d_qoff.p, h_in, in_words * 8, cudaMemcpyHostToDevice, st));
+                d_minc = ws->d_qoff.p + n_queries + 1;
+            }
+            if (direct && n) CUDA_CHECK(cudaMemcpyAsync(ws->d_rows.p, d_batch_rows, n * 8, cudaMemcpyDefault, st));
             rows_device(m, ws, ws->d_rows.p, n, 4, &total);   // ordered CSR (u32 ids) in ws->d_offsets / ws->d_out
             if (ws->d_qstage_cols.n < total + 1) { ws->d_qstage_cols.alloc(total + total / 8 + 1024); ws->d_qstage_cnt.alloc(total + total / 8 + 1024); }
             if (hist_smem > 48 * 1024)

@@ -135,6 +135,7 @@ struct Workspace {
     DeviceBuf<unsigned char> d_out, d_cub;
     size_t cub_bytes = 0;
     u64 cap_rows = 0;
+    bool ctrl_clean = false;       // d_ctrl[0..8] are zero: the last direct label call cleared them on the device (no memset needed)
     u64 *h_ctrl = nullptr;
     unsigned char *h_stage = nullptr;
     size_t h_stage_bytes = 0;

@@ -195,8 +195,8 @@ gather_rows_kernel(const u32 *tmp_cols, const u64 *row_tmp_off, const u64 *offse
 //   host[2 .. 2+n] = offsets, then the u64 column ids.
 constexpr int kSmallRows = 1024;
 __global__ void __launch_bounds__(256)
-small_finish_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_cols, u64 tmp_cap, const u64 *ctrl,
-                    u32 n, u64 *host, u64 host_cap_ids) {
+small_finish_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_cols, u64 tmp_cap, u64 *ctrl,
+                    u32 n, u64 *host, u64 host_cap_ids, u64 *done) {
     __shared__ u64 s_off[kSmallRows + 1];
     __shared__ u64 s_src[kSmallRows];
     __shared__ u32 s_warp[8];
@@ -239,16 +239,30 @@ small_finish_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_c
         host[0] = total;
         host[1] = (ctrl[4] ? 1u : 0u) | (fits ? 0u : 2u);
     }
-    if (!fits) return;
-    for (u32 q = threadIdx.x; q <= n; q += 256) host[2 + q] = s_off[q];
-    u64 *cols = host + 2 + n + 1;
-    for (u64 p = threadIdx.x; p < total; p += 256) {
-        u32 lo = 0, hi = n;   // last row with s_off[row] <= p
-        while (hi - lo > 1) {
-            const u32 mid = (lo + hi) >> 1;
-            if (s_off[mid] <= p) lo = mid; else hi = mid;
+    if (fits) {
+        for (u32 q = threadIdx.x; q <= n; q += 256) host[2 + q] = s_off[q];
+        u64 *cols = host + 2 + n + 1;
+        for (u64 p = threadIdx.x; p < total; p += 256) {
+            u32 lo = 0, hi = n;   // last row with s_off[row] <= p
+            while (hi - lo > 1) {
+                const u32 mid = (lo + hi) >> 1;
+                if (s_off[mid] <= p) lo = mid; else hi = mid;
+            }
+            cols[p] = tmp_cols[s_src[lo] + (p - s_off[lo])];
         }
-        cols[p] = tmp_cols[s_src[lo] + (p - s_off[lo])];
+    }
+    // `done` (pinned, zeroed by the host before the launch): the control words are left cleared — the next small call on
+    // this workspace needs no memset — and the flag is set once everything above is visible to the host, which may
+    // poll it instead of synchronising the stream.
+    if (done) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            #pragma unroll
+            for (int i = 0; i < 9; ++i) ctrl[i] = 0;
+            __threadfence_system();
+            *reinterpret_cast<volatile u64 *>(done) = 1;
+        }
     }
 }
 
@@ -372,8 +386,28 @@ query_labels_kernel(const u64 *csr_offsets, const u32 *ids, const u64 *query_off
 // (order is irrelevant to a histogram), thresholds it, reserves room with one atomic and writes the kept
 // (column | count << 32) pairs, ascending, into PINNED HOST memory; the host waits once.
 //   host[0] = status, zeroed by the host before the launch (bit 0: descent stack overflow, bit 1: arena too small)
+//   host[1] = completion flag, zeroed by the host before the launch: the LAST CTA to finish (ticket in ctrl[8]) clears
+//   the nine control words — the next direct call on this workspace needs no memset — and then sets it to 1, after
+//   every CTA's writes have been fenced to the system: the host may poll it instead of synchronising the stream
 //   host[2 + 2q], host[3 + 2q] = first pair and number of pairs of query q (first + number > capacity: the pairs
 //   were not written; the host falls back to the general path);  pairs from host[2 + 2 n_queries]
+// query_offsets / min_counts may live in pinned host memory (read once per CTA).
+__device__ __forceinline__ void direct_kernel_epilogue(u64 *ctrl, u32 n_queries, u64 *host) {
+    __threadfence_system();   // every thread: its pairs are visible to the host before the ticket is taken
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long t = atomicAdd(reinterpret_cast<unsigned long long *>(ctrl + 8), 1ull);
+        if (t == n_queries - 1) {   // all other CTAs are past their last read of ctrl and their last write to host
+            __threadfence();
+            #pragma unroll
+            for (int i = 0; i < 9; ++i) ctrl[i] = 0;
+            __threadfence_system();
+            *reinterpret_cast<volatile u64 *>(host + 1) = 1;
+            __threadfence_system();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 query_labels_direct_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32 *tmp_cols, u64 tmp_cap, u64 *ctrl,
                            const u64 *query_offsets, const u64 *min_counts, u32 n_cols, u32 n_queries, u64 *host,
@@ -385,7 +419,8 @@ query_labels_direct_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32
     const u32 q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool overflow = *reinterpret_cast<const int *>(ctrl + 4) != 0, too_small = ctrl[0] > tmp_cap;
     if (overflow || too_small) {
-        if (q == 0 && threadIdx.x == 0) { host[0] = (overflow ? 1u : 0u) | (too_small ? 2u : 0u); __threadfence_system(); }
+        if (q == 0 && threadIdx.x == 0) { host[0] = (overflow ? 1u : 0u) | (too_small ? 2u : 0u); }
+        direct_kernel_epilogue(ctrl, n_queries, host);
         return;
     }
     const u64 r0 = query_offsets[q], r1 = query_offsets[q + 1];
@@ -435,7 +470,7 @@ query_labels_direct_kernel(const u32 *row_cnt, const u64 *row_tmp_off, const u32
         __syncthreads();
         if (threadIdx.x == 0) base_s = base + total;
     }
-    __threadfence_system();
+    direct_kernel_epilogue(ctrl, n_queries, host);
 }
 
 // staging -> dense per-query lists (8 lanes copy one query)
