@@ -1499,6 +1499,7 @@ int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, ui
     if (consumed) *consumed = in.consumed();
     FlatTree t;
     flatten_parsed(std::move(root), &t);
+    t.slot_bits = default_slot_bits();   // (the image size below is that of the layout a load would use now)
     assign_groups(&t);
     assign_geometry(&t);
     u64 rel = 0, tcs = 0;

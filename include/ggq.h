@@ -82,7 +82,7 @@ void ggq_free(ggq_matrix *m);
 /* Host-only: parse + flatten a serialized BRWT exactly as ggq_brwt_load does, without touching the
  * device (works on a box with no GPU; used by the CPU tests and by tools that size a deployment).
  * stats[0..7] = num_rows, num_columns, num_nodes, num_relations, total_column_size (BRWT.hpp:44-49),
- * sibling groups, device image bytes, max depth. */
+ * sibling groups, device image bytes (in the slot layout ggq_set_default_option currently selects), max depth. */
 int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t stats[8]);
 /* Host-only: DFS (= get_row) order of the columns and the root-to-leaf depth of every column of a
  * serialized BRWT.  dfs_cols / depth: num_columns entries each, caller-allocated (may be NULL). */

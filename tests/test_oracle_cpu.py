@@ -201,6 +201,33 @@ def test_vector_lengths_at_the_rrr_block_boundaries(ref, monkeypatch, n, lazy):
     assert info["consumed"] == len(data)
 
 
+def test_inspect_sizes_the_image_in_the_selected_slot_layout(ref):
+    """Host-only deployment sizing (ggq_brwt_inspect_buffer, no GPU): the capacity layout (32-byte slots of 224
+    positions, DESIGN.md 1.1c) stores 8/7 of the plain bits instead of 4/3 — same tree, same statistics, smaller image;
+    both sizes bracketed by the plain bits of the reference's own total_column_size."""
+    import genome_graph_annotation_b200 as g
+    n = 2_000_000
+    cw = ref.gen_norepl(n, 16, 0.2, seed=9)
+    rm = ref.RefMatrix.build_brwt(cw, n, arity=4, threads=8)   # (arity 4: every sibling group fills its four lanes)
+    data = rm.serialize()
+    try:
+        g.set_default_option("wide_slots", 0)
+        a = g.inspect_brwt(data)
+        g.set_default_option("wide_slots", 1)
+        b = g.inspect_brwt(data)
+    finally:
+        g.set_default_option("wide_slots", 0)
+    for k in ("num_rows", "num_columns", "num_nodes", "num_relations", "total_column_size", "groups", "max_depth"):
+        assert a[k] == b[k], k
+    assert np.array_equal(a["dfs_columns"], b["dfs_columns"])
+    plain = rm.total_column_size / 8
+    assert a["total_column_size"] == rm.total_column_size
+    assert 4 / 3 * plain <= a["device_bytes"] < 1.40 * plain      # rank header in every 16-byte slot (+ samples, padding)
+    assert 8 / 7 * plain <= b["device_bytes"] < 1.20 * plain      # one header per 32-byte slot
+    with pytest.raises(g.GgqError):
+        g.set_default_option("no_such_option", 1)
+
+
 def test_rrr_writer_is_byte_identical_to_sdsl(ref, monkeypatch):
     """ggq_rrr63_encode_buffer (host only; the building block of ggq_brwt_serialize) against the reference's
     bit_vector_rrr<63>::serialize on the same bits: every array of sdsl's rrr_vector — block classes, offsets in
