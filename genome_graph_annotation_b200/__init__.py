@@ -83,6 +83,7 @@ def lib():
         "ggq_total_column_size": (C.c_uint64, [vp]),
         "ggq_device_bytes": (C.c_uint64, [vp]),
         "ggq_slot_bits": (C.c_uint32, [vp]),
+        "ggq_rrr63_decode_buffer": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), u64p, C.c_uint64, u64p]),
         "ggq_brwt_serialize_file": (C.c_int, [vp, C.c_char_p, u64p]),
         "ggq_brwt_load_file": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(vp)]),
         "ggq_set_default_option": (C.c_int, [C.c_char_p, C.c_uint64]),
@@ -249,6 +250,18 @@ def rrr63_encode(words, n_bits):
     data = C.string_at(out, n.value)
     lib().ggq_buffer_free(out)
     return data
+
+
+def rrr63_decode(data):
+    """Host only: (plain bits as LSB-first uint64 words, n_bits, bytes consumed) of one serialized rrr_vector<63>, by the
+    loader's own decoder (ggq_rrr63_decode_buffer)."""
+    n_bits, used = C.c_uint64(), C.c_size_t()
+    rc = lib().ggq_rrr63_decode_buffer(data, len(data), C.byref(used), None, 0, C.byref(n_bits))
+    if rc != 0 and n_bits.value == 0:
+        _check(rc)
+    w = np.zeros(max((n_bits.value + 63) // 64, 1), np.uint64)
+    _check(lib().ggq_rrr63_decode_buffer(data, len(data), C.byref(used), w.ctypes.data_as(u64p), w.size, C.byref(n_bits)))
+    return w[: (n_bits.value + 63) // 64], n_bits.value, used.value
 
 
 def inspect_brwt(data):

@@ -1490,6 +1490,27 @@ int ggq_rrr63_encode_buffer(const uint64_t *words, uint64_t n_bits, uint8_t **ou
     GGQ_CATCH
 }
 
+// Host only: the inverse — the loader's own decoder (read_rrr63_raw + decode_rrr63) on one serialized rrr_vector<63>.
+int ggq_rrr63_decode_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t *words, uint64_t n_words, uint64_t *n_bits) {
+    GGQ_TRY
+    if ((!buf && len) || !n_bits || (!words && n_words)) return fail(GGQ_ERR_ARG, "bad argument");
+    Reader in(buf, len);
+    RrrRaw raw;
+    read_rrr63_raw(in, &raw);
+    if (consumed) *consumed = in.consumed();
+    PlainBits bits;
+    decode_rrr63(raw, &bits);
+    *n_bits = bits.size;
+    const u64 need = (bits.size + 63) / 64;
+    if (need > n_words) return fail(GGQ_ERR_ARG, "capacity too small");
+    for (u64 i = 0; i < need; ++i) {   // u32 words (zero padded) -> LSB-first u64 words
+        const u64 lo = 2 * i < bits.w.size() ? bits.w[2 * i] : 0, hi = 2 * i + 1 < bits.w.size() ? bits.w[2 * i + 1] : 0;
+        words[i] = lo | (hi << 32);
+    }
+    return GGQ_OK;
+    GGQ_CATCH
+}
+
 int ggq_brwt_inspect_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t stats[8]) {
     GGQ_TRY
     if ((!buf && len) || !stats) return fail(GGQ_ERR_ARG, "bad argument");

@@ -22,6 +22,11 @@
 #include <thread>
 #include <vector>
 
+// ggq_rrr_simd.cpp (host compiler only): the AVX-512 form of the block walk.  Weak: a program that includes this header
+// without linking that file simply uses the scalar walk.
+extern "C" int ggq_rrr_simd_available() __attribute__((weak));
+extern "C" int ggq_rrr_walk16(const uint64_t (*walk)[64], const unsigned *k, const uint64_t *nr, uint64_t *bits) __attribute__((weak));
+
 namespace ggq {
 
 struct ParseError : std::runtime_error {
@@ -139,6 +144,7 @@ struct PlainBits {
 // ---------------------------------------------------------------------------------------
 struct Binomial63 {
     uint64_t c[64][64];   // c[n][k], n,k <= 63
+    uint64_t walk[63][64];  // c[n][k] with walk[n][0] = 2^63 ("never taken"): the table of decode_batch
     uint8_t space[64];    // bits used to store the block number of a block with k ones (sdsl rrr_helper.hpp:267-272)
     Binomial63() {
         for (int n = 0; n < 64; ++n)
@@ -151,11 +157,48 @@ struct Binomial63 {
             uint64_t b = c[63][k];
             space[k] = (b == 1) ? 0 : uint8_t(64 - __builtin_clzll(b));
         }
+        for (int n = 0; n < 63; ++n)
+            for (int k = 0; k < 64; ++k) walk[n][k] = k == 0 ? (uint64_t(1) << 63) : c[n][k];
     }
     static const Binomial63 &get() {
         static const Binomial63 t;
         return t;
     }
+    // The same walk for N blocks at once, without data-dependent branches.  One block's walk is a chain of dependent
+    // steps (k -> table entry -> compare -> k), and on a BRWT's vectors — dense below the root: a child is as long as
+    // its parent has ones — the branch "bit set?" is a coin flip: the scalar loop spends 300-550 ns per block.  N
+    // independent chains in one loop fill the core's issue slots instead (~100 ns per block).  Walking on to k == 0
+    // (C(n, 1) = n reproduces the closed form of the last one, C(n, k > n) = 0 forces the remaining ones; walk[n][0] is
+    // a value no offset reaches, so a finished lane takes nothing more) leaves nr == 0 for every valid (k, nr);
+    // anything else is a corrupt block.
+    template <int N>
+    void decode_batch(const unsigned *k_in, const uint64_t *nr_in, unsigned n, uint64_t *bits_out) const {
+        uint64_t k[N], nr[N], bits[N];
+        for (int j = 0; j < N; ++j) {
+            const bool live = unsigned(j) < n;
+            k[j] = live ? k_in[j] : 0;
+            nr[j] = live ? nr_in[j] : 0;
+            bits[j] = 0;
+        }
+        for (unsigned i = 0; i < 63; ++i) {
+            const uint64_t *row = walk[62 - i];
+            const uint64_t bit = uint64_t(1) << i;
+            auto lane = [&](int j) {
+                const uint64_t cv = row[k[j]];
+                const uint64_t m = 0 - uint64_t(nr[j] >= cv);   // all ones: the bit is set
+                nr[j] -= cv & m;
+                k[j] += m;
+                bits[j] |= bit & m;
+            };
+            static_assert(N == 8, "the lanes are written out: keep them in registers");
+            lane(0); lane(1); lane(2); lane(3); lane(4); lane(5); lane(6); lane(7);
+        }
+        for (unsigned j = 0; j < n; ++j) {
+            if (k[j] != 0 || nr[j] != 0) throw ParseError("corrupt rrr block");
+            bits_out[j] = bits[j];
+        }
+    }
+
     // Inverse of sdsl's bin_to_nr (rrr_helper.hpp:295-312): bit i of the block is set iff
     // nr >= C(62 - i, k) at the moment i is visited.
     uint64_t decode(unsigned k, uint64_t nr) const {
@@ -217,41 +260,73 @@ inline void decode_rrr63(const RrrRaw &raw, PlainBits *out, unsigned max_threads
     const uint64_t n_blocks = (m_size + BS) / BS;
     const uint64_t n_sb = (n_blocks + K - 1) / K;
     const Binomial63 &B = Binomial63::get();
+    static const bool simd = [] {   // GGQ_RRR_SIMD=0: the scalar walk (tests run both)
+        const char *e = std::getenv("GGQ_RRR_SIMD");
+        return !(e && *e == '0') && ggq_rrr_simd_available && ggq_rrr_walk16 && ggq_rrr_simd_available();
+    }();
     out->resize(m_size);
     // Superblocks (32 blocks = 2016 bits = 63 u32 words) are independent: each starts at its own offset pointer and
     // on a word boundary of the output, so large vectors are decoded by several host threads.
     auto decode_range = [&](uint64_t sb0, uint64_t sb1) {
+        constexpr int kBatch = 16;   // blocks walked together: one AVX-512 walk, or two scalar walks of eight
+        unsigned qk[kBatch], qlen[kBatch], nq = 0;
+        uint64_t qnr[kBatch], qstart[kBatch], qbits[kBatch];
+        auto flush = [&] {
+            if (!nq) return;
+            if (simd) {
+                for (unsigned j = nq; j < kBatch; ++j) { qk[j] = 0; qnr[j] = 0; }   // idle lanes: k = 0, nr = 0 is a valid end state
+                if (!ggq_rrr_walk16(B.walk, qk, qnr, qbits)) throw ParseError("corrupt rrr block");
+            } else {
+                B.decode_batch<8>(qk, qnr, std::min(nq, 8u), qbits);
+                if (nq > 8) B.decode_batch<8>(qk + 8, qnr + 8, nq - 8, qbits + 8);
+            }
+            for (unsigned j = 0; j < nq; ++j) {
+                if (qlen[j] < BS && (qbits[j] >> qlen[j])) throw ParseError("rrr: bits beyond the end");
+                out->or_bits(qstart[j], qbits[j], qlen[j]);
+            }
+            nq = 0;
+        };
+        // (bt holds n_blocks entries of bt.width >= 6 bits and invert / btnrp n_sb entries: checked by read_rrr63_raw)
+        const unsigned btw = bt.width;
         uint64_t pos = 0;
-        const uint64_t b_end = std::min<uint64_t>(n_blocks, sb1 * K);
-        for (uint64_t b = sb0 * K; b < b_end; ++b) {
+        for (uint64_t sb = sb0; sb < sb1; ++sb) {
+            const uint64_t b0 = sb * K, b1 = std::min<uint64_t>(n_blocks, b0 + K);
             // The dummy block sdsl appends when m_size is a multiple of 63 holds nothing — and when it opens a superblock
             // (m_size a multiple of 2016) that superblock was never "reached" by the construction loop: its pointer and
             // rank sample are 0 (rrr_vector.hpp:196-238), which is not a pointer running backwards.
-            if (b * BS >= m_size) break;
-            if (b % K == 0) {
-                const uint64_t p = btnrp.get(b / K);   // file-controlled: must not run backwards or past the offsets
-                if (p > btnr.bit_size || (b > sb0 * K && p < pos) || (b && p < btnrp.get(b / K - 1)))
-                    throw ParseError("rrr: superblock pointer out of range");
-                pos = p;
+            if (b0 * BS >= m_size) break;
+            const uint64_t p = btnrp.get(sb);   // file-controlled: must not run backwards or past the offsets
+            if (p > btnr.bit_size || (sb > sb0 && p < pos) || (sb && p < btnrp.get(sb - 1)))
+                throw ParseError("rrr: superblock pointer out of range");
+            pos = p;
+            const bool inverted = invert.bit(sb);
+            for (uint64_t b = b0; b < b1; ++b) {
+                const uint64_t start = b * BS;
+                if (start >= m_size) break;   // the dummy block
+                const unsigned stored = unsigned(bt.get_bits(b * btw, btw));
+                if (stored > BS) throw ParseError("rrr: block type out of range");
+                const unsigned sp = B.space[stored];  // space[k] == space[63-k]
+                const unsigned k = inverted ? BS - stored : stored;
+                const unsigned len = unsigned(std::min<uint64_t>(BS, m_size - start));
+                if (sp) {
+                    if (pos > btnr.bit_size || sp > btnr.bit_size - pos) throw ParseError("rrr: btnr overrun");
+                    const uint64_t nr = btnr.get_bits(pos, sp);
+                    if (k <= 2) {   // (sparse vectors: one or two ones — the scalar walk ends early)
+                        const uint64_t bits = B.decode(k, nr);
+                        if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");
+                        out->or_bits(start, bits, len);
+                    } else {
+                        qk[nq] = k; qnr[nq] = nr; qstart[nq] = start; qlen[nq] = len;
+                        if (++nq == kBatch) flush();
+                    }
+                    pos += sp;
+                } else if (k == BS) {
+                    if (len < BS) throw ParseError("rrr: bits beyond the end");
+                    out->or_bits(start, ~uint64_t(0), len);
+                }
             }
-            unsigned stored = unsigned(bt.get(b));
-            if (stored > BS) throw ParseError("rrr: block type out of range");
-            unsigned sp = B.space[stored];  // space[k] == space[63-k]
-            unsigned k = invert.bit(b / K) ? BS - stored : stored;
-            uint64_t start = b * BS;
-            unsigned len = unsigned(std::min<uint64_t>(BS, m_size - std::min(m_size, start)));
-            if (sp) {
-                if (pos > btnr.bit_size || sp > btnr.bit_size - pos) throw ParseError("rrr: btnr overrun");
-                uint64_t nr = btnr.get_bits(pos, sp);
-                uint64_t bits = B.decode(k, nr);
-                if (len < BS && (bits >> len)) throw ParseError("rrr: bits beyond the end");
-                out->or_bits(start, bits, len);
-            } else if (k == BS) {
-                if (len < BS) throw ParseError("rrr: bits beyond the end");
-                out->or_bits(start, ~uint64_t(0), len);
-            }
-            pos += sp;
         }
+        flush();
     };
     unsigned n_thr = 1;
     if (n_sb >= (uint64_t(1) << 12)) {

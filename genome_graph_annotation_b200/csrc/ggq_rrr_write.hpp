@@ -91,14 +91,16 @@ inline uint64_t plain_bits(const uint64_t *w, uint64_t n_words, uint64_t pos, un
 }
 
 // rrr_helper<63>::bin_to_nr (rrr_helper.hpp:295-313): the block's offset among the blocks of its class
+// (one step per SET bit — position by count-trailing-zeros — instead of one unpredictable branch per position: the
+// additions are independent of each other, ~20 ns per dense block instead of ~300)
 inline uint64_t rrr63_block_number(uint64_t bin, const Binomial63 &B) {
-    if (bin == 0 || bin == ((uint64_t(1) << 63) - 1)) return 0;
     uint64_t nr = 0;
-    unsigned k = unsigned(__builtin_popcountll(bin)), nn = 63;
+    unsigned k = unsigned(__builtin_popcountll(bin));
     while (bin) {
-        if (bin & 1) { nr += B.c[nn - 1][k]; --k; }
-        bin >>= 1;
-        --nn;
+        const unsigned i = unsigned(__builtin_ctzll(bin));   // a set bit at distance i from the start, k ones still to place
+        nr += B.c[62 - i][k];                                // (C(n, k > n) = 0: a full block numbers 0)
+        --k;
+        bin &= bin - 1;
     }
     return nr;
 }

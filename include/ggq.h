@@ -102,6 +102,11 @@ int ggq_brwt_serialize_file(const ggq_matrix *m, const char *path, uint64_t *n_b
 /* Host only: the bytes sdsl's rrr_vector<63>(bits).serialize() writes for the given plain bits (LSB-first words) —
  * the building block of ggq_brwt_serialize.  *out is malloc'ed (ggq_buffer_free). */
 int ggq_rrr63_encode_buffer(const uint64_t *words, uint64_t n_bits, uint8_t **out, size_t *len);
+/* Host only: the inverse, by the decoder BRWT::load uses here (sdsl rrr_vector.hpp:101-109 load, rrr_helper.hpp
+ * decode): *n_bits = length of the vector; its bits go to `words` (LSB first, capacity n_words; too small: GGQ_ERR_ARG
+ * with *n_bits set).  A damaged vector: GGQ_ERR_FORMAT. */
+int ggq_rrr63_decode_buffer(const uint8_t *buf, size_t len, size_t *consumed, uint64_t *words, uint64_t n_words,
+                            uint64_t *n_bits);
 
 /* The reference's BRWT construction on the device: BRWTBottomUpBuilder::build(columns, partitioner)
  * (annotation/hierarchical_annotation/BRWT_builders.cpp:122-163) with partitioner 0 = get_basic_partitioner(arity)

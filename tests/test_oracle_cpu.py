@@ -201,6 +201,58 @@ def test_vector_lengths_at_the_rrr_block_boundaries(ref, monkeypatch, n, lazy):
     assert info["consumed"] == len(data)
 
 
+def _pack_bits(bits):
+    n = bits.size
+    pad = np.zeros(((n + 63) // 64) * 64, np.uint8)
+    pad[:n] = bits
+    return np.packbits(pad, bitorder="little").view(np.uint64).copy() if n else np.zeros(0, np.uint64)
+
+
+def test_rrr_decoder_reproduces_the_bits_of_reference_streams(ref, monkeypatch):
+    """The loader's rrr_vector<63> decoder (ggq_rrr63_decode_buffer = read_rrr63_raw + decode_rrr63: eight blocks walked
+    together, branch-free) against streams serialized by the REFERENCE's bit_vector_rrr on known bits: every bit, at
+    every density (all classes 0..63 occur, both sides of the inversion rule), at the lengths where sdsl's layout has
+    corners, single- and multi-threaded; damaged offsets are an error or some other vector, never a crash."""
+    import genome_graph_annotation_b200 as g
+    rng = np.random.default_rng(7)
+    for n in [0, 1, 5, 62, 63, 64, 125, 126, 127, 2015, 2016, 2017, 4032, 63 * 32 * 3 + 1, 100_003, 1 << 19]:
+        for d in [0.0, 0.001, 0.02, 0.1, 0.3, 0.5, 0.7, 0.9, 0.99, 1.0]:
+            bits = (rng.random(n) < d).astype(np.uint8)
+            w = _pack_bits(bits)
+            data = ref.RefBitVector.build("rrr", w, n).serialize()
+            got, n_bits, used = g.rrr63_decode(data)
+            assert n_bits == n and used == len(data), (n, d)
+            assert np.array_equal(got, w), (n, d)
+    # every class in one vector: block b has (b mod 64) ones at random places
+    blocks = []
+    for b in range(64 * 40):
+        x = np.zeros(63, np.uint8)
+        x[rng.permutation(63)[: b % 64]] = 1
+        blocks.append(x)
+    bits = np.concatenate(blocks)
+    w = _pack_bits(bits)
+    got, n_bits, _ = g.rrr63_decode(ref.RefBitVector.build("rrr", w, bits.size).serialize())
+    assert n_bits == bits.size and np.array_equal(got, w)
+    # long vectors: several host threads, dense and sparse stretches
+    for thr in ("1", "5"):
+        monkeypatch.setenv("GGQ_LOAD_THREADS", thr)
+        n = 2016 * 5000 + 17
+        bits = (rng.random(n) < 0.25).astype(np.uint8)
+        bits[n // 3:n // 2] = (rng.random(n // 2 - n // 3) < 0.95).astype(np.uint8)
+        w = _pack_bits(bits)
+        data = ref.RefBitVector.build("rrr", w, n).serialize()
+        got, n_bits, _ = g.rrr63_decode(data)
+        assert n_bits == n and np.array_equal(got, w), thr
+    bad = bytearray(data)
+    for i in range(len(bad) // 2, len(bad) // 2 + 512):
+        bad[i] ^= 0xFF
+    try:
+        got, n_bits, _ = g.rrr63_decode(bytes(bad))
+        assert n_bits == n
+    except g.GgqError as e:
+        assert e.code == -1
+
+
 def test_inspect_sizes_the_image_in_the_selected_slot_layout(ref):
     """Host-only deployment sizing (ggq_brwt_inspect_buffer, no GPU): the capacity layout (32-byte slots of 224
     positions, DESIGN.md 1.1c) stores 8/7 of the plain bits instead of 4/3 — same tree, same statistics, smaller image;
